@@ -1,0 +1,13 @@
+"""B200-native (sm_100a) GraphCNNDropEdge hot path -- drop-in for hoangthanh283/graph-representation-learning.
+
+Public surface (mirrors the reference's ``gnn.models`` / ``gnn.cl_warper`` names for this path):
+``GraphCNNDropEdge``, ``GraphConv``, ``NodeSelfAtten``, ``RanPACLayer``, ``make_linear_relu``, ``BaseNetwork``,
+``PackedGraphBatch`` (device CSR/CSC batch), plus the collate / trainer / wrapper modules.
+"""
+from ._lib import GrlError, LIB_PATH  # noqa: F401
+from .graph import PackedGraphBatch  # noqa: F401
+from .networks import (BaseNetwork, GraphCNNDropEdge, GraphConv, NodeSelfAtten, RanPACLayer,  # noqa: F401
+                       make_linear_relu)
+
+__all__ = ["GraphCNNDropEdge", "GraphConv", "NodeSelfAtten", "RanPACLayer", "make_linear_relu", "BaseNetwork",
+           "PackedGraphBatch", "GrlError", "LIB_PATH"]

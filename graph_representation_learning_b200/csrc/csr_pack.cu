@@ -1,0 +1,365 @@
+// CSR / CSC packing of the typed document-graph adjacency (integer, bit-exact work; HBM-bound).
+//
+// Reference semantics: GraphConv.preprocess_adj, gnn/models/networks/robust_gcn.py:53-72 --
+// A'[b, i*(L+1)+t, j] with t=0 the identity block.  Here A' is never materialised: the dense
+// [B,N,L,N] batch tensor is read twice (count, fill) and only rowptr/col/val are written.
+#include "common.cuh"
+#include <cub/device/device_scan.cuh>
+
+namespace grl {
+
+// One warp per (b, i, l) adjacency row of N contiguous elements.  VEC elements per lane per step.
+template <typename T, int VEC>
+__device__ __forceinline__ unsigned load_nz_bits(const T* row, int j0, int N) {
+    // returns a VEC-bit mask of non-zero elements row[j0 .. j0+VEC)
+    unsigned bits = 0;
+    if (VEC > 1 && j0 + VEC <= N) {
+        if constexpr (sizeof(T) * VEC == 16) {
+            uint4 t = __ldcs(reinterpret_cast<const uint4*>(row + j0));
+            const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+            if constexpr (sizeof(T) == 4) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) bits |= ((w[k] << 1) != 0u) << k;  // ignore sign bit: -0.0 is zero
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    bits |= ((w[k] & 0x7FFFu) != 0u) << (2 * k);
+                    bits |= ((w[k] & 0x7FFF0000u) != 0u) << (2 * k + 1);
+                }
+            }
+        } else if constexpr (sizeof(T) * VEC == 8) {
+            uint2 t = __ldcs(reinterpret_cast<const uint2*>(row + j0));
+            const uint32_t w[2] = {t.x, t.y};
+            if constexpr (sizeof(T) == 4) {
+#pragma unroll
+                for (int k = 0; k < 2; ++k) bits |= ((w[k] << 1) != 0u) << k;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    bits |= ((w[k] & 0x7FFFu) != 0u) << (2 * k);
+                    bits |= ((w[k] & 0x7FFF0000u) != 0u) << (2 * k + 1);
+                }
+            }
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k)
+            if (j0 + k < N) bits |= (to_float(row[j0 + k]) != 0.0f) << k;
+    }
+    return bits;
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) csr_count_kernel(const T* __restrict__ adj, int64_t n_adj_rows, int N, int L,
+                                                        int self_loop, int32_t* __restrict__ rowptr) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    if (warp == 0 && lane == 0) rowptr[0] = 0;
+    for (int64_t ar = warp; ar < n_adj_rows; ar += n_warps) {  // ar = (b*N+i)*L + l
+        const T* row = adj + ar * N;
+        int cnt = 0;
+        for (int j0 = lane * VEC; j0 < N; j0 += 32 * VEC) cnt += __popc(load_nz_bits<T, VEC>(row, j0, N));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) {
+            const int64_t node = ar / L;
+            const int l = static_cast<int>(ar - node * L);
+            const int64_t r = node * (L + self_loop) + l + self_loop;
+            rowptr[r + 1] = cnt;
+            if (self_loop && l == 0) rowptr[r] = 1;  // self-loop row (t = 0) holds exactly the diagonal entry
+        }
+    }
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) csr_fill_kernel(const T* __restrict__ adj, int64_t n_adj_rows, int N, int L,
+                                                       int self_loop, const int32_t* __restrict__ rowptr,
+                                                       int32_t* __restrict__ col, float* __restrict__ val) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t ar = warp; ar < n_adj_rows; ar += n_warps) {
+        const T* row = adj + ar * N;
+        const int64_t node = ar / L;
+        const int l = static_cast<int>(ar - node * L);
+        const int64_t r = node * (L + self_loop) + l + self_loop;
+        if (self_loop && l == 0 && lane == 0) {
+            const int32_t e = rowptr[r - 1];
+            col[e] = static_cast<int32_t>(node % N);
+            val[e] = 1.0f;
+        }
+        int32_t out = rowptr[r];
+        const int32_t end = rowptr[r + 1];
+        if (out == end) continue;  // empty row: nothing to re-read
+        for (int jb = 0; jb < N && out < end; jb += 32 * VEC) {
+            const int j0 = jb + lane * VEC;
+            unsigned bits = (j0 < N) ? load_nz_bits<T, VEC>(row, j0, N) : 0u;
+            const int mine = __popc(bits);
+            int incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            int pos = out + incl - mine;
+            while (bits) {
+                const int k = __ffs(bits) - 1;
+                bits &= bits - 1;
+                col[pos] = j0 + k;
+                val[pos] = to_float(row[j0 + k]);
+                ++pos;
+            }
+            out += __shfl_sync(0xffffffffu, incl, 31);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- COO (edge list) -> CSR
+__global__ void coo_count_kernel(const int32_t* __restrict__ edges, int64_t E, int N, int L,
+                                 int32_t* __restrict__ rowptr, int64_t n_nodes) {
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t e = tid; e < E; e += stride) {
+        const int4 q = __ldg(reinterpret_cast<const int4*>(edges) + e);  // (b, i, l, j)
+        const int64_t r = (static_cast<int64_t>(q.x) * N + q.y) * (L + 1) + q.z + 1;
+        atomicAdd(&rowptr[r + 1], 1);
+    }
+    for (int64_t v = tid; v < n_nodes; v += stride) atomicAdd(&rowptr[v * (L + 1) + 1], 1);  // self loop
+}
+
+__global__ void coo_scatter_kernel(const int32_t* __restrict__ edges, const float* __restrict__ weights, int64_t E,
+                                   int N, int L, const int32_t* __restrict__ rowptr, int32_t* __restrict__ cursor,
+                                   int32_t* __restrict__ col, float* __restrict__ val, int64_t n_nodes) {
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t e = tid; e < E; e += stride) {
+        const int4 q = __ldg(reinterpret_cast<const int4*>(edges) + e);
+        const int64_t r = (static_cast<int64_t>(q.x) * N + q.y) * (L + 1) + q.z + 1;
+        const int32_t pos = rowptr[r] + atomicAdd(&cursor[r], 1);
+        col[pos] = q.w;
+        val[pos] = weights ? weights[e] : 1.0f;
+    }
+    for (int64_t v = tid; v < n_nodes; v += stride) {
+        const int32_t pos = rowptr[v * (L + 1)];
+        col[pos] = static_cast<int32_t>(v % N);
+        val[pos] = 1.0f;
+    }
+}
+
+// Rows are tiny (a handful of entries): one thread insertion-sorts its row by (col, val) so the
+// result is independent of the atomic arrival order above.
+__global__ void csr_sort_rows_kernel(const int32_t* __restrict__ rowptr, int64_t R, int32_t* __restrict__ col,
+                                     float* __restrict__ val) {
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t r = tid; r < R; r += stride) {
+        const int32_t s = rowptr[r], e = rowptr[r + 1];
+        for (int32_t a = s + 1; a < e; ++a) {
+            const int32_t c = col[a];
+            const float v = val[a];
+            int32_t b = a - 1;
+            while (b >= s && (col[b] > c || (col[b] == c && val[b] > v))) {
+                col[b + 1] = col[b];
+                val[b + 1] = val[b];
+                --b;
+            }
+            col[b + 1] = c;
+            val[b + 1] = v;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- CSR -> CSC (+perm)
+__global__ void csc_count_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int64_t R,
+                                 int rows_per_graph, int N, int32_t* __restrict__ colptr) {
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    if (tid == 0) colptr[0] = 0;
+    for (int64_t r = tid; r < R; r += stride) {
+        const int64_t base = (r / rows_per_graph) * N;
+        for (int32_t e = rowptr[r]; e < rowptr[r + 1]; ++e) atomicAdd(&colptr[base + col[e] + 1], 1);
+    }
+}
+
+__global__ void csc_scatter_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int64_t R,
+                                   int rows_per_graph, int N, const int32_t* __restrict__ colptr,
+                                   int32_t* __restrict__ cursor, int32_t* __restrict__ tmp_e,
+                                   int32_t* __restrict__ tmp_r) {
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t r = tid; r < R; r += stride) {
+        const int64_t base = (r / rows_per_graph) * N;
+        for (int32_t e = rowptr[r]; e < rowptr[r + 1]; ++e) {
+            const int64_t c = base + col[e];
+            const int32_t pos = colptr[c] + atomicAdd(&cursor[c], 1);
+            tmp_e[pos] = e;
+            tmp_r[pos] = static_cast<int32_t>(r);
+        }
+    }
+}
+
+// One warp per column: rank every entry by its CSR position (unique) -> deterministic order.
+__global__ void __launch_bounds__(256) csc_rank_kernel(const int32_t* __restrict__ colptr, int64_t n_cols,
+                                                       const int32_t* __restrict__ tmp_e,
+                                                       const int32_t* __restrict__ tmp_r,
+                                                       int32_t* __restrict__ rowidx, int32_t* __restrict__ perm) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t c = warp; c < n_cols; c += n_warps) {
+        const int32_t s = colptr[c], d = colptr[c + 1] - s;
+        for (int32_t a = lane; a < d; a += 32) {
+            const int32_t mine = tmp_e[s + a];
+            int32_t rank = 0;
+            for (int32_t t = 0; t < d; ++t) rank += (tmp_e[s + t] < mine);
+            perm[s + rank] = mine;
+            rowidx[s + rank] = tmp_r[s + a];
+        }
+    }
+}
+
+static inline int grid_for(int64_t work_items, int threads, int items_per_thread = 1) {
+    int64_t blocks = (work_items + static_cast<int64_t>(threads) * items_per_thread - 1) /
+                     (static_cast<int64_t>(threads) * items_per_thread);
+    const int64_t cap = static_cast<int64_t>(kNumSMs) * 64;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+template <typename T>
+static int launch_count(const T* adj, int B, int N, int L, int self_loop, int32_t* rowptr, cudaStream_t st) {
+    const int64_t rows = static_cast<int64_t>(B) * N * L;
+    const int grid = grid_for(rows * 32, 256);
+    constexpr int V16 = 16 / sizeof(T), V8 = 8 / sizeof(T);
+    if (N % V16 == 0 && aligned_to(adj, 16)) csr_count_kernel<T, V16><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr);
+    else if (N % V8 == 0 && aligned_to(adj, 8)) csr_count_kernel<T, V8><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr);
+    else csr_count_kernel<T, 1><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr);
+    GRL_LAUNCH_CHECK("csr_count_kernel");
+    return 0;
+}
+
+template <typename T>
+static int launch_fill(const T* adj, int B, int N, int L, int self_loop, const int32_t* rowptr, int32_t* col, float* val,
+                       cudaStream_t st) {
+    const int64_t rows = static_cast<int64_t>(B) * N * L;
+    const int grid = grid_for(rows * 32, 256);
+    constexpr int V16 = 16 / sizeof(T), V8 = 8 / sizeof(T);
+    if (N % V16 == 0 && aligned_to(adj, 16))
+        csr_fill_kernel<T, V16><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, col, val);
+    else if (N % V8 == 0 && aligned_to(adj, 8))
+        csr_fill_kernel<T, V8><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, col, val);
+    else
+        csr_fill_kernel<T, 1><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, col, val);
+    GRL_LAUNCH_CHECK("csr_fill_kernel");
+    return 0;
+}
+
+}  // namespace grl
+
+using namespace grl;
+
+extern "C" int grl_csr_count(const void* adj, int adj_dtype, int B, int N, int L, int self_loop, int32_t* rowptr,
+                             void* stream) {
+    GRL_CHECK_ARG(adj && rowptr, GRL_E_BADARG, "grl_csr_count: null pointer");
+    GRL_CHECK_ARG(B > 0 && N > 0 && L > 0, GRL_E_BADARG, "grl_csr_count: B=%d N=%d L=%d must be positive", B, N, L);
+    self_loop = self_loop ? 1 : 0;
+    GRL_CHECK_ARG(static_cast<int64_t>(B) * N * (L + 1) < INT32_MAX, GRL_E_UNSUP, "grl_csr_count: too many rows for int32");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (adj_dtype == GRL_F32) return launch_count(static_cast<const float*>(adj), B, N, L, self_loop, rowptr, st);
+    if (adj_dtype == GRL_F16) return launch_count(static_cast<const __half*>(adj), B, N, L, self_loop, rowptr, st);
+    set_error("grl_csr_count: adjacency dtype %d unsupported (f32 or f16)", adj_dtype);
+    return GRL_E_UNSUP;
+}
+
+extern "C" int grl_csr_fill(const void* adj, int adj_dtype, int B, int N, int L, int self_loop, const int32_t* rowptr,
+                            int32_t* col, float* val, void* stream) {
+    GRL_CHECK_ARG(adj && rowptr && col && val, GRL_E_BADARG, "grl_csr_fill: null pointer");
+    GRL_CHECK_ARG(B > 0 && N > 0 && L > 0, GRL_E_BADARG, "grl_csr_fill: B=%d N=%d L=%d must be positive", B, N, L);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    self_loop = self_loop ? 1 : 0;
+    if (adj_dtype == GRL_F32) return launch_fill(static_cast<const float*>(adj), B, N, L, self_loop, rowptr, col, val, st);
+    if (adj_dtype == GRL_F16) return launch_fill(static_cast<const __half*>(adj), B, N, L, self_loop, rowptr, col, val, st);
+    set_error("grl_csr_fill: adjacency dtype %d unsupported (f32 or f16)", adj_dtype);
+    return GRL_E_UNSUP;
+}
+
+extern "C" size_t grl_scan_workspace_bytes(int64_t n) {
+    size_t bytes = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, bytes, static_cast<int32_t*>(nullptr), static_cast<int32_t*>(nullptr),
+                                  static_cast<int>(n));
+    return bytes + 256;
+}
+
+extern "C" int grl_scan_inclusive_i32(int32_t* data, int64_t n, void* workspace, size_t workspace_bytes, void* stream) {
+    GRL_CHECK_ARG(data && workspace, GRL_E_BADARG, "grl_scan_inclusive_i32: null pointer");
+    GRL_CHECK_ARG(n > 0 && n < INT32_MAX, GRL_E_BADARG, "grl_scan_inclusive_i32: bad n");
+    size_t need = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, need, data, data, static_cast<int>(n));
+    GRL_CHECK_ARG(workspace_bytes >= need, GRL_E_WORKSPACE, "grl_scan_inclusive_i32: workspace %zu < %zu", workspace_bytes, need);
+    cudaError_t e = cub::DeviceScan::InclusiveSum(workspace, need, data, data, static_cast<int>(n),
+                                                  static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "cub::DeviceScan::InclusiveSum");
+    return 0;
+}
+
+extern "C" int grl_coo_count(const int32_t* edges, int64_t E, int B, int N, int L, int32_t* rowptr, void* stream) {
+    GRL_CHECK_ARG(rowptr && (edges || E == 0), GRL_E_BADARG, "grl_coo_count: null pointer");
+    GRL_CHECK_ARG(E == 0 || aligned_to(edges, 16), GRL_E_ALIGN, "grl_coo_count: edges must be 16-byte aligned");
+    const int64_t n_nodes = static_cast<int64_t>(B) * N;
+    coo_count_kernel<<<grid_for(E > n_nodes ? E : n_nodes, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        edges, E, N, L, rowptr, n_nodes);
+    GRL_LAUNCH_CHECK("coo_count_kernel");
+    return 0;
+}
+
+extern "C" int grl_coo_fill(const int32_t* edges, const float* weights, int64_t E, int B, int N, int L,
+                            const int32_t* rowptr, int32_t* cursor, int32_t* col, float* val, void* stream) {
+    GRL_CHECK_ARG(rowptr && cursor && col && val && (edges || E == 0), GRL_E_BADARG, "grl_coo_fill: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t n_nodes = static_cast<int64_t>(B) * N, R = n_nodes * (L + 1);
+    cudaError_t e = cudaMemsetAsync(cursor, 0, sizeof(int32_t) * R, st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(cursor)");
+    coo_scatter_kernel<<<grid_for(E > n_nodes ? E : n_nodes, 256), 256, 0, st>>>(edges, weights, E, N, L, rowptr, cursor,
+                                                                                   col, val, n_nodes);
+    GRL_LAUNCH_CHECK("coo_scatter_kernel");
+    csr_sort_rows_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, R, col, val);
+    GRL_LAUNCH_CHECK("csr_sort_rows_kernel");
+    return 0;
+}
+
+extern "C" size_t grl_csr_transpose_workspace_bytes(int64_t n_nodes, int64_t nnz) {
+    return sizeof(int32_t) * static_cast<size_t>(n_nodes + 2 * nnz) + 256 + grl_scan_workspace_bytes(n_nodes);
+}
+
+extern "C" int grl_csr_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, int L, int64_t nnz,
+                                 int32_t* colptr, int32_t* rowidx, int32_t* perm, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+    GRL_CHECK_ARG(rowptr && col && colptr && rowidx && perm && workspace, GRL_E_BADARG, "grl_csr_transpose: null pointer");
+    const int64_t n_nodes = static_cast<int64_t>(B) * N, R = n_nodes * (L + 1);
+    GRL_CHECK_ARG(workspace_bytes >= grl_csr_transpose_workspace_bytes(n_nodes, nnz), GRL_E_WORKSPACE,
+                  "grl_csr_transpose: workspace too small");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int32_t* cursor = static_cast<int32_t*>(workspace);
+    int32_t* tmp_e = cursor + n_nodes;
+    int32_t* tmp_r = tmp_e + nnz;
+    uintptr_t scan_ws = reinterpret_cast<uintptr_t>(tmp_r + nnz);
+    scan_ws = (scan_ws + 255) & ~static_cast<uintptr_t>(255);
+    const size_t scan_bytes = grl_scan_workspace_bytes(n_nodes) - 256;
+
+    cudaError_t e = cudaMemsetAsync(colptr, 0, sizeof(int32_t) * (n_nodes + 1), st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(colptr)");
+    e = cudaMemsetAsync(cursor, 0, sizeof(int32_t) * n_nodes, st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(cursor)");
+    const int rows_per_graph = N * (L + 1);
+    csc_count_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, col, R, rows_per_graph, N, colptr);
+    GRL_LAUNCH_CHECK("csc_count_kernel");
+    int rc = grl_scan_inclusive_i32(colptr + 1, n_nodes, reinterpret_cast<void*>(scan_ws), scan_bytes, stream);
+    if (rc) return rc;
+    csc_scatter_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, col, R, rows_per_graph, N, colptr, cursor, tmp_e, tmp_r);
+    GRL_LAUNCH_CHECK("csc_scatter_kernel");
+    csc_rank_kernel<<<grid_for(n_nodes * 32, 256), 256, 0, st>>>(colptr, n_nodes, tmp_e, tmp_r, rowidx, perm);
+    GRL_LAUNCH_CHECK("csc_rank_kernel");
+    return 0;
+}

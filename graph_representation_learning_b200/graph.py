@@ -1,0 +1,183 @@
+"""Device-resident packed batch of typed document graphs (CSR + CSC of the reference's ``A'``).
+
+The reference keeps the batch adjacency dense -- ``B x N x L x N`` from the collate
+(gnn/data_generator/base_dataloader.py:57) turned into ``A' = B x (L+1)N x N`` by
+``GraphConv.preprocess_adj`` (gnn/models/networks/robust_gcn.py:53-72).  Here the same matrix is
+held as CSR (forward gather) and CSC+perm (transposed gather for the gradient):
+
+    row r = (b*N + i)*(L+1) + t     t = 0: self loop, t = l+1: edge type l
+    col   = local node j of graph b (ascending inside a row)
+    val   = adjacency value as fp32 (1.0 for binary graphs and for self loops)
+
+All packing runs in the CUDA library (csrc/csr_pack.cu); nothing here touches the CPU.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+@dataclass
+class PackedGraphBatch:
+    B: int
+    N: int
+    L: int
+    nnz: int                      # number of stored entries (or capacity when packed without a host sync)
+    rowptr: torch.Tensor          # int32 [R+1]
+    col: torch.Tensor             # int32 [nnz]
+    val: torch.Tensor             # float32 [nnz]
+    colptr: Optional[torch.Tensor] = None   # int32 [B*N+1]
+    rowidx: Optional[torch.Tensor] = None   # int32 [nnz]   global CSR row of each CSC entry
+    perm: Optional[torch.Tensor] = None     # int32 [nnz]   CSR position of each CSC entry
+
+    @property
+    def num_nodes(self) -> int:
+        return self.B * self.N
+
+    @property
+    def num_rows(self) -> int:
+        return self.B * self.N * (self.L + 1)
+
+    @property
+    def device(self) -> torch.device:
+        return self.rowptr.device
+
+    # ------------------------------------------------------------------ builders
+    @staticmethod
+    def from_dense(adj: torch.Tensor, nnz_capacity: Optional[int] = None, with_transpose: bool = True,
+                   self_loop: bool = True) -> "PackedGraphBatch":
+        """Pack the collate's dense ``[B, N, L, N]`` adjacency (fp16 or fp32, layout [b, start, type, end]).
+
+        ``nnz_capacity``: give an upper bound to skip the one host read of ``rowptr[R]``.
+        ``self_loop=False``: ``adj`` is an already preprocessed ``A'`` viewed as ``[B, N, L+1, N]`` (its
+        identity block, possibly DropEdge-masked, is taken as data).
+        """
+        _lib.require_cuda(adj, "adjacency")
+        if adj.dim() != 4 or adj.shape[1] != adj.shape[3]:
+            raise _lib.GrlError(f"adjacency must be [B, N, L, N], got {tuple(adj.shape)}")
+        if adj.dtype not in (torch.float16, torch.float32):
+            adj = adj.float()
+        adj = adj.contiguous()
+        B, N, T, _ = adj.shape
+        sl = 1 if self_loop else 0
+        L = T if self_loop else T - 1
+        lib = _lib.load()
+        dev = adj.device
+        st = _lib.stream_ptr(dev)
+        R = B * N * (L + 1)
+        rowptr = torch.empty(R + 1, dtype=torch.int32, device=dev)
+        code = _lib.dtype_code(adj)
+        _lib.check(lib.grl_csr_count(adj.data_ptr(), code, B, N, T, sl, rowptr.data_ptr(), st), "grl_csr_count")
+        ws_bytes = lib.grl_scan_workspace_bytes(R)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.grl_scan_inclusive_i32(rowptr.data_ptr() + 4, R, ws.data_ptr(), ws_bytes, st),
+                   "grl_scan_inclusive_i32")
+        _lib.count_launch(2)
+        nnz = int(rowptr[-1].item()) if nnz_capacity is None else int(nnz_capacity)
+        col = torch.empty(nnz, dtype=torch.int32, device=dev)
+        val = torch.zeros(nnz, dtype=torch.float32, device=dev) if nnz_capacity is not None else \
+            torch.empty(nnz, dtype=torch.float32, device=dev)
+        _lib.check(lib.grl_csr_fill(adj.data_ptr(), code, B, N, T, sl, rowptr.data_ptr(), col.data_ptr(),
+                                    val.data_ptr(), st), "grl_csr_fill")
+        _lib.count_launch(1)
+        g = PackedGraphBatch(B, N, L, nnz, rowptr, col, val)
+        if with_transpose:
+            g.build_transpose()
+        return g
+
+    @staticmethod
+    def from_edges(edges: torch.Tensor, B: int, N: int, L: int, weights: Optional[torch.Tensor] = None,
+                   with_transpose: bool = True) -> "PackedGraphBatch":
+        """Pack an edge list ``int32 [E, 4] = (b, i, l, j)`` (node indices already include the collate's pad
+        offset).  Self loops are added here, exactly once per node, as type-0 rows."""
+        _lib.require_cuda(edges, "edges")
+        if edges.dim() != 2 or edges.shape[1] != 4:
+            raise _lib.GrlError(f"edges must be [E, 4], got {tuple(edges.shape)}")
+        edges = edges.to(torch.int32).contiguous()
+        E = edges.shape[0]
+        if weights is not None:
+            weights = weights.to(device=edges.device, dtype=torch.float32).contiguous()
+        lib = _lib.load()
+        dev = edges.device
+        st = _lib.stream_ptr(dev)
+        R = B * N * (L + 1)
+        rowptr = torch.zeros(R + 1, dtype=torch.int32, device=dev)
+        _lib.check(lib.grl_coo_count(_lib.ptr(edges) if E else 0, E, B, N, L, rowptr.data_ptr(), st), "grl_coo_count")
+        ws_bytes = lib.grl_scan_workspace_bytes(R)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.grl_scan_inclusive_i32(rowptr.data_ptr() + 4, R, ws.data_ptr(), ws_bytes, st),
+                   "grl_scan_inclusive_i32")
+        nnz = E + B * N
+        col = torch.empty(nnz, dtype=torch.int32, device=dev)
+        val = torch.empty(nnz, dtype=torch.float32, device=dev)
+        cursor = torch.empty(R, dtype=torch.int32, device=dev)
+        _lib.check(lib.grl_coo_fill(_lib.ptr(edges) if E else 0, _lib.ptr(weights), E, B, N, L, rowptr.data_ptr(),
+                                    cursor.data_ptr(), col.data_ptr(), val.data_ptr(), st), "grl_coo_fill")
+        _lib.count_launch(5)
+        g = PackedGraphBatch(B, N, L, nnz, rowptr, col, val)
+        if with_transpose:
+            g.build_transpose()
+        return g
+
+    def build_transpose(self) -> None:
+        """CSC + perm for the transposed SpMM of the backward pass (csrc/csr_pack.cu)."""
+        if self.colptr is not None:
+            return
+        lib = _lib.load()
+        dev = self.device
+        n_nodes = self.num_nodes
+        self.colptr = torch.empty(n_nodes + 1, dtype=torch.int32, device=dev)
+        self.rowidx = torch.empty(self.nnz, dtype=torch.int32, device=dev)
+        self.perm = torch.empty(self.nnz, dtype=torch.int32, device=dev)
+        ws_bytes = lib.grl_csr_transpose_workspace_bytes(n_nodes, self.nnz)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.grl_csr_transpose(self.rowptr.data_ptr(), self.col.data_ptr(), self.B, self.N, self.L,
+                                         self.nnz, self.colptr.data_ptr(), self.rowidx.data_ptr(),
+                                         self.perm.data_ptr(), ws.data_ptr(), ws_bytes, _lib.stream_ptr(dev)),
+                   "grl_csr_transpose")
+        _lib.count_launch(4)
+
+    # ------------------------------------------------------------------ DropEdge
+    def edge_weights(self, p: float, seed: int = 0, stream_id: int = 0,
+                     mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Per-entry weights of one layer: ``val * keep / (1-p)`` (reference: nn.Dropout(p=0.3) on A',
+        gnn/models/networks/drop_robust_gcn.py:38,76,80,85).  ``mask`` (uint8 [nnz], CSR order) injects
+        the keep bits for parity tests; otherwise Philox(seed, stream_id, entry)."""
+        if p == 0.0 and mask is None:
+            return self.val
+        if mask is not None:
+            _lib.require_cuda(mask, "edge mask")
+            if mask.dtype != torch.uint8 or mask.numel() != self.nnz:
+                raise _lib.GrlError("edge mask must be uint8 with one entry per stored non-zero")
+            mask = mask.contiguous()
+        w = torch.empty_like(self.val)
+        _lib.check(_lib.load().grl_dropedge_weights(self.val.data_ptr(), _lib.ptr(mask), self.nnz, float(p),
+                                                    int(seed) & (2**64 - 1), int(stream_id), w.data_ptr(),
+                                                    _lib.stream_ptr(self.device)), "grl_dropedge_weights")
+        _lib.count_launch(1)
+        return w
+
+    def to_dense(self, w: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Dense ``A'`` ``[B, (L+1)N, N]`` fp32 (what the reference's preprocess_adj returns); tests / debugging."""
+        R = self.num_rows
+        counts = (self.rowptr[1:] - self.rowptr[:-1]).long()
+        rows = torch.repeat_interleave(torch.arange(R, device=self.device), counts)
+        n = rows.numel()
+        out = torch.zeros(R, self.N, dtype=torch.float32, device=self.device)
+        out.index_put_((rows, self.col.long()[:n]), (self.val if w is None else w)[:n], accumulate=True)
+        return out.view(self.B, self.N * (self.L + 1), self.N)
+
+    def gather_dense_mask(self, dense_mask: torch.Tensor) -> torch.Tensor:
+        """Test helper: pick the keep bits of a reference-style dense mask ``[B, (L+1)N, N]`` at the stored
+        entries (CSR order) -> uint8 [nnz]."""
+        R = self.num_rows
+        counts = (self.rowptr[1:] - self.rowptr[:-1]).long()
+        rows = torch.repeat_interleave(torch.arange(R, device=self.device), counts)
+        rows_per_graph = self.N * (self.L + 1)
+        b = rows // rows_per_graph
+        rr = rows % rows_per_graph
+        return (dense_mask[b, rr, self.col.long()[: rows.numel()]] != 0).to(torch.uint8)

@@ -1,0 +1,236 @@
+"""Autograd operators of the hot path, each a thin launcher of C-ABI kernels (include/grl_b200.h).
+
+* ``spmm_aggregate``  -- K3+K4 of SURVEY.md: DropEdge-weighted multi-relational aggregation
+  (reference: torch.matmul(A', V), gnn/models/networks/robust_gcn.py:45-47) and its transposed gradient.
+* ``linear_act``      -- Linear (+bias) (+ReLU) (+dropout) over a *virtual concat* of inputs
+  (reference: make_linear_relu / nn.Linear / F.relu / nn.Dropout / torch.cat,
+  gnn/models/networks/robust_gcn.py:10-11, drop_robust_gcn.py:64,84-89,99-103).
+* ``graph_conv``      -- aggregate-then-project GraphConv with the ReLU/dropout epilogue fused
+  (reference: GraphConv.forward, robust_gcn.py:32-51 + drop_robust_gcn.py:76-77).
+
+Dense contractions go through ``gemm`` below.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from .graph import PackedGraphBatch
+
+
+# ----------------------------------------------------------------------------------------------
+# kernel launchers (no autograd)
+# ----------------------------------------------------------------------------------------------
+def _row_major_2d(t: torch.Tensor, name: str) -> int:
+    """returns the leading dimension (elements) of a 2-D row-major view"""
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise _lib.GrlError(f"{name} must be a 2-D row-major view, got shape {tuple(t.shape)} stride {t.stride()}")
+    return t.stride(0) if t.shape[0] > 1 else max(t.stride(0), t.shape[1])
+
+
+def spmm_fwd_(g: PackedGraphBatch, w: torch.Tensor, X: torch.Tensor, Y: torch.Tensor) -> None:
+    """Y[r, :F] = sum_e w[e] X[base(r)+col[e], :F];  Y is a [R, F] view (possibly a column slice)."""
+    ldx, ldy = _row_major_2d(X, "X"), _row_major_2d(Y, "Y")
+    F = X.shape[1]
+    if X.shape[0] != g.num_nodes or Y.shape[0] != g.num_rows or Y.shape[1] != F or X.dtype != Y.dtype:
+        raise _lib.GrlError(f"spmm_fwd shape mismatch: X {tuple(X.shape)} Y {tuple(Y.shape)} for {g.num_nodes} nodes")
+    _lib.check(_lib.load().grl_spmm_fwd(g.rowptr.data_ptr(), g.col.data_ptr(), w.data_ptr(), X.data_ptr(), ldx,
+                                        Y.data_ptr(), ldy, _lib.dtype_code(X), g.B, g.N, g.L, F,
+                                        _lib.stream_ptr(X.device)), "grl_spmm_fwd")
+    _lib.count_launch(1)
+
+
+def spmm_bwd_(g: PackedGraphBatch, w: torch.Tensor, dY: torch.Tensor, dX: torch.Tensor, accumulate: bool = False) -> None:
+    """dX[c, :F] (+)= sum_k w[perm[k]] dY[rowidx[k], :F]"""
+    if g.colptr is None:
+        g.build_transpose()
+    lddy, lddx = _row_major_2d(dY, "dY"), _row_major_2d(dX, "dX")
+    F = dX.shape[1]
+    if dX.shape[0] != g.num_nodes or dY.shape[0] != g.num_rows or dY.shape[1] != F or dX.dtype != dY.dtype:
+        raise _lib.GrlError(f"spmm_bwd shape mismatch: dY {tuple(dY.shape)} dX {tuple(dX.shape)}")
+    _lib.check(_lib.load().grl_spmm_bwd(g.colptr.data_ptr(), g.rowidx.data_ptr(), g.perm.data_ptr(), w.data_ptr(),
+                                        dY.data_ptr(), lddy, dX.data_ptr(), lddx, _lib.dtype_code(dX), g.B, g.N, g.L, F,
+                                        1 if accumulate else 0, _lib.stream_ptr(dX.device)), "grl_spmm_bwd")
+    _lib.count_launch(1)
+
+
+def epilogue_fwd_(X: torch.Tensor, bias: Optional[torch.Tensor], Y: torch.Tensor, relu: bool, p: float,
+                  mask: Optional[torch.Tensor], seed: int, stream_id: int) -> None:
+    flags = (_lib.EPI_BIAS if bias is not None else 0) | (_lib.EPI_RELU if relu else 0) | \
+            (_lib.EPI_DROPOUT if p > 0.0 else 0)
+    M, C = X.shape
+    if mask is not None:
+        if mask.dtype != torch.uint8 or mask.numel() != M * C or not mask.is_contiguous():
+            raise _lib.GrlError("dropout mask must be contiguous uint8 [M, C]")
+    if bias is not None and (bias.dtype != torch.float32 or not bias.is_contiguous()):
+        raise _lib.GrlError("bias must be contiguous fp32")
+    _lib.check(_lib.load().grl_bias_act_dropout_fwd(X.data_ptr(), _row_major_2d(X, "X"), _lib.ptr(bias), Y.data_ptr(),
+                                                    _row_major_2d(Y, "Y"), _lib.dtype_code(X), M, C, flags, float(p),
+                                                    _lib.ptr(mask), int(seed) & (2**64 - 1), int(stream_id),
+                                                    _lib.stream_ptr(X.device)), "grl_bias_act_dropout_fwd")
+    _lib.count_launch(1)
+
+
+def epilogue_bwd_(dY: torch.Tensor, Y: Optional[torch.Tensor], dX: torch.Tensor, relu: bool, p: float) -> None:
+    flags = (_lib.EPI_RELU if relu else 0) | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+    M, C = dY.shape
+    _lib.check(_lib.load().grl_bias_act_dropout_bwd(dY.data_ptr(), _row_major_2d(dY, "dY"), _lib.ptr(Y),
+                                                    _row_major_2d(Y, "Y") if Y is not None else C, dX.data_ptr(),
+                                                    _row_major_2d(dX, "dX"), _lib.dtype_code(dY), M, C, flags, float(p),
+                                                    _lib.stream_ptr(dY.device)), "grl_bias_act_dropout_bwd")
+    _lib.count_launch(1)
+
+
+def colsum(X: torch.Tensor) -> torch.Tensor:
+    out = torch.zeros(X.shape[1], dtype=torch.float32, device=X.device)
+    _lib.check(_lib.load().grl_colsum(X.data_ptr(), _row_major_2d(X, "X"), _lib.dtype_code(X), X.shape[0], X.shape[1],
+                                      out.data_ptr(), _lib.stream_ptr(X.device)), "grl_colsum")
+    _lib.count_launch(1)
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# dense contractions
+# ----------------------------------------------------------------------------------------------
+def gemm(a: torch.Tensor, b: torch.Tensor, out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """C = a @ b for 2-D operands (row-major views allowed).
+
+    TRANSITIONAL (DESIGN.md "GEMM status"): this is the cuBLAS library call via torch.mm; the
+    tcgen05/TMEM kernel replaces it behind this same function.
+    """
+    if out_dtype is not None and out_dtype != a.dtype:
+        return torch.mm(a, b, out_dtype=out_dtype)  # bf16 operands, fp32 accumulate and output
+    return torch.mm(a, b)
+
+
+# ----------------------------------------------------------------------------------------------
+# autograd functions
+# ----------------------------------------------------------------------------------------------
+class _SpmmAggregate(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, g: PackedGraphBatch, w: torch.Tensor, *xs: torch.Tensor):
+        F_total = sum(x.shape[1] for x in xs)
+        Y = torch.empty(g.num_nodes, (g.L + 1) * F_total, dtype=xs[0].dtype, device=xs[0].device)
+        Yr = Y.view(g.num_rows, F_total)
+        off = 0
+        for x in xs:
+            spmm_fwd_(g, w, x, Yr[:, off:off + x.shape[1]])
+            off += x.shape[1]
+        ctx.g, ctx.w = g, w
+        ctx.widths = [x.shape[1] for x in xs]
+        return Y
+
+    @staticmethod
+    def backward(ctx, dY: torch.Tensor):
+        g, w = ctx.g, ctx.w
+        dY = dY.contiguous()
+        F_total = sum(ctx.widths)
+        dYr = dY.view(g.num_rows, F_total)
+        grads: List[Optional[torch.Tensor]] = []
+        off = 0
+        for k, Fk in enumerate(ctx.widths):
+            if ctx.needs_input_grad[2 + k]:
+                dX = torch.empty(g.num_nodes, Fk, dtype=dY.dtype, device=dY.device)
+                spmm_bwd_(g, w, dYr[:, off:off + Fk], dX)
+                grads.append(dX)
+            else:
+                grads.append(None)
+            off += Fk
+        return (None, None, *grads)
+
+
+def spmm_aggregate(g: PackedGraphBatch, w: torch.Tensor, xs: Sequence[torch.Tensor]) -> torch.Tensor:
+    """new_V [B*N, (L+1)*F] of the virtual concat ``xs`` (each [B*N, F_k] row-major)."""
+    return _SpmmAggregate.apply(g, w, *xs)
+
+
+class _LinearAct(torch.autograd.Function):
+    """y = dropout(relu(sum_k x_k @ W[:, slice_k]^T + b)); weight is [out, in] like nn.Linear."""
+
+    @staticmethod
+    def forward(ctx, weight, bias, relu, p, mask, seed, stream_id, weight_is_kn, *xs):
+        # weight_is_kn: weight stored [in, out] (GraphConv.h_weights) instead of nn.Linear's [out, in]
+        cdt = xs[0].dtype
+        wc = weight if weight.dtype == cdt else weight.to(cdt)
+        off = 0
+        z = None
+        for x in xs:
+            K = x.shape[1]
+            wk = wc[off:off + K, :] if weight_is_kn else wc[:, off:off + K].t()
+            zk = gemm(x, wk)
+            z = zk if z is None else z.add_(zk)
+            off += K
+        C = z.shape[1]
+        if C % 4 == 0:
+            epilogue_fwd_(z, bias, z, relu, p, mask, seed, stream_id)
+        else:  # narrow classifier head (C = 53): bias only
+            if relu or p > 0.0:
+                raise _lib.GrlError("ReLU/dropout epilogue needs an output width that is a multiple of 4")
+            if bias is not None:
+                z.add_(bias.to(z.dtype))
+        ctx.save_for_backward(weight, z if relu else None, *xs)
+        ctx.cfg = (relu, p, weight_is_kn, bias is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dY):
+        weight, y, *xs = ctx.saved_tensors
+        relu, p, weight_is_kn, has_bias = ctx.cfg
+        dY = dY.contiguous()
+        if relu or p > 0.0:
+            dZ = torch.empty_like(dY)
+            epilogue_bwd_(dY, y, dZ, relu, p)
+        else:
+            dZ = dY
+        cdt = dZ.dtype
+        wc = weight if weight.dtype == cdt else weight.to(cdt)
+        d_weight = d_bias = None
+        if ctx.needs_input_grad[0]:
+            parts = []
+            for x in xs:
+                # fp32 master gradient whatever the compute dtype
+                parts.append(gemm(x.t(), dZ, torch.float32) if weight_is_kn else gemm(dZ.t(), x, torch.float32))
+            d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
+        if has_bias and ctx.needs_input_grad[1]:
+            d_bias = colsum(dZ)
+        dxs = []
+        off = 0
+        for k, x in enumerate(xs):
+            K = x.shape[1]
+            if ctx.needs_input_grad[8 + k]:
+                wk = wc[off:off + K, :].t() if weight_is_kn else wc[:, off:off + K]
+                dxs.append(gemm(dZ, wk))
+            else:
+                dxs.append(None)
+            off += K
+        return (d_weight, d_bias, None, None, None, None, None, None, *dxs)
+
+
+def linear_act(xs: Sequence[torch.Tensor], weight: torch.Tensor, bias: Optional[torch.Tensor], relu: bool = False,
+               p: float = 0.0, mask: Optional[torch.Tensor] = None, seed: int = 0, stream_id: int = 0,
+               weight_is_kn: bool = False) -> torch.Tensor:
+    return _LinearAct.apply(weight, bias, relu, float(p), mask, seed, stream_id, weight_is_kn, *xs)
+
+
+def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Tensor, h_weights: torch.Tensor,
+               bias: Optional[torch.Tensor], relu: bool = False, p: float = 0.0, mask: Optional[torch.Tensor] = None,
+               seed: int = 0, stream_id: int = 0) -> torch.Tensor:
+    """GraphConv over a virtual concat of node-feature tensors: aggregate over the (L+1) typed adjacencies,
+    then one projection with K = (L+1)*F (reference robust_gcn.py:45-51), epilogue fused."""
+    new_v = spmm_aggregate(g, w_edge, xs)
+    return linear_act([new_v], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
+
+
+def self_attention(f_out: torch.Tensor, g_out: torch.Tensor, h_out: torch.Tensor, gamma: torch.Tensor,
+                   V: torch.Tensor) -> torch.Tensor:
+    """NodeSelfAtten core (reference robust_gcn.py:94-96): gamma * (softmax(f g^T) h) + V, per graph,
+    unscaled and unmasked.
+
+    TRANSITIONAL (DESIGN.md "attention status"): dense library bmm + softmax; the streaming-softmax
+    kernel replaces it behind this same function.
+    """
+    s = torch.softmax(torch.bmm(f_out, g_out.transpose(1, 2)).float(), dim=-1).to(h_out.dtype)
+    o = torch.bmm(s, h_out)
+    return gamma.to(o.dtype) * o + V

@@ -1,0 +1,147 @@
+/*
+ * grl_b200.h -- C ABI of the B200 (sm_100a) GraphCNNDropEdge hot path.
+ *
+ * The reference (hoangthanh283/graph-representation-learning) has no FFI: its hot path is
+ * plain PyTorch.  This header is the boundary a maintainer binds instead of the ATen call
+ * sites listed beside each entry point (paths relative to the reference root).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - the caller owns every buffer (outputs, workspaces, masks); nothing is allocated here;
+ *   - every call only enqueues work on `stream` (a cudaStream_t passed as void*); no device
+ *     synchronisation, CUDA-graph capturable unless stated;
+ *   - return value: 0 = OK, >0 = cudaError_t, <0 = argument error (GRL_E_*);
+ *     grl_last_error() returns a thread-local human-readable message;
+ *   - no C++ exceptions cross this boundary.
+ *
+ * Row numbering of the packed multi-relational adjacency ("A'" of the reference):
+ *   R = B*N*(L+1) rows;  row r = (b*N + i)*(L+1) + t,  t = 0 is the self loop (identity block),
+ *   t = l+1 is edge type l;  column = local node index j in [0,N) of the same graph b.
+ *   This is exactly reference GraphConv.preprocess_adj (gnn/models/networks/robust_gcn.py:53-72)
+ *   reshaped to (B*N*(L+1), N) and stored CSR.
+ */
+#ifndef GRL_B200_H_
+#define GRL_B200_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GRL_ABI_VERSION 1
+
+/* dtype enum for feature / adjacency buffers */
+#define GRL_F32  0
+#define GRL_BF16 1
+#define GRL_F16  2
+
+/* argument errors */
+#define GRL_E_BADARG   (-1)
+#define GRL_E_ALIGN    (-2)
+#define GRL_E_UNSUP    (-3)
+#define GRL_E_WORKSPACE (-4)
+
+/* epilogue flags (grl_bias_act_dropout_*, grl_gemm_*) */
+#define GRL_EPI_BIAS    1u
+#define GRL_EPI_RELU    2u
+#define GRL_EPI_DROPOUT 4u
+
+int grl_abi_version(void);
+const char* grl_last_error(void);
+/* 1 when the running device is compute capability 10.x, 0 otherwise, <0 on CUDA error (host call). */
+int grl_device_ok(void);
+
+/* ------------------------------------------------------------------------------------------
+ * CSR pack of the dense typed adjacency.
+ * Replaces: GraphConv.preprocess_adj  gnn/models/networks/robust_gcn.py:53-72  (identity concat,
+ *           view/transpose/reshape to B x (L+1)N x N) and the A.permute(0,1,3,2) of
+ *           gnn/models/networks/drop_robust_gcn.py:63.
+ * adj: dense [B, N, L, N] (reference batch layout [b, start i, type l, end j]), dtype f32 or f16.
+ * self_loop = 1: the identity block is added as type row t = 0 (R = B*N*(L+1) rows).
+ * self_loop = 0: adj is an already preprocessed A' viewed as [B, N, L, N] with L = (types+1), rows as given
+ *                (R = B*N*L) -- the API-compat path of GraphConv.forward(V, A', preprocess_A=False).
+ * Step 1 (count): rowptr[0] = 0, rowptr[r+1] = nnz of row r (self-loop rows count 1).
+ * Step 2 (scan):  in-place inclusive scan of rowptr[1..R]; after it rowptr[R] = nnz.
+ * Step 3 (fill):  col[e] = j ascending inside each row, val[e] = (float)adj value (1 for self loops).
+ * ------------------------------------------------------------------------------------------ */
+int grl_csr_count(const void* adj, int adj_dtype, int B, int N, int L, int self_loop,
+                  int32_t* rowptr, void* stream);
+size_t grl_scan_workspace_bytes(int64_t n);
+int grl_scan_inclusive_i32(int32_t* data, int64_t n, void* workspace, size_t workspace_bytes,
+                           void* stream);
+int grl_csr_fill(const void* adj, int adj_dtype, int B, int N, int L, int self_loop,
+                 const int32_t* rowptr, int32_t* col, float* val, void* stream);
+
+/* CSR pack from an edge list (COO).  Replaces the dense N x L x N intermediate written by
+ * Graph -> adj[start, label, end] = 1 (gnn/data_generator/data_process/utils/graph_utils.py:821-829)
+ * followed by NumpyPadding (gnn/data_generator/data_collate/numpy_padding.py:63-103).
+ * edges: int32 [E, 4] = (b, i, l, j) with i, j already shifted by the collate's pad offset;
+ * weights: float [E] or NULL (=1).  Duplicate (b,i,l,j) are kept as separate entries.
+ * count: rowptr[r+1] += 1 per edge (rowptr must be zeroed by the caller; self loops are added here);
+ * fill (after the scan): entries of a row are sorted by j ascending; cursor is an int32 [R] workspace. */
+int grl_coo_count(const int32_t* edges, int64_t E, int B, int N, int L, int32_t* rowptr, void* stream);
+int grl_coo_fill(const int32_t* edges, const float* weights, int64_t E, int B, int N, int L,
+                 const int32_t* rowptr, int32_t* cursor, int32_t* col, float* val, void* stream);
+
+/* Transpose for the gradient: CSC of the (R x B*N) matrix.
+ * colptr [B*N+1]; rowidx[k] = global CSR row r of the k-th entry of column (b*N+j), ascending;
+ * perm[k] = CSR position e of that entry (so masks / vals drawn in CSR order are reused bit-identically).
+ * workspace: int32 [B*N + 2*nnz] (+ scan workspace).  Replaces autograd's transposed bmm of
+ * torch.matmul(A, V) gnn/models/networks/robust_gcn.py:45. */
+size_t grl_csr_transpose_workspace_bytes(int64_t n_nodes, int64_t nnz);
+int grl_csr_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, int L, int64_t nnz,
+                      int32_t* colptr, int32_t* rowidx, int32_t* perm,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * DropEdge: materialise the per-entry weight of one layer,
+ *   w[e] = val[e] * keep[e] / (1 - p),   keep[e] = mask[e] (injected, uint8) if mask != NULL
+ *                                        else Philox4x32-10(seed, stream_id, e) >= p.
+ * Replaces nn.Dropout(p=0.3) on the dense A'  gnn/models/networks/drop_robust_gcn.py:38,76,80,85.
+ * p == 0 (eval) gives w = val.  The SpMM kernels can also draw the same bits on the fly.
+ * ------------------------------------------------------------------------------------------ */
+int grl_dropedge_weights(const float* val, const uint8_t* mask, int64_t nnz, float p,
+                         uint64_t seed, uint64_t stream_id, float* w, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Segmented SpMM (aggregation).  Replaces torch.matmul(A, V.view(-1,N,F)).view(-1,N,(L+1)F)
+ * gnn/models/networks/robust_gcn.py:45-47.
+ *   Y[r, 0:F] = sum_{e in row r} w[e] * X[base(r) + col[e], 0:F]      r in [0, R)
+ * Y is [B*N, (L+1)*F] viewed as [R, F] (ldy = F).  base(r) = (r / ((L+1)N)) * N.
+ * X: [B*N, F] with leading dimension ldx (elements).  dtype f32 or bf16 (fp32 accumulate).
+ * w: per-entry weights, float [nnz], required (grl_dropedge_weights output; pass val itself in eval).
+ * ------------------------------------------------------------------------------------------ */
+int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
+                 const void* X, int64_t ldx, void* Y, int64_t ldy, int dtype,
+                 int B, int N, int L, int F, void* stream);
+
+/* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.
+ *   dX[b*N+j, 0:F] = sum_{k in column (b*N+j)} w[perm[k]] * dY[rowidx[k], 0:F]
+ * dY: [R, F] (ld = lddy), dX: [B*N, F] (ld = lddx); accumulate != 0 adds into dX. */
+int grl_spmm_bwd(const int32_t* colptr, const int32_t* rowidx, const int32_t* perm, const float* w,
+                 const void* dY, int64_t lddy, void* dX, int64_t lddx, int dtype,
+                 int B, int N, int L, int F, int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused epilogue  Y = dropout(relu(X + bias))   (any subset, see GRL_EPI_*), row-major [M, C],
+ * X ld = ldx, Y ld = ldy (Y may alias X; ldy > C writes into a column slice of a concat buffer).
+ * Replaces F.relu / nn.Dropout(p=0.5) / torch.cat  gnn/models/networks/drop_robust_gcn.py:64,76-77,
+ * 80-81,84-89,99-100.  keep bit = mask[m*C + c] (uint8, injected) or Philox(seed, stream_id, m*C+c) >= p.
+ * Backward: dX = dY * (Y > 0 ? 1/(1-p) : 0) when RELU is set (Y > 0 <=> relu passed and kept);
+ * without RELU dropout is not supported in backward (the reference never does that).
+ * ------------------------------------------------------------------------------------------ */
+int grl_bias_act_dropout_fwd(const void* X, int64_t ldx, const float* bias, void* Y, int64_t ldy,
+                             int dtype, int64_t M, int C, uint32_t flags, float p,
+                             const uint8_t* mask, uint64_t seed, uint64_t stream_id, void* stream);
+int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void* Y, int64_t ldy,
+                             void* dX, int64_t lddx, int dtype, int64_t M, int C,
+                             uint32_t flags, float p, void* stream);
+/* column sums  out[c] = sum_m X[m, c]  (bias gradient), fp32 output; out must be zeroed by the caller. */
+int grl_colsum(const void* X, int64_t ldx, int dtype, int64_t M, int C, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRL_B200_H_ */

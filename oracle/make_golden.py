@@ -1,0 +1,194 @@
+"""ORACLE -- TEST INFRASTRUCTURE ONLY.  Generates ``tests/golden/*`` from the UNMODIFIED reference.
+
+Run in the authoring container only (``/root/reference`` does not exist on the GPU box):
+
+    python oracle/make_golden.py
+
+It imports the reference's own ``GraphCNNDropEdge`` / ``NumpyPadding`` (with two in-memory shims for the missing
+``colorlog`` and ``decouple`` packages, nothing else is touched), replaces ``model.dropout`` / ``model.edge_dropout``
+by mask-injecting modules, and stores inputs, masks, weights, logits, loss, gradients and the parameters after
+one ``_run_train_step`` (gnn/trainer/training_procedures/kv_procedure.py:143-164: clip 5.0, Adam defaults).
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def import_reference():
+    if not os.path.isdir(REF):
+        raise SystemExit(f"{REF} not present: golden vectors can only be regenerated in the authoring container")
+    colorlog = types.ModuleType("colorlog")
+    colorlog.basicConfig = lambda **kw: None
+    sys.modules.setdefault("colorlog", colorlog)
+    decouple = types.ModuleType("decouple")
+    decouple.config = lambda key, default=None, **kw: default
+    sys.modules.setdefault("decouple", decouple)
+    if not hasattr(np, "float"):
+        np.float = float  # removed numpy alias used by textline_encoding.py:71
+    sys.path.insert(0, REF)
+    from gnn.models import GraphCNNDropEdge  # noqa: E402
+    from gnn.data_generator.data_collate.numpy_padding import NumpyPadding  # noqa: E402
+    return GraphCNNDropEdge, NumpyPadding
+
+
+class InjectedDropout(torch.nn.Module):
+    """Stands in for nn.Dropout on the reference instance: pops pre-drawn keep masks in call order."""
+
+    def __init__(self, p, masks):
+        super().__init__()
+        self.p, self.masks, self.i = p, masks, 0
+
+    def forward(self, x):
+        if not self.training:
+            return x
+        m = self.masks[self.i]
+        self.i += 1
+        assert m.shape == x.shape, (m.shape, x.shape)
+        return x * m.to(x.dtype) / (1.0 - self.p)
+
+
+def synth_graph(gen, B, N, L, deg, weighted=False, empty_types=()):
+    """A[b, i, l, j] with ~deg neighbours per (node, type), j != i; fp16 like graph_utils.py:782-784."""
+    A = torch.zeros(B, N, L, N)
+    for b in range(B):
+        for l in range(L):
+            if l in empty_types:
+                continue
+            prob = torch.full((N, N), deg / max(N - 1, 1))
+            prob.fill_diagonal_(0.0)
+            hit = torch.bernoulli(prob, generator=gen)
+            if weighted:
+                hit = hit * (torch.randint(1, 9, (N, N), generator=gen).float() / 8.0)
+            A[b, :, l, :] = hit
+    return A.half()
+
+
+def small_model_case(GraphCNNDropEdge, name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0, weighted=False,
+                     empty_types=(), use_attention=True, pad=0):
+    gen = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    model = GraphCNNDropEdge(in_dim, out_dim, L, net_size=S, use_attention=use_attention)
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    V = torch.rand(B, N, in_dim, generator=gen)
+    A = synth_graph(gen, B, N, L, deg, weighted, empty_types)
+    y = torch.randint(0, out_dim, (B, N), generator=gen)
+    if pad:  # emulate collate padding: last graph has `pad` padded nodes on each side
+        V[-1, :pad] = 0; V[-1, -pad:] = 0
+        A[-1, :pad] = 0; A[-1, -pad:] = 0; A[-1, :, :, :pad] = 0; A[-1, :, :, -pad:] = 0
+        y[-1, :pad] = -100; y[-1, -pad:] = -100
+    H = S // 2
+    edge_masks = [torch.bernoulli(torch.full((B, (L + 1) * N, N), 0.7), generator=gen).to(torch.uint8) for _ in range(3)]
+    feat_masks = [torch.bernoulli(torch.full((B, N, S), 0.5), generator=gen).to(torch.uint8) for _ in range(4)]
+    feat_masks.append(torch.bernoulli(torch.full((B, N, 10 * H), 0.5), generator=gen).to(torch.uint8))
+
+    # eval forward
+    model.eval()
+    with torch.no_grad():
+        logits_eval = model([V, A.float()])
+
+    # train step with injected masks; dropout call order in drop_robust_gcn.py: emb(0) g1(1) g2(2) g3(3) rp(4)
+    model.train()
+    model.dropout = InjectedDropout(0.5, feat_masks)
+    model.edge_dropout = InjectedDropout(0.3, edge_masks)
+    opt = torch.optim.Adam([p for p in model.parameters() if p.requires_grad])
+    opt.zero_grad()
+    logits_train = model.forward([V, A.float()])
+    loss = torch.nn.CrossEntropyLoss()(logits_train.transpose(1, 2), y)
+    loss.backward()
+    grads = {k: p.grad.detach().clone() for k, p in model.named_parameters() if p.grad is not None}
+    total_norm = torch.nn.utils.clip_grad_norm_(model.parameters(), 5.0)
+    opt.step()
+    sd1 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+
+    out = {"V": V.numpy(), "A": A.numpy(), "y": y.numpy(), "logits_eval": logits_eval.numpy(),
+           "logits_train": logits_train.detach().numpy(), "loss": loss.detach().numpy(),
+           "grad_norm": total_norm.detach().numpy(),
+           "meta": np.array(json.dumps(dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed,
+                                            use_attention=use_attention)))}
+    for i, m in enumerate(edge_masks):
+        out[f"edge_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for i, m in enumerate(feat_masks):
+        out[f"feat_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for k, v in sd0.items():
+        out["sd0/" + k] = v.numpy()
+    for k, v in grads.items():
+        out["grad/" + k] = v.numpy()
+    for k, v in sd1.items():
+        out["sd1/" + k] = v.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(f"{name}: loss {float(loss):.6f} grad-norm {float(total_norm):.4f} nnz(A) {int((A != 0).sum())}")
+
+
+def preprocess_case(GraphCNNDropEdge):
+    """Golden fact (i) of SURVEY 8c: the exact A' of preprocess_adj, stored as CSR."""
+    gen = torch.Generator().manual_seed(7)
+    B, N, L = 2, 9, 6
+    A = synth_graph(gen, B, N, L, 2.0, weighted=True, empty_types=(4,))
+    torch.manual_seed(0)
+    model = GraphCNNDropEdge(8, 3, L, net_size=8)
+    Ap = model.gcn1.preprocess_adj(A.float().permute(0, 1, 3, 2))     # B x 7N x N
+    csr = Ap.reshape(B * N * (L + 1), N).to_sparse_csr()
+    np.savez_compressed(os.path.join(OUT, "preprocess_adj.npz"), A=A.numpy(),
+                        rowptr=csr.crow_indices().numpy().astype(np.int32),
+                        col=csr.col_indices().numpy().astype(np.int32), val=csr.values().numpy())
+    print("preprocess_adj: nnz", csr.values().numel())
+
+
+def init_case(GraphCNNDropEdge):
+    """Same seed -> same initial weights as the reference constructor (full-size model): per-tensor checksums."""
+    torch.manual_seed(1234)
+    model = GraphCNNDropEdge(4369, 53, 6, net_size=256)
+    rec = {}
+    for k, v in model.state_dict().items():
+        v64 = v.double().reshape(-1)
+        rec[k] = {"shape": list(v.shape), "sum": float(v64.sum()), "abs_sum": float(v64.abs().sum()),
+                  "first": [float(x) for x in v64[:4]], "last": [float(x) for x in v64[-4:]]}
+    with open(os.path.join(OUT, "init_seed1234.json"), "w") as f:
+        json.dump(rec, f, indent=1)
+    print("init: ", len(rec), "tensors")
+
+
+def collate_case(NumpyPadding):
+    """NumpyPadding symmetric padding (numpy_padding.py:63-103) on ragged samples."""
+    rng = np.random.default_rng(5)
+    sizes = [5, 9, 6, 9, 2]
+    samples = []
+    for n in sizes:
+        samples.append({"textline_encoding": rng.random((n, 11), dtype=np.float32),
+                        "adjacency_matrix": (rng.random((n, 6, n)) < 0.3).astype(np.float16),
+                        "node_label": rng.integers(0, 7, size=(n,)).astype(np.int64),
+                        "other": "dropped"})
+    raw = {f"in{i}/{k}": v for i, s in enumerate(samples) for k, v in s.items() if k != "other"}
+    pad = NumpyPadding({"textline_encoding": 0.0, "adjacency_matrix": 0.0, "node_label": -100.0}, True)
+    out = pad([dict(s) for s in samples])
+    from torch.utils.data._utils.collate import default_collate
+    batch = default_collate(out)
+    res = {f"out/{k}": v.numpy() for k, v in batch.items()}
+    np.savez_compressed(os.path.join(OUT, "collate.npz"), sizes=np.array(sizes), **raw, **res)
+    print("collate:", {k: tuple(v.shape) for k, v in batch.items()}, {k: v.dtype for k, v in batch.items()})
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    GraphCNNDropEdge, NumpyPadding = import_reference()
+    small_model_case(GraphCNNDropEdge, "model_small", seed=11, B=3, N=10, in_dim=24, S=32, out_dim=7)
+    small_model_case(GraphCNNDropEdge, "model_weighted_pad", seed=12, B=2, N=12, in_dim=20, S=32, out_dim=5,
+                     weighted=True, empty_types=(4, 5), pad=2)
+    small_model_case(GraphCNNDropEdge, "model_noatt", seed=13, B=2, N=8, in_dim=16, S=32, out_dim=4,
+                     use_attention=False)
+    preprocess_case(GraphCNNDropEdge)
+    init_case(GraphCNNDropEdge)
+    collate_case(NumpyPadding)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,33 @@
+"""Loader for the committed reference vectors (tests/golden, written by oracle/make_golden.py)."""
+import json
+import os
+
+import numpy as np
+import torch
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+MODEL_CASES = ["model_small", "model_weighted_pad", "model_noatt"]
+
+
+def load_model_case(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    B, N, S, L = meta["B"], meta["N"], meta["S"], meta["L"]
+    H = S // 2
+    case = {"meta": meta}
+    for k in ("V", "A", "y", "logits_eval", "logits_train", "loss", "grad_norm"):
+        case[k] = torch.from_numpy(z[k])
+    case["edge_masks"] = [torch.from_numpy(np.unpackbits(z[f"edge_mask{i}"])[: B * (L + 1) * N * N]
+                                           .reshape(B, (L + 1) * N, N).copy()) for i in range(3)]
+    widths = [S, S, S, S, 10 * H]
+    case["feat_masks"] = [torch.from_numpy(np.unpackbits(z[f"feat_mask{i}"])[: B * N * w].reshape(B, N, w).copy())
+                          for i, w in enumerate(widths)]
+    for group in ("sd0", "grad", "sd1"):
+        case[group] = {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith(group + "/")}
+    return case
+
+
+def rel_err(x, ref):
+    """norm-wise relative error against a reference tensor (SURVEY.md 8c tolerance definition)."""
+    x, ref = x.double().reshape(-1), ref.double().reshape(-1)
+    return float((x - ref).norm() / ref.norm().clamp_min(1e-30))

@@ -1,0 +1,259 @@
+#!/usr/bin/env python
+"""bench.py -- train graphs/s of the GraphCNNDropEdge hot path on N B200s (BASELINE.json metric).
+
+  python bench.py --gpus 1 --steps K --warmup W              our arm (CUDA kernels behind the C ABI)
+  python bench.py --impl reference --gpus 1 --steps K ...    the reference's CPU implementation (oracle port)
+  torchrun --nproc-per-node N bench.py --gpus N ...          data parallel, one process per GPU (weak scaling)
+
+A "step" is one KVProcedure train step (kv_procedure.py:143-164: forward([V, A]) -> CE -> backward -> clip -> Adam)
+over one synthetic batch of the named workload.  One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "train graphs/sec (fwd+bwd)"
+UNIT = "graphs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg1", "cfg2", "cfg3"])
+    ap.add_argument("--batch", type=int, default=None, help="override graphs per GPU (debug)")
+    ap.add_argument("--cpu-batch", type=int, default=8, help="graphs per step of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ helpers
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "bf16_tflops": p["bf16_tflops"],
+                "bf16_tflops_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._halt = index, [], threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [x.strip() for x in out.strip().split(",")]
+                if len(parts) >= 7:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def finish(self):
+        self._halt.set()
+        self.join(timeout=3)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_reference_arm(wl, B, steps, warmup):
+    """The reference's CPU path (oracle port of drop_robust_gcn.py:61-103 + kv_procedure.py:143-164) on the host
+    cores, dense adjacency, nn.Dropout semantics.  Returns (graphs/s, ms/step, cores)."""
+    import torch
+    from graph_representation_learning_b200 import GraphCNNDropEdge, synthetic
+    from oracle import reference_port as rp
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    V, A, y = synthetic.make_batch(wl, 1234, "cpu", B=B)
+    A = A.float()                                            # kv_procedure.py:118
+    state = {}
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        rp.train_step(sd, V, A, y, state, step=it + 1)
+        times.append(time.perf_counter() - t0)
+    t = sum(times[warmup:]) / steps
+    return B / t, t * 1e3, cores
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from graph_representation_learning_b200 import synthetic
+    wl = synthetic.CONFIGS[args.workload]
+    B = args.cpu_batch
+    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    val, ms, cores = cpu_reference_arm(wl, B, steps, warmup)
+    sample = f"{B} graphs x {wl.N} nodes per step ({warmup}+{steps} steps) of {wl.name}, dense fp32 adjacency"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam", "graphs_per_step": B},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from graph_representation_learning_b200 import GraphCNNDropEdge, PackedGraphBatch, _lib, ops, synthetic
+    from graph_representation_learning_b200.trainer import KVTrainStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if _lib.load().grl_device_ok() != 1:
+        raise SystemExit("bench.py needs a compute-capability 10.x GPU (B200); there is no fallback path")
+
+    wl = synthetic.CONFIGS[args.workload]
+    B = args.batch or wl.B
+    torch.manual_seed(0)                                     # identical replicas
+    model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention).to(dev)
+    model.set_compute_dtype(wl.dtype)
+    model.rng_seed = 1000 + rank                             # independent DropEdge/dropout streams per rank
+    step = KVTrainStep(model)
+    feat_dtype = torch.float32 if wl.dtype == torch.float32 else torch.bfloat16
+    V, A, y = synthetic.make_batch(wl, 1234 + rank, dev, B=B, feature_dtype=feat_dtype)
+    batch_dev = {"textline_encoding": V, "adjacency_matrix": A, "node_label": y}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = _lib.launches()
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        if sampler:
+            sampler.start()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = sampler.finish() if sampler else None
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t) / steps, _lib.launches() - n0, clocks
+
+    # (1) device-resident inputs: the whole forward([V, A]) API call incl. the CSR/CSC pack of the dense fp16 A
+    ms_step, launches, clocks = timed(lambda: step.run_train_step(batch_dev), args.steps, args.warmup)
+    value = world * B / (ms_step * 1e-3)
+
+    # (2) end to end: pinned HOST buffers -> H2D inside the timed region, loss read back to the host
+    e2e = None
+    if not args.no_e2e:
+        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in batch_dev.items()}
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+
+        def e2e_step():
+            loss = step.run_train_step(host)
+            return float(loss)                               # D2H read of the step's result (4 bytes)
+        e_steps = max(3, min(args.steps, 10))
+        ms_e2e, _, _ = timed(e2e_step, e_steps, 2)
+        e2e = {"value": world * B / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+               "ms_per_step": ms_e2e, "steps": e_steps}
+
+    # (3) roofline of the aggregation kernel (gcn1 SpMM, DropEdge weights applied), timed alone with CUDA events
+    pk = peaks()
+    g = PackedGraphBatch.from_dense(A)
+    S = wl.net_size
+    X = torch.randn(B * wl.N, S, device=dev, dtype=wl.dtype)
+    Y = torch.empty(g.num_rows, S, device=dev, dtype=wl.dtype)
+    w = g.edge_weights(0.3, seed=1, stream_id=1)
+    ms_spmm, _, _ = timed(lambda: ops.spmm_fwd_(g, w, X, Y), 20, 5)
+    es = X.element_size()
+    alg_bytes = 4 * (g.num_rows + 1) + 8 * g.nnz + X.numel() * es + Y.numel() * es   # SURVEY 8d bytes_compulsory (+w)
+    achieved = alg_bytes / (ms_spmm * 1e-3) / 1e9
+    roofline = {"kernel": "spmm_rows_kernel (gcn1 aggregation, fwd)", "bound": "hbm", "achieved": achieved,
+                "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None,
+                "peak_source": pk["source"], "ms_per_launch": ms_spmm, "algorithmic_bytes": alg_bytes}
+    dYt = torch.randn(g.num_rows, S, device=dev, dtype=wl.dtype)
+    dX = torch.empty(B * wl.N, S, device=dev, dtype=wl.dtype)
+    ms_bwd, _, _ = timed(lambda: ops.spmm_bwd_(g, w, dYt, dX), 20, 5)
+    alg_bwd = 4 * (g.num_nodes + 1) + 12 * g.nnz + dYt.numel() * es + dX.numel() * es
+    roofline["bwd"] = {"kernel": "spmm_rows_kernel<transposed>", "achieved": alg_bwd / (ms_bwd * 1e-3) / 1e9,
+                       "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"], "ms_per_launch": ms_bwd}
+    del X, Y, dYt, dX
+
+    # (4) CPU baseline: the oracle port on a bounded sample of the same workload (rank 0, N=1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb = args.cpu_batch
+        v, ms_cpu, cores = cpu_reference_arm(wl, cb, 3, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms_cpu,
+               "sample": f"{cb} graphs x {wl.N} nodes per step (1+3 steps) of the same workload, dense fp32 adjacency"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if wl.dtype == torch.float32 else "bf16", "data": "synthetic",
+            "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam (forward includes the CSR/CSC pack of dense A)",
+                       "graphs_per_gpu": B, "global_batch": world * B, "parallelism": f"dp{world}",
+                       "l2": "inputs (V %.2f GB) larger than L2" % (V.numel() * V.element_size() / 1e9),
+                       "features": "dense U[0,1)"},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -105,6 +105,43 @@ bias_act_dropout_bwd_kernel(const T* dY, int64_t lddy, const T* Y, int64_t ldy,
     }
 }
 
+// Any-width variants (C % 4 != 0, e.g. the 2-wide attention projections of tiny models or the 53-wide head):
+// one thread per element; Philox::word(idx) picks the same bit the 4-wide kernel would.
+template <typename T>
+__global__ void __launch_bounds__(256)
+bias_act_dropout_fwd_scalar_kernel(const T* X, int64_t ldx, const float* __restrict__ bias, T* Y, int64_t ldy, int64_t M,
+                                   int C, uint32_t flags, float scale, uint32_t thresh,
+                                   const uint8_t* __restrict__ mask, uint64_t seed, uint64_t stream_id) {
+    const int64_t total = M * C;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int64_t m = t / C;
+        const int c = static_cast<int>(t - m * C);
+        float v = to_float(X[m * ldx + c]);
+        if (flags & GRL_EPI_BIAS) v += bias[c];
+        if (flags & GRL_EPI_RELU) v = fmaxf(v, 0.0f);
+        if (flags & GRL_EPI_DROPOUT) {
+            const bool keep = mask ? (mask[t] != 0) : (Philox::word(seed, stream_id, static_cast<uint64_t>(t)) >= thresh);
+            v = keep ? v * scale : 0.0f;
+        }
+        Y[m * ldy + c] = from_float<T>(v);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+bias_act_dropout_bwd_scalar_kernel(const T* dY, int64_t lddy, const T* Y, int64_t ldy, T* dX, int64_t lddx, int64_t M,
+                                   int C, bool relu, float scale) {
+    const int64_t total = M * C;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int64_t m = t / C;
+        const int c = static_cast<int>(t - m * C);
+        const float y = relu ? to_float(Y[m * ldy + c]) : 1.0f;
+        dX[m * lddx + c] = from_float<T>(y > 0.0f ? to_float(dY[m * lddy + c]) * scale : 0.0f);
+    }
+}
+
 // out[c] += sum over a slab of rows; one block = 32 x 8 threads covering 32 columns, rows strided by gridDim.y.
 template <typename T>
 __global__ void colsum_kernel(const T* __restrict__ X, int64_t ldx, int64_t M, int C, float* __restrict__ out) {
@@ -142,15 +179,31 @@ extern "C" int grl_bias_act_dropout_fwd(const void* X, int64_t ldx, const float*
                                         uint64_t stream_id, void* stream) {
     GRL_CHECK_ARG(X && Y, GRL_E_BADARG, "grl_bias_act_dropout_fwd: null pointer");
     GRL_CHECK_ARG(!(flags & GRL_EPI_BIAS) || bias, GRL_E_BADARG, "grl_bias_act_dropout_fwd: BIAS flag without bias");
-    GRL_CHECK_ARG(M >= 0 && C > 0 && C % 4 == 0, GRL_E_UNSUP, "grl_bias_act_dropout_fwd: C=%d must be a positive multiple of 4", C);
+    GRL_CHECK_ARG(M >= 0 && C > 0, GRL_E_BADARG, "grl_bias_act_dropout_fwd: bad shape M=%lld C=%d", (long long)M, C);
     GRL_CHECK_ARG(ldx >= C && ldy >= C, GRL_E_BADARG, "grl_bias_act_dropout_fwd: leading dimension < C");
     GRL_CHECK_ARG(p >= 0.0f && p < 1.0f, GRL_E_BADARG, "grl_bias_act_dropout_fwd: p outside [0,1)");
-    GRL_CHECK_ARG(!(flags & GRL_EPI_BIAS) || aligned_to(bias, 16), GRL_E_ALIGN, "grl_bias_act_dropout_fwd: bias must be 16-byte aligned");
     if (M == 0) return 0;
     if (p == 0.0f) flags &= ~GRL_EPI_DROPOUT;
     const float scale = 1.0f / (1.0f - p);
     const uint32_t thresh = keep_threshold(p);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (C % 4 != 0 || ((flags & GRL_EPI_BIAS) && !aligned_to(bias, 16))) {
+        const int sgrid = ew_grid(M * C);
+        if (dtype == GRL_F32)
+            bias_act_dropout_fwd_scalar_kernel<float><<<sgrid, 256, 0, st>>>(
+                static_cast<const float*>(X), ldx, bias, static_cast<float*>(Y), ldy, M, C, flags, scale, thresh, mask, seed,
+                stream_id);
+        else if (dtype == GRL_BF16)
+            bias_act_dropout_fwd_scalar_kernel<__nv_bfloat16><<<sgrid, 256, 0, st>>>(
+                static_cast<const __nv_bfloat16*>(X), ldx, bias, static_cast<__nv_bfloat16*>(Y), ldy, M, C, flags, scale,
+                thresh, mask, seed, stream_id);
+        else {
+            set_error("grl_bias_act_dropout_fwd: dtype %d unsupported", dtype);
+            return GRL_E_UNSUP;
+        }
+        GRL_LAUNCH_CHECK("bias_act_dropout_fwd_scalar_kernel");
+        return 0;
+    }
     const int grid = ew_grid(M * (C / 4));
     const size_t a4 = 4 * (dtype == GRL_F32 ? 4 : 2);
     const bool vec = aligned_to(X, a4) && aligned_to(Y, a4) && ldx % 4 == 0 && ldy % 4 == 0;
@@ -173,7 +226,7 @@ extern "C" int grl_bias_act_dropout_fwd(const void* X, int64_t ldx, const float*
 extern "C" int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void* Y, int64_t ldy, void* dX, int64_t lddx,
                                         int dtype, int64_t M, int C, uint32_t flags, float p, void* stream) {
     GRL_CHECK_ARG(dY && dX, GRL_E_BADARG, "grl_bias_act_dropout_bwd: null pointer");
-    GRL_CHECK_ARG(M >= 0 && C > 0 && C % 4 == 0, GRL_E_UNSUP, "grl_bias_act_dropout_bwd: C=%d must be a positive multiple of 4", C);
+    GRL_CHECK_ARG(M >= 0 && C > 0, GRL_E_BADARG, "grl_bias_act_dropout_bwd: bad shape M=%lld C=%d", (long long)M, C);
     const bool relu = (flags & GRL_EPI_RELU) != 0;
     GRL_CHECK_ARG(relu || !(flags & GRL_EPI_DROPOUT) || p == 0.0f, GRL_E_UNSUP,
                   "grl_bias_act_dropout_bwd: dropout without ReLU is not supported");
@@ -181,6 +234,23 @@ extern "C" int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void
     if (M == 0) return 0;
     const float scale = (flags & GRL_EPI_DROPOUT) ? 1.0f / (1.0f - p) : 1.0f;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (C % 4 != 0) {
+        const int sgrid = ew_grid(M * C);
+        if (dtype == GRL_F32)
+            bias_act_dropout_bwd_scalar_kernel<float><<<sgrid, 256, 0, st>>>(
+                static_cast<const float*>(dY), lddy, static_cast<const float*>(Y), ldy, static_cast<float*>(dX), lddx, M, C,
+                relu, scale);
+        else if (dtype == GRL_BF16)
+            bias_act_dropout_bwd_scalar_kernel<__nv_bfloat16><<<sgrid, 256, 0, st>>>(
+                static_cast<const __nv_bfloat16*>(dY), lddy, static_cast<const __nv_bfloat16*>(Y), ldy,
+                static_cast<__nv_bfloat16*>(dX), lddx, M, C, relu, scale);
+        else {
+            set_error("grl_bias_act_dropout_bwd: dtype %d unsupported", dtype);
+            return GRL_E_UNSUP;
+        }
+        GRL_LAUNCH_CHECK("bias_act_dropout_bwd_scalar_kernel");
+        return 0;
+    }
     const int grid = ew_grid(M * (C / 4));
     const size_t a4 = 4 * (dtype == GRL_F32 ? 4 : 2);
     const bool vec = aligned_to(dY, a4) && aligned_to(dX, a4) && (!relu || aligned_to(Y, a4)) && lddy % 4 == 0 &&

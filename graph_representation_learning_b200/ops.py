@@ -162,14 +162,8 @@ class _LinearAct(torch.autograd.Function):
             zk = gemm(x, wk)
             z = zk if z is None else z.add_(zk)
             off += K
-        C = z.shape[1]
-        if C % 4 == 0:
+        if bias is not None or relu or p > 0.0:
             epilogue_fwd_(z, bias, z, relu, p, mask, seed, stream_id)
-        else:  # narrow classifier head (C = 53): bias only
-            if relu or p > 0.0:
-                raise _lib.GrlError("ReLU/dropout epilogue needs an output width that is a multiple of 4")
-            if bias is not None:
-                z.add_(bias.to(z.dtype))
         ctx.save_for_backward(weight, z if relu else None, *xs)
         ctx.cfg = (relu, p, weight_is_kn, bias is not None)
         return z

@@ -1,0 +1,67 @@
+"""Seeded synthetic document-graph batches of the shapes BASELINE.json names.
+
+Graph: for every graph, node i and edge type l, each j != i is a neighbour with probability d/(N-1)
+(so the out-degree is Binomial(N-1, d/(N-1)) with distinct uniform targets) -> ``A[b, i, l, j] = 1`` in fp16,
+the dtype the reference's graph builder emits (gnn/data_generator/data_process/utils/graph_utils.py:782-784).
+Features: ``dense`` = U[0,1) on all columns (headline variant); ``bow`` = 7 ones in the first input_dim-4
+binary columns + 4 spatial floats in U[0.09,1) (what TextlineEncoding produces,
+gnn/data_generator/data_process/textline_encoding.py:33-55).  Labels uniform over the classes.
+Everything is generated with a torch.Generator on the requested device, so CPU (oracle) and GPU runs that
+need identical data generate on CPU and copy.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+
+@dataclass
+class Workload:
+    name: str
+    B: int
+    N: int
+    input_dim: int = 4369
+    output_dim: int = 53
+    num_edges: int = 6
+    net_size: int = 256
+    degree: float = 8.0
+    dtype: torch.dtype = torch.float32
+    use_attention: bool = True
+
+
+CONFIGS = {
+    "cfg1": Workload("cfg1: 8 graphs x 200 nodes, S=256, fp32", 8, 200),
+    "cfg2": Workload("cfg2: 256 graphs x 500 nodes, ~8 nbrs/type, S=256, fp32", 256, 500),
+    "cfg3": Workload("cfg3: 128 graphs/GPU x 1000 nodes, S=512, bf16", 128, 1000, net_size=512, dtype=torch.bfloat16),
+}
+
+
+def make_batch(wl: Workload, seed: int, device, features: str = "dense", B: Optional[int] = None,
+               feature_dtype: torch.dtype = torch.float32):
+    """returns (V [B,N,input_dim], A [B,N,L,N] fp16, y [B,N] int64) on ``device``"""
+    B = wl.B if B is None else B
+    N, L = wl.N, wl.num_edges
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev).manual_seed(seed)
+    A = torch.empty(B, N, L, N, dtype=torch.float16, device=dev)
+    prob = wl.degree / max(N - 1, 1)
+    eye = torch.eye(N, dtype=torch.bool, device=dev).view(N, 1, N)
+    for b in range(B):  # per graph to bound the fp32 temporary
+        hit = torch.rand(N, L, N, generator=gen, device=dev) < prob
+        hit &= ~eye
+        A[b] = hit.to(torch.float16)
+    if features == "dense":
+        V = torch.rand(B, N, wl.input_dim, generator=gen, device=dev, dtype=torch.float32)
+    elif features == "bow":
+        V = torch.zeros(B, N, wl.input_dim, device=dev, dtype=torch.float32)
+        idx = torch.randint(0, wl.input_dim - 4, (B, N, 7), generator=gen, device=dev)
+        V.scatter_(2, idx, 1.0)
+        V[:, :, -4:] = 0.09 + 0.91 * torch.rand(B, N, 4, generator=gen, device=dev)
+    else:
+        raise ValueError(features)
+    if feature_dtype != torch.float32:
+        V = V.to(feature_dtype)
+    y = torch.randint(0, wl.output_dim, (B, N), generator=gen, device=dev)
+    return V, A, y

@@ -49,7 +49,15 @@ SIGNATURES = {
     "grl_bias_act_dropout_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64,
                                          c_int, c_uint32, c_float, c_void_p]),
     "grl_colsum": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p]),
+    "grl_gemm_nt": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int,
+                            c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int,
+                            c_void_p, c_int64, c_int, c_int, c_int, c_int,
+                            c_void_p, c_uint32, c_float, c_void_p, c_uint64, c_uint64, c_void_p]),
+    "grl_gemm_x3_set_promo": (c_int, [c_int]),
+    "grl_split_tf32": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
 }
+
+GEMM_BF16, GEMM_TF32, GEMM_TF32X3 = 0, 1, 2
 
 _lib = None
 

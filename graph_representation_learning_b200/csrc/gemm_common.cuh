@@ -1,0 +1,132 @@
+// Pieces shared by the tcgen05 GEMM kernels: parameters, the fused epilogue, TMA tensor-map construction.
+#pragma once
+#include "common.cuh"
+#include "tcgen05.cuh"
+
+#include <mutex>
+
+namespace grl {
+
+enum GemmMode { kBF16 = 0, kTF32 = 1, kTF32X3 = 2 };
+
+struct GemmParams {
+    int M, N;
+    int kblocks0, kblocks1;     // K blocks of segment 0 / 1 (segment 1 may be 0)
+    void* C;
+    int64_t ldc;
+    int out_bf16;               // 0: fp32 output, 1: bf16 output
+    int atomic_add;             // 1: red.global.add.f32 into C (split-K partial tiles; fp32 output only)
+    const float* bias;
+    uint32_t flags;
+    float scale;                // 1/(1-p)
+    uint32_t thresh;            // keep iff philox word >= thresh
+    const uint8_t* mask;        // injected keep bits [M*N] or null
+    uint64_t seed, stream_id;
+};
+
+// Fused epilogue for 4 consecutive columns [col, col+4) of one output row held in registers.
+// Same Philox indexing (row*N + col) as grl_bias_act_dropout_fwd, so fused and unfused paths agree bit for bit.
+__device__ __forceinline__ void epilogue_store4(const GemmParams& p, int row, int col, float (&v)[4], bool vec_ok) {
+    if (p.flags & GRL_EPI_BIAS) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (col + t < p.N) v[t] += __ldg(p.bias + col + t);
+    }
+    if (p.flags & GRL_EPI_RELU) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) v[t] = fmaxf(v[t], 0.0f);
+    }
+    if (p.flags & GRL_EPI_DROPOUT) {
+        const int64_t e0 = static_cast<int64_t>(row) * p.N + col;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            if (col + t < p.N) {
+                const bool keep = p.mask ? (p.mask[e0 + t] != 0)
+                                         : (Philox::word(p.seed, p.stream_id, static_cast<uint64_t>(e0 + t)) >= p.thresh);
+                v[t] = keep ? v[t] * p.scale : 0.0f;
+            }
+        }
+    }
+    if (p.out_bf16) {
+        __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.C) + static_cast<int64_t>(row) * p.ldc + col;
+        if (vec_ok && col + 3 < p.N) {
+            __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+            *reinterpret_cast<uint2*>(out) = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+        } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (col + t < p.N) out[t] = __float2bfloat16_rn(v[t]);
+        }
+    } else {
+        float* out = static_cast<float*>(p.C) + static_cast<int64_t>(row) * p.ldc + col;
+        if (p.atomic_add) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (col + t < p.N) atomicAdd(out + t, v[t]);
+        } else if (vec_ok && col + 3 < p.N) {
+            *reinterpret_cast<float4*>(out) = make_float4(v[0], v[1], v[2], v[3]);
+        } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (col + t < p.N) out[t] = v[t];
+        }
+    }
+}
+
+__device__ __forceinline__ bool epilogue_vec_ok(const GemmParams& p) {
+    const int eb = p.out_bf16 ? 2 : 4;
+    return (p.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.C) % (4 * eb)) == 0);
+}
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    });
+    return fn;
+}
+
+// Row-major matrix [rows, cols] with leading dimension ld (elements); box = one 128-byte swizzle atom along the
+// contiguous dimension x box_rows rows.  K-major operands: cols = K.  MN-major operands: cols = the M/N extent.
+inline int make_tmap_sw128(CUtensorMap* out, const void* ptr, int elem_bytes, int64_t rows, int64_t cols, int64_t ld,
+                           int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return GRL_E_UNSUP;
+    }
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * elem_bytes};
+    const cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / elem_bytes), static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    CUresult r = enc(out, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d): ptr=%p rows=%lld cols=%lld ld=%lld elem=%d box_rows=%d",
+                  static_cast<int>(r), ptr, static_cast<long long>(rows), static_cast<long long>(cols),
+                  static_cast<long long>(ld), elem_bytes, box_rows);
+        return GRL_E_BADARG;
+    }
+    return 0;
+}
+
+struct GemmArgs {
+    const void *A0, *B0, *B0lo, *A1, *B1, *B1lo;
+    int64_t lda0, ldb0, lda1, ldb1;
+    int K0, K1;
+};
+
+int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_x3_tcgen05.cu
+
+}  // namespace grl

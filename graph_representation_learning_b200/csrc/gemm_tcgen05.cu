@@ -1,0 +1,242 @@
+// tcgen05 / TMEM / TMA GEMM with fused bias + ReLU + dropout epilogue for the dense projections of the
+// GraphCNNDropEdge stack (reference: nn.Linear / torch.matmul(new_V, h_weights) --
+// gnn/models/networks/robust_gcn.py:10-11,50; drop_robust_gcn.py:59,64,89,99-103 -- and their autograd).
+//
+//   C[M, N] = epilogue( sum_seg  A_seg[M, K_seg] * B_seg[N, K_seg]^T )        ("NT": both operands K-major)
+//
+// * up to two K segments = the reference's torch.cat([g1, g2]) / cat([g1, g3]) consumed without a concat buffer;
+// * this file: single-pass kernels, BF16 (kind::f16) and TF32 (kind::tf32, fp32 operands, ~1e-3);
+//   the fp32-grade error-compensated TF32X3 kernel lives in gemm_x3_tcgen05.cu;
+// * one CTA = one 128 x BLOCK_N output tile; warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner,
+//   warps 2..5 = epilogue: tcgen05.ld -> bias/ReLU/dropout -> global.  fp32 accumulators live in TMEM.
+#include "gemm_common.cuh"
+
+namespace grl {
+using namespace sm100;
+
+template <int kMode, int BLOCK_N>
+struct GemmCfg {
+    static constexpr int BLOCK_M = 128;
+    static constexpr int ELEM = (kMode == kBF16) ? 2 : 4;
+    static constexpr int BLOCK_K = 128 / ELEM;          // one 128-byte swizzle atom along K
+    static constexpr int UMMA_K = 32 / ELEM;            // 16 (bf16) / 8 (tf32)
+    static constexpr int A_BYTES = BLOCK_M * 128;
+    static constexpr int B_BYTES = BLOCK_N * 128;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int kMaxSmem = 227 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/;
+    static constexpr int STAGES_RAW = kMaxSmem / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
+    static_assert(STAGES >= 2, "pipeline needs at least two stages");
+    static_assert(BLOCK_N % 16 == 0 && BLOCK_N >= 16 && BLOCK_N <= 256, "UMMA N for M=128");
+};
+
+constexpr int kGemmThreads = 192;
+
+template <int kMode, int BLOCK_N>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_nt_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmB0,
+               const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1) {
+    static_assert(kMode == kBF16 || kMode == kTF32, "TF32X3 has its own kernel (gemm_nt_x3_kernel)");
+    using Cfg = GemmCfg<kMode, BLOCK_N>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* full_bar = bars;                 // [STAGES] TMA bytes landed
+    uint64_t* empty_bar = bars + STAGES;       // [STAGES] MMAs reading the stage retired
+    uint64_t* accum_bar = bars + 2 * STAGES;   // accumulator complete
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+    const int m0 = (blockIdx.x / tiles_n) * Cfg::BLOCK_M;
+    const int n0 = (blockIdx.x % tiles_n) * BLOCK_N;
+    const int total_kb = p.kblocks0 + p.kblocks1;
+
+    auto stage_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
+    auto stage_b = [&](int s) { return tiles + s * Cfg::STAGE_BYTES + Cfg::A_BYTES; };
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA0);
+        tma_prefetch_desc(&tmB0);
+        if (p.kblocks1) {
+            tma_prefetch_desc(&tmA1);
+            tma_prefetch_desc(&tmB1);
+        }
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(accum_bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================================================================== TMA producer (one lane)
+        if (lane == 0) {
+            for (int kb = 0; kb < total_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+                const bool seg1 = kb >= p.kblocks0;
+                const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
+                tma_load_2d(stage_a(s), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
+                tma_load_2d(stage_b(s), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================================== MMA issuer (one lane)
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(kMode == kBF16 ? 1 : 2, Cfg::BLOCK_M, BLOCK_N, 0, 0);
+            for (int kb = 0; kb < total_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after_sync();
+                const uint64_t a_desc = umma_desc_kmajor_sw128(smem_u32(stage_a(s)));
+                const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(stage_b(s)));
+#pragma unroll
+                for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                    const uint64_t koff = static_cast<uint64_t>(k * 2);   // 32 bytes per UMMA_K step, >> 4
+                    umma<kMode != kBF16>(tmem_base, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                }
+                umma_commit(&empty_bar[s]);       // frees the stage once these MMAs have read it
+            }
+            umma_commit(accum_bar);               // accumulator final
+        }
+    } else {
+        // ===================================================================== epilogue (warps 2..5)
+        mbar_wait(accum_bar, 0);
+        tc_fence_after_sync();
+        const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
+        const int row = m0 + quarter * 32 + lane;
+        const bool row_ok = row < p.M;
+        const bool vec_ok = epilogue_vec_ok(p);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+            if (n0 + c0 >= p.N) break;                      // warp-uniform
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + c0, r);
+            tmem_ld_wait();
+            if (!row_ok) continue;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const int col = n0 + c0 + j;
+                if (col >= p.N) break;
+                float v[4] = {__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                              __uint_as_float(r[j + 3])};
+                epilogue_store4(p, row, col, v, vec_ok);
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+template <int kMode, int BLOCK_N>
+static int launch_gemm(const GemmArgs& a, GemmParams p, cudaStream_t st) {
+    using Cfg = GemmCfg<kMode, BLOCK_N>;
+    const int eb = Cfg::ELEM;
+    CUtensorMap tA0, tB0, tA1, tB1;
+    int rc;
+    if ((rc = make_tmap_sw128(&tA0, a.A0, eb, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;
+    if ((rc = make_tmap_sw128(&tB0, a.B0, eb, p.N, a.K0, a.ldb0, BLOCK_N))) return rc;
+    tA1 = tA0;
+    tB1 = tB0;
+    if (a.K1 > 0) {
+        if ((rc = make_tmap_sw128(&tA1, a.A1, eb, p.M, a.K1, a.lda1, Cfg::BLOCK_M))) return rc;
+        if ((rc = make_tmap_sw128(&tB1, a.B1, eb, p.N, a.K1, a.ldb1, BLOCK_N))) return rc;
+    }
+    p.kblocks0 = (a.K0 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K;
+    p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
+    auto kern = gemm_nt_kernel<kMode, BLOCK_N>;
+    static bool attr_set = false;   // per template instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+        attr_set = true;
+    }
+    const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+    kern<<<tiles_m * tiles_n, kGemmThreads, Cfg::SMEM_BYTES, st>>>(p, tA0, tB0, tA1, tB1);
+    GRL_LAUNCH_CHECK("gemm_nt_kernel");
+    return 0;
+}
+
+__global__ void split_tf32_kernel(const float* __restrict__ src, int64_t ld_src, float* __restrict__ hi,
+                                  float* __restrict__ lo, int64_t ld_dst, int64_t rows, int cols) {
+    const int64_t total = rows * cols;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int64_t r = t / cols;
+        const int c = static_cast<int>(t - r * cols);
+        const float v = src[r * ld_src + c];
+        const float h = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+        hi[r * ld_dst + c] = h;
+        lo[r * ld_dst + c] = v - h;
+    }
+}
+
+}  // namespace grl
+
+using namespace grl;
+
+extern "C" int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst, int64_t rows,
+                              int cols, void* stream) {
+    GRL_CHECK_ARG(src && hi && lo, GRL_E_BADARG, "grl_split_tf32: null pointer");
+    GRL_CHECK_ARG(rows >= 0 && cols > 0 && ld_src >= cols && ld_dst >= cols, GRL_E_BADARG, "grl_split_tf32: bad shape");
+    if (rows == 0) return 0;
+    int64_t blocks = (rows * cols + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    split_tf32_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, ld_src, hi, lo, ld_dst,
+                                                                                             rows, cols);
+    GRL_LAUNCH_CHECK("split_tf32_kernel");
+    return 0;
+}
+
+extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo, int64_t ldb0, int K0,
+                           const void* A1, int64_t lda1, const void* B1, const void* B1_lo, int64_t ldb1, int K1,
+                           void* C, int64_t ldc, int out_dtype, int M, int N, int mode, const float* bias,
+                           uint32_t flags, float p, const uint8_t* mask, uint64_t seed, uint64_t stream_id,
+                           void* stream) {
+    GRL_CHECK_ARG(A0 && B0 && C, GRL_E_BADARG, "grl_gemm_nt: null pointer");
+    GRL_CHECK_ARG(M > 0 && N > 0 && K0 > 0 && K1 >= 0, GRL_E_BADARG, "grl_gemm_nt: bad shape M=%d N=%d K0=%d K1=%d", M, N, K0, K1);
+    GRL_CHECK_ARG(mode >= kBF16 && mode <= kTF32X3, GRL_E_BADARG, "grl_gemm_nt: bad mode %d", mode);
+    GRL_CHECK_ARG(K1 == 0 || (A1 && B1), GRL_E_BADARG, "grl_gemm_nt: second K segment without operands");
+    GRL_CHECK_ARG(mode != kTF32X3 || (B0_lo && (K1 == 0 || B1_lo)), GRL_E_BADARG, "grl_gemm_nt: TF32X3 needs the low parts of B");
+    GRL_CHECK_ARG(out_dtype == GRL_F32 || out_dtype == GRL_BF16, GRL_E_UNSUP, "grl_gemm_nt: output dtype %d", out_dtype);
+    GRL_CHECK_ARG(!(flags & GRL_EPI_BIAS) || bias, GRL_E_BADARG, "grl_gemm_nt: BIAS flag without bias");
+    GRL_CHECK_ARG(p >= 0.0f && p < 1.0f, GRL_E_BADARG, "grl_gemm_nt: p outside [0,1)");
+    GRL_CHECK_ARG(ldc >= N, GRL_E_BADARG, "grl_gemm_nt: ldc < N");
+    const int eb = mode == kBF16 ? 2 : 4;
+    const int64_t ld_mult = 16 / eb;
+    // TMA: 16-byte aligned base pointers and row pitches
+    GRL_CHECK_ARG(lda0 % ld_mult == 0 && ldb0 % ld_mult == 0 && (K1 == 0 || (lda1 % ld_mult == 0 && ldb1 % ld_mult == 0)),
+                  GRL_E_ALIGN, "grl_gemm_nt: leading dimensions must be multiples of %lld elements (16 bytes)", (long long)ld_mult);
+    GRL_CHECK_ARG(aligned_to(A0, 16) && aligned_to(B0, 16) && (K1 == 0 || (aligned_to(A1, 16) && aligned_to(B1, 16))) &&
+                      (mode != kTF32X3 || (aligned_to(B0_lo, 16) && (K1 == 0 || aligned_to(B1_lo, 16)))),
+                  GRL_E_ALIGN, "grl_gemm_nt: operand base pointers must be 16-byte aligned");
+    GRL_CHECK_ARG(lda0 >= K0 && ldb0 >= K0 && (K1 == 0 || (lda1 >= K1 && ldb1 >= K1)), GRL_E_BADARG, "grl_gemm_nt: ld < K");
+
+    if (p == 0.0f) flags &= ~GRL_EPI_DROPOUT;
+    GemmParams gp{};
+    gp.M = M; gp.N = N; gp.C = C; gp.ldc = ldc; gp.out_bf16 = out_dtype == GRL_BF16; gp.bias = bias; gp.flags = flags;
+    gp.scale = 1.0f / (1.0f - p); gp.thresh = keep_threshold(p); gp.mask = mask; gp.seed = seed; gp.stream_id = stream_id;
+    GemmArgs ga{A0, B0, B0_lo, A1, B1, B1_lo, lda0, ldb0, lda1, ldb1, K0, K1};
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool wide = N > 128;
+    switch (mode) {
+        case kBF16: return wide ? launch_gemm<kBF16, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kBF16, 128>(ga, gp, st) : launch_gemm<kBF16, 64>(ga, gp, st));
+        case kTF32: return wide ? launch_gemm<kTF32, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kTF32, 128>(ga, gp, st) : launch_gemm<kTF32, 64>(ga, gp, st));
+        default:    return launch_gemm_x3(ga, gp, st);
+    }
+}

@@ -94,15 +94,98 @@ def colsum(X: torch.Tensor) -> torch.Tensor:
 # ----------------------------------------------------------------------------------------------
 # dense contractions
 # ----------------------------------------------------------------------------------------------
-def gemm(a: torch.Tensor, b: torch.Tensor, out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
-    """C = a @ b for 2-D operands (row-major views allowed).
+class GemmConfig:
+    """fp32_mode: how fp32 operands go through the tensor cores -- "tf32x3" (error-compensated, fp32-grade,
+    the parity mode and default) or "tf32" (single pass, ~1e-3).  bf16 operands always use kind::f16."""
+    fp32_mode = "tf32x3"
 
-    TRANSITIONAL (DESIGN.md "GEMM status"): this is the cuBLAS library call via torch.mm; the
-    tcgen05/TMEM kernel replaces it behind this same function.
-    """
-    if out_dtype is not None and out_dtype != a.dtype:
-        return torch.mm(a, b, out_dtype=out_dtype)  # bf16 operands, fp32 accumulate and output
-    return torch.mm(a, b)
+
+def _mode_for(dtype: torch.dtype) -> int:
+    if dtype == torch.bfloat16:
+        return _lib.GEMM_BF16
+    if dtype == torch.float32:
+        return _lib.GEMM_TF32X3 if GemmConfig.fp32_mode == "tf32x3" else _lib.GEMM_TF32
+    raise _lib.GrlError(f"GEMM operands must be fp32 or bf16, got {dtype}")
+
+
+def _ld_multiple(dtype: torch.dtype) -> int:
+    return 16 // torch.empty(0, dtype=dtype).element_size()
+
+
+def _tma_ready(x: torch.Tensor) -> torch.Tensor:
+    """TMA needs a 16-byte aligned base and row pitch.  Aligned row-major views pass through untouched; anything
+    else (e.g. a dense [*, 4369] fp32 batch handed over without a padded leading dimension) is re-laid once."""
+    m = _ld_multiple(x.dtype)
+    if x.dim() == 2 and x.stride(1) == 1 and x.stride(0) % m == 0 and x.data_ptr() % 16 == 0 and x.stride(0) >= x.shape[1]:
+        return x
+    K = x.shape[1]
+    buf = torch.empty(x.shape[0], (K + m - 1) // m * m, dtype=x.dtype, device=x.device)
+    buf[:, :K].copy_(x)
+    return buf[:, :K]
+
+
+def _prep_weight(b_view: torch.Tensor, dtype: torch.dtype, mode: int):
+    """[N, K] view of a (small) weight -> contiguous, 16-byte-pitched operand(s): (hi, lo) for TF32X3 else (b, None)."""
+    N, K = b_view.shape
+    m = _ld_multiple(dtype)
+    Kp = (K + m - 1) // m * m
+    if mode != _lib.GEMM_TF32X3:
+        if Kp == K:
+            return b_view.to(dtype).contiguous(), None
+        buf = torch.empty(N, Kp, dtype=dtype, device=b_view.device)
+        buf[:, :K].copy_(b_view)
+        return buf[:, :K], None
+    src = b_view.float().contiguous()
+    hi = torch.empty(N, Kp, dtype=torch.float32, device=b_view.device)
+    lo = torch.empty(N, Kp, dtype=torch.float32, device=b_view.device)
+    _lib.check(_lib.load().grl_split_tf32(src.data_ptr(), K, hi.data_ptr(), lo.data_ptr(), Kp, N, K,
+                                          _lib.stream_ptr(src.device)), "grl_split_tf32")
+    _lib.count_launch(1)
+    return hi[:, :K], lo[:, :K]
+
+
+def gemm_nt(a_list: Sequence[torch.Tensor], b_list: Sequence[torch.Tensor], out_dtype: Optional[torch.dtype] = None,
+            bias: Optional[torch.Tensor] = None, relu: bool = False, p: float = 0.0, mask: Optional[torch.Tensor] = None,
+            seed: int = 0, stream_id: int = 0) -> torch.Tensor:
+    """C[M, N] = epilogue(sum_k a_k[M, K_k] @ b_k[N, K_k]^T) on the tcgen05 kernel (csrc/gemm_tcgen05.cu).
+    ``a_k`` are activations (row-major views), ``b_k`` are [N, K_k] views of weights in any layout."""
+    if not 1 <= len(a_list) <= 2 or len(a_list) != len(b_list):
+        raise _lib.GrlError("gemm_nt takes one or two K segments")
+    cdt = a_list[0].dtype
+    mode = _mode_for(cdt)
+    M, N = a_list[0].shape[0], b_list[0].shape[0]
+    out_dtype = out_dtype or cdt
+    C = torch.empty(M, N, dtype=out_dtype, device=a_list[0].device)
+    if M == 0:
+        return C
+    a_ops = [_tma_ready(a) for a in a_list]
+    b_ops = [_prep_weight(b, cdt, mode) for b in b_list]
+    if bias is not None and (bias.dtype != torch.float32 or not bias.is_contiguous()):
+        bias = bias.float().contiguous()
+    if mask is not None and (mask.dtype != torch.uint8 or mask.numel() != M * N or not mask.is_contiguous()):
+        raise _lib.GrlError("dropout mask must be contiguous uint8 [M, N]")
+    flags = (_lib.EPI_BIAS if bias is not None else 0) | (_lib.EPI_RELU if relu else 0) | \
+            (_lib.EPI_DROPOUT if p > 0.0 else 0)
+    two = len(a_list) == 2
+    a1, (b1, b1lo) = (a_ops[1], b_ops[1]) if two else (None, (None, None))
+    _lib.check(_lib.load().grl_gemm_nt(
+        a_ops[0].data_ptr(), a_ops[0].stride(0), b_ops[0][0].data_ptr(), _lib.ptr(b_ops[0][1]), b_ops[0][0].stride(0),
+        a_ops[0].shape[1],
+        _lib.ptr(a1), a1.stride(0) if two else 0, _lib.ptr(b1), _lib.ptr(b1lo), b1.stride(0) if two else 0,
+        a1.shape[1] if two else 0,
+        C.data_ptr(), C.stride(0), _lib.dtype_code(C), M, N, mode, _lib.ptr(bias), flags, float(p), _lib.ptr(mask),
+        int(seed) & (2**64 - 1), int(stream_id), _lib.stream_ptr(C.device)), "grl_gemm_nt")
+    _lib.count_launch(1)
+    return C
+
+
+def gemm_tn_library(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """dW = a^T @ b with fp32 output (reduction over the node dimension, both operands MN-major).
+
+    TRANSITIONAL (DESIGN.md "GEMM status"): cuBLAS via torch.mm until the MN-major tcgen05 kernel lands."""
+    if a.dtype != torch.float32:
+        return torch.mm(a.t(), b, out_dtype=torch.float32)
+    return torch.mm(a.t(), b)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -152,18 +235,12 @@ class _LinearAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, weight, bias, relu, p, mask, seed, stream_id, weight_is_kn, *xs):
         # weight_is_kn: weight stored [in, out] (GraphConv.h_weights) instead of nn.Linear's [out, in]
-        cdt = xs[0].dtype
-        wc = weight if weight.dtype == cdt else weight.to(cdt)
-        off = 0
-        z = None
+        b_views, off = [], 0
         for x in xs:
             K = x.shape[1]
-            wk = wc[off:off + K, :] if weight_is_kn else wc[:, off:off + K].t()
-            zk = gemm(x, wk)
-            z = zk if z is None else z.add_(zk)
+            b_views.append(weight[off:off + K, :].t() if weight_is_kn else weight[:, off:off + K])   # [N, K_k]
             off += K
-        if bias is not None or relu or p > 0.0:
-            epilogue_fwd_(z, bias, z, relu, p, mask, seed, stream_id)
+        z = gemm_nt(xs, b_views, None, bias, relu, p, mask, seed, stream_id)     # epilogue fused in the kernel
         ctx.save_for_backward(weight, z if relu else None, *xs)
         ctx.cfg = (relu, p, weight_is_kn, bias is not None)
         return z
@@ -178,14 +255,10 @@ class _LinearAct(torch.autograd.Function):
             epilogue_bwd_(dY, y, dZ, relu, p)
         else:
             dZ = dY
-        cdt = dZ.dtype
-        wc = weight if weight.dtype == cdt else weight.to(cdt)
         d_weight = d_bias = None
         if ctx.needs_input_grad[0]:
-            parts = []
-            for x in xs:
-                # fp32 master gradient whatever the compute dtype
-                parts.append(gemm(x.t(), dZ, torch.float32) if weight_is_kn else gemm(dZ.t(), x, torch.float32))
+            # fp32 master gradient whatever the compute dtype; [K, N] for h_weights, [N, K] for nn.Linear
+            parts = [gemm_tn_library(x, dZ) if weight_is_kn else gemm_tn_library(dZ, x) for x in xs]
             d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
         if has_bias and ctx.needs_input_grad[1]:
             d_bias = colsum(dZ)
@@ -194,8 +267,9 @@ class _LinearAct(torch.autograd.Function):
         for k, x in enumerate(xs):
             K = x.shape[1]
             if ctx.needs_input_grad[8 + k]:
-                wk = wc[off:off + K, :].t() if weight_is_kn else wc[:, off:off + K]
-                dxs.append(gemm(dZ, wk))
+                # dX_k[M, K_k] = dZ[M, N] @ W_k with W_k presented as the NT "B" operand [K_k, N]
+                wk = weight[off:off + K, :] if weight_is_kn else weight[:, off:off + K].t()
+                dxs.append(gemm_nt([dZ], [wk]))
             else:
                 dxs.append(None)
             off += K

@@ -52,16 +52,19 @@ def make_batch(wl: Workload, seed: int, device, features: str = "dense", B: Opti
         hit = torch.rand(N, L, N, generator=gen, device=dev) < prob
         hit &= ~eye
         A[b] = hit.to(torch.float16)
+    # The collate emits V with a 16-byte-aligned row pitch (leading dimension rounded up to 8 elements) so that
+    # TMA can read it in place; callers see the logical [B, N, input_dim] view.
+    ld = (wl.input_dim + 7) // 8 * 8
+    Vp = torch.zeros(B, N, ld, device=dev, dtype=feature_dtype)
+    V = Vp[:, :, :wl.input_dim]
     if features == "dense":
-        V = torch.rand(B, N, wl.input_dim, generator=gen, device=dev, dtype=torch.float32)
+        for b in range(B):
+            V[b] = torch.rand(N, wl.input_dim, generator=gen, device=dev, dtype=torch.float32).to(feature_dtype)
     elif features == "bow":
-        V = torch.zeros(B, N, wl.input_dim, device=dev, dtype=torch.float32)
         idx = torch.randint(0, wl.input_dim - 4, (B, N, 7), generator=gen, device=dev)
         V.scatter_(2, idx, 1.0)
-        V[:, :, -4:] = 0.09 + 0.91 * torch.rand(B, N, 4, generator=gen, device=dev)
+        V[:, :, -4:] = (0.09 + 0.91 * torch.rand(B, N, 4, generator=gen, device=dev)).to(feature_dtype)
     else:
         raise ValueError(features)
-    if feature_dtype != torch.float32:
-        V = V.to(feature_dtype)
     y = torch.randint(0, wl.output_dim, (B, N), generator=gen, device=dev)
     return V, A, y

@@ -138,6 +138,33 @@ int grl_bias_act_dropout_fwd(const void* X, int64_t ldx, const float* bias, void
 int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void* Y, int64_t ldy,
                              void* dX, int64_t lddx, int dtype, int64_t M, int C,
                              uint32_t flags, float p, void* stream);
+/* ------------------------------------------------------------------------------------------
+ * tcgen05 / TMEM / TMA GEMM with fused epilogue ("NT": both operands K-major, i.e. row-major [rows, K]):
+ *   C[M, N] = dropout(relu( A0[M,K0] * B0[N,K0]^T  (+ A1[M,K1] * B1[N,K1]^T)  + bias ))
+ * Replaces nn.Linear / torch.matmul(new_V, h_weights) + bias (gnn/models/networks/robust_gcn.py:10-11,50;
+ * gnn/models/networks/drop_robust_gcn.py:59,64,89,99-103), the torch.cat feeding them (:84,88: the two K
+ * segments), F.relu and nn.Dropout(p=0.5) after them, and the dX = dZ * W products of their autograd.
+ * mode: GRL_GEMM_BF16 (bf16 operands), GRL_GEMM_TF32 (fp32 operands, single tf32 pass, ~1e-3),
+ *       GRL_GEMM_TF32X3 (fp32 operands, error-compensated 3-pass, fp32-grade ~1e-6; needs B0_lo / B1_lo =
+ *       the low parts of B from grl_split_tf32, B0/B1 being the high parts).
+ * Alignment (TMA): base pointers 16-byte aligned, lda/ldb multiples of 16 bytes.  C: fp32 or bf16, any ldc >= N.
+ * Epilogue flags / dropout bits exactly as grl_bias_act_dropout_fwd (same Philox indexing m*N + n).
+ * ------------------------------------------------------------------------------------------ */
+#define GRL_GEMM_BF16   0
+#define GRL_GEMM_TF32   1
+#define GRL_GEMM_TF32X3 2
+int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo, int64_t ldb0, int K0,
+                const void* A1, int64_t lda1, const void* B1, const void* B1_lo, int64_t ldb1, int K1,
+                void* C, int64_t ldc, int out_dtype, int M, int N, int mode,
+                const float* bias, uint32_t flags, float p, const uint8_t* mask,
+                uint64_t seed, uint64_t stream_id, void* stream);
+/* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
+ * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2. */
+int grl_gemm_x3_set_promo(int promo);
+/* hi = src with the 13 low mantissa bits cleared (exactly representable in tf32), lo = src - hi. */
+int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst,
+                   int64_t rows, int cols, void* stream);
+
 /* column sums  out[c] = sum_m X[m, c]  (bias gradient), fp32 output; out must be zeroed by the caller. */
 int grl_colsum(const void* X, int64_t ldx, int dtype, int64_t M, int C, float* out, void* stream);
 

@@ -1,0 +1,98 @@
+"""tcgen05 GEMM (csrc/gemm_tcgen05.cu) against an fp64 torch matmul of the same operands.
+
+Tolerances: TF32X3 (the fp32 parity mode) 2e-6 norm-wise; single-pass TF32 2e-3; BF16 operands are quantised
+first, so only the fp32 accumulation differs from the fp64 product: 1e-5 (2e-2 once the OUTPUT is bf16)."""
+import pytest
+import torch
+
+from _golden import rel_err
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(128, 256, 64), (128, 128, 32), (300, 256, 1000), (1000, 128, 512), (257, 53, 1280), (100, 16, 128),
+          (640, 1280, 128), (129, 256, 4369), (5, 8, 7)]
+
+
+def _mk(M, N, K, gen, dev, dtype):
+    a = torch.randn(M, K, generator=gen)
+    b = torch.randn(N, K, generator=gen) / K ** 0.5
+    if dtype == torch.bfloat16:
+        a, b = a.bfloat16().float(), b.bfloat16().float()
+    return a, b
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("mode", ["tf32x3", "tf32", "bf16"])
+def test_gemm_nt_plain(M, N, K, mode):
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(M * 7 + N * 3 + K)
+    dtype = torch.bfloat16 if mode == "bf16" else torch.float32
+    a, b = _mk(M, N, K, gen, dev, dtype)
+    ref = a.double() @ b.double().t()
+    ops.GemmConfig.fp32_mode = mode if mode != "bf16" else "tf32x3"
+    try:
+        out = ops.gemm_nt([a.to(dev, dtype)], [b.to(dev, dtype)], out_dtype=torch.float32)
+    finally:
+        ops.GemmConfig.fp32_mode = "tf32x3"
+    tol = {"tf32x3": 2e-6, "tf32": 2e-3, "bf16": 1e-5}[mode]
+    assert out.shape == (M, N)
+    assert rel_err(out.cpu(), ref) < tol
+
+
+@pytest.mark.parametrize("mode", ["tf32x3", "bf16"])
+def test_gemm_nt_two_segments_strided_views_and_epilogue(mode):
+    """virtual concat [x1 | x2] @ W^T with W an [N, K1+K2] nn.Linear weight, x1/x2 column slices of wider buffers,
+    bias + ReLU + injected dropout mask fused."""
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(42)
+    dtype = torch.bfloat16 if mode == "bf16" else torch.float32
+    M, N, K1, K2 = 777, 128, 256, 192
+    big1 = torch.randn(M, K1 + 64, generator=gen).to(dtype)
+    big2 = torch.randn(M, K2 + 32, generator=gen).to(dtype)
+    W = (torch.randn(N, K1 + K2, generator=gen) / 20).to(dtype)
+    bias = torch.randn(N, generator=gen)
+    keep = torch.rand(M, N, generator=gen) < 0.5
+    x1, x2 = big1[:, 64:], big2[:, :K2]
+    ref = torch.relu(torch.cat([x1, x2], 1).double() @ W.double().t() + bias.double()) * keep / 0.5
+    d1, d2, dW = big1.to(dev), big2.to(dev), W.to(dev)
+    out = ops.gemm_nt([d1[:, 64:], d2[:, :K2]], [dW[:, :K1], dW[:, K1:]], bias=bias.to(dev), relu=True, p=0.5,
+                      mask=keep.to(dev, torch.uint8).contiguous())
+    assert out.dtype == dtype
+    assert rel_err(out.cpu(), ref) < (2e-6 if mode == "tf32x3" else 2e-2)
+
+
+def test_gemm_nt_kn_weight_and_philox_matches_unfused_epilogue():
+    """h_weights-style [K, N] weight through a transposed view; fused Philox dropout == the standalone epilogue kernel."""
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(1)
+    M, K, N = 515, 448, 256
+    x = torch.randn(M, K, generator=gen).to(dev)
+    h = (torch.randn(K, N, generator=gen) / 20).to(dev)
+    b = torch.randn(N, generator=gen).to(dev)
+    fused = ops.gemm_nt([x], [h.t()], bias=b, relu=True, p=0.5, seed=77, stream_id=5)
+    plain = ops.gemm_nt([x], [h.t()])
+    assert rel_err(plain.cpu(), x.double().cpu() @ h.double().cpu()) < 2e-6
+    unfused = torch.empty_like(plain)
+    ops.epilogue_fwd_(plain, b, unfused, True, 0.5, None, 77, 5)
+    assert torch.equal(fused, unfused)
+    frac = float((fused != 0).float().mean())
+    assert 0.2 < frac < 0.3          # relu keeps ~half, dropout keeps half of those
+
+
+def test_gemm_large_k_tail_and_m_tail_fp32_grade():
+    """emb1-like: K = 4369 (not a multiple of the 32-element K block), leading dimension padded to 4372."""
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(3)
+    M, N, K = 1000, 256, 4369
+    buf = torch.rand(M, 4372, generator=gen)
+    W = torch.randn(N, K, generator=gen) / 60
+    ref = buf[:, :K].double() @ W.double().t()
+    out = ops.gemm_nt([buf.to(dev)[:, :K]], [W.to(dev)])
+    assert rel_err(out.cpu(), ref) < 2e-6
+    # unaligned input (ld = 4369): re-laid internally, same result
+    out2 = ops.gemm_nt([buf[:, :K].contiguous().to(dev)], [W.to(dev)])
+    assert torch.equal(out, out2)

@@ -98,8 +98,10 @@ inline EncodeTiledFn get_encode_fn() {
 
 // Row-major matrix [rows, cols] with leading dimension ld (elements); box = one 128-byte swizzle atom along the
 // contiguous dimension x box_rows rows.  K-major operands: cols = K.  MN-major operands: cols = the M/N extent.
+// atom32 = true selects CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B (32-byte chunks XOR (row % 4)), the only shared-memory
+// layout the tensor core accepts for MN-major tf32 operands (UMMA layout type SWIZZLE_128B_BASE32B).
 inline int make_tmap_sw128(CUtensorMap* out, const void* ptr, int elem_bytes, int64_t rows, int64_t cols, int64_t ld,
-                           int box_rows) {
+                           int box_rows, bool atom32 = false) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) {
         set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -111,7 +113,8 @@ inline int make_tmap_sw128(CUtensorMap* out, const void* ptr, int elem_bytes, in
     const cuuint32_t estr[2] = {1, 1};
     const CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     CUresult r = enc(out, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (%d): ptr=%p rows=%lld cols=%lld ld=%lld elem=%d box_rows=%d",
                   static_cast<int>(r), ptr, static_cast<long long>(rows), static_cast<long long>(cols),

@@ -1,8 +1,8 @@
-// fp32-grade GEMM on the tf32 tensor cores ("TF32X3"), the fp32 parity mode of every dense projection:
+// fp32-grade GEMMs on the tf32 tensor cores ("TF32X3"), the fp32 parity mode of every dense contraction:
 //
 //   C = A_hi*B_hi  +  (A_lo*B_hi + A_hi*B_lo)          a = a_hi + a_lo,  a_hi = a with 13 low mantissa bits cleared
 //
-// Two measured facts of the sm_100a tensor core shape this kernel (scripts/gemm_accuracy.py, profiles/):
+// Two measured facts of the sm_100a tensor core shape these kernels (scripts/gemm_accuracy.py, profiles/):
 //  (1) each tcgen05.mma accumulation into TMEM truncates (~1.5e-8 relative per step, biased), so a single
 //      accumulator over K = 4369 (1638 steps) ends at 3e-5 -- 30x worse than an fp32 FFMA loop;
 //  (2) the error is proportional to the number of accumulation steps into ONE accumulator.
@@ -10,9 +10,17 @@
 // (4*promo steps), then drained by four dedicated warps into fp32 REGISTERS (round-to-nearest FADD) while the
 // tensor core fills the other of two TMEM accumulators; the two correction products (2^-11 smaller, so their
 // truncation is irrelevant) share a third TMEM accumulator that is read once at the end.
+// Measured: 4-7e-7 norm-wise for K = 32 .. 8192 (cuBLAS fp32 SIMT: 1e-7 .. 1.2e-6) at 2.8x its speed.
 //
-// Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = A splitter (hi/lo in smem),
-// 6..9 = accumulator drain + fused epilogue.  B (weights) arrives pre-split from grl_split_tf32.
+// Two operand arrangements share the kernel body:
+//   kTN = false  "NT":  C[M,N] = A[M,K] * B[N,K]^T      forward projections and dX.  Both operands K-major.
+//                       B = weights, pre-split (hi/lo) by grl_split_tf32; A split in shared memory.
+//   kTN = true   "TN":  C[Ma,Nb] = A[R,Ma]^T * B[R,Nb]  weight gradients: reduction over the node dimension R.
+//                       Both operands MN-major activations, both split in shared memory; split-K over R
+//                       (blockIdx.y), partial tiles to a workspace that grl_gemm_tn reduces deterministically.
+//
+// Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = operand splitter,
+// 6..9 = accumulator drain + fused epilogue.
 #include "gemm_common.cuh"
 
 namespace grl {
@@ -20,22 +28,42 @@ using namespace sm100;
 
 struct X3Cfg {
     static constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 32, UMMA_K = 8;
-    static constexpr int TILE_BYTES = 128 * 128;                    // every operand tile: 128 rows x 128 bytes
-    static constexpr int STAGE_BYTES = 4 * TILE_BYTES;              // A | B_hi | B_lo | A_lo
-    static constexpr int TX_BYTES = 3 * TILE_BYTES;                 // TMA delivers A, B_hi, B_lo
+    static constexpr int TILE_BYTES = 128 * 128;                    // every operand tile is 16 KB
+    static constexpr int STAGE_BYTES = 4 * TILE_BYTES;              // A | B(_hi) | B_lo | A_lo
     static constexpr int STAGES = 3;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
     static constexpr int TMEM_COLS = 512;                           // main0 | main1 | small | (unused)
     static constexpr int THREADS = 320;
 };
 
-#define GRL_X3_RAW_HI (1u << 8)   // experiment: trust the tensor core to ignore the low 13 bits of A (no in-place hi)
+#define GRL_X3_RAW_HI (1u << 8)   // experiment: trust the tensor core to ignore the 13 low bits (no in-place hi write)
 
+// split one 16 KB fp32 tile held in shared memory into hi (in place) and lo; elementwise on raw bytes, so the
+// 128B swizzle written by TMA does not matter
+__device__ __forceinline__ void split_tile(uint8_t* raw, uint8_t* lo_tile, int tid, bool raw_hi) {
+    uint4* a = reinterpret_cast<uint4*>(raw);
+    uint4* alo = reinterpret_cast<uint4*>(lo_tile);
+#pragma unroll
+    for (int i = 0; i < X3Cfg::TILE_BYTES / 16 / 128; ++i) {
+        const int idx = i * 128 + tid;
+        const uint4 v = a[idx];
+        const uint4 hi = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
+        uint4 lo;
+        lo.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x));
+        lo.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y));
+        lo.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z));
+        lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
+        if (!raw_hi) a[idx] = hi;
+        alo[idx] = lo;
+    }
+}
+
+template <bool kTN>
 __global__ void __launch_bounds__(X3Cfg::THREADS, 1)
-gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ CUtensorMap tmA0,
-                  const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmBlo0,
-                  const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
-                  const __grid_constant__ CUtensorMap tmBlo1) {
+gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
+               const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmB0,
+               const __grid_constant__ CUtensorMap tmBlo0, const __grid_constant__ CUtensorMap tmA1,
+               const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ CUtensorMap tmBlo1) {
     using Cfg = X3Cfg;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -44,7 +72,7 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
     uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES);
     uint64_t* full_bar = bars;                     // [STAGES] TMA bytes landed
     uint64_t* empty_bar = bars + STAGES;           // [STAGES] MMAs reading the stage retired
-    uint64_t* split_bar = bars + 2 * STAGES;       // [STAGES] A_hi / A_lo written by the splitter warps
+    uint64_t* split_bar = bars + 2 * STAGES;       // [STAGES] hi / lo tiles written by the splitter warps
     uint64_t* acc_full = bars + 3 * STAGES;        // [2] chunk accumulator complete
     uint64_t* acc_empty = bars + 3 * STAGES + 2;   // [2] chunk accumulator drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
@@ -53,7 +81,11 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
     const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
     const int m0 = (blockIdx.x / tiles_n) * Cfg::BLOCK_M;
     const int n0 = (blockIdx.x % tiles_n) * Cfg::BLOCK_N;
-    const int total_kb = p.kblocks0 + p.kblocks1;
+    // K-block range of this CTA: everything for NT; one slice of the reduction for TN (split-K over blockIdx.y)
+    const int all_kb = p.kblocks0 + p.kblocks1;
+    const int kb_begin = kTN ? static_cast<int>(blockIdx.y) * kb_per_split : 0;
+    const int kb_end = kTN ? min(all_kb, kb_begin + kb_per_split) : all_kb;
+    const int total_kb = max(kb_end - kb_begin, 0);
     const int n_chunks = (total_kb + promo - 1) / promo;
 
     auto tile = [&](int s, int which) { return tiles + s * Cfg::STAGE_BYTES + which * Cfg::TILE_BYTES; };
@@ -62,7 +94,7 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA0);
         tma_prefetch_desc(&tmB0);
-        tma_prefetch_desc(&tmBlo0);
+        if (!kTN) tma_prefetch_desc(&tmBlo0);
         if (p.kblocks1) {
             tma_prefetch_desc(&tmA1);
             tma_prefetch_desc(&tmB1);
@@ -88,43 +120,67 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
     if (warp == 0) {
         // ===================================================================== TMA producer (one lane)
         if (lane == 0) {
-            for (int kb = 0; kb < total_kb; ++kb) {
-                const int s = kb % STAGES;
-                const uint32_t ph = (kb / STAGES) & 1;
+            for (int it = 0; it < total_kb; ++it) {
+                const int kb = kb_begin + it;
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);
-                mbar_expect_tx(&full_bar[s], Cfg::TX_BYTES);
-                const bool seg1 = kb >= p.kblocks0;
-                const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
-                tma_load_2d(tile(s, T_A), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
-                tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
-                tma_load_2d(tile(s, T_BLO), seg1 ? &tmBlo1 : &tmBlo0, &full_bar[s], k_elem, n0);
+                if constexpr (kTN) {
+                    // operands are [R, Ma] / [R, Nb] row-major: 4 boxes of {32 columns (128 B), 32 reduction rows}
+                    mbar_expect_tx(&full_bar[s], 2 * Cfg::TILE_BYTES);
+                    const int r0 = kb * Cfg::BLOCK_K;
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) {
+                        tma_load_2d(tile(s, T_A) + a * 4096, &tmA0, &full_bar[s], m0 + a * 32, r0);
+                        tma_load_2d(tile(s, T_B) + a * 4096, &tmB0, &full_bar[s], n0 + a * 32, r0);
+                    }
+                } else {
+                    mbar_expect_tx(&full_bar[s], 3 * Cfg::TILE_BYTES);
+                    const bool seg1 = kb >= p.kblocks0;
+                    const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
+                    tma_load_2d(tile(s, T_A), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
+                    tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
+                    tma_load_2d(tile(s, T_BLO), seg1 ? &tmBlo1 : &tmBlo0, &full_bar[s], k_elem, n0);
+                }
             }
         }
     } else if (warp == 1) {
         // ===================================================================== MMA issuer (one lane)
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc(2, Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 0);
+            constexpr uint32_t idesc = umma_idesc(2, Cfg::BLOCK_M, Cfg::BLOCK_N, kTN ? 1 : 0, kTN ? 1 : 0);
             const uint32_t d_small = tmem_base + 256;
-            int kb = 0;
+            int it = 0;
             for (int c = 0; c < n_chunks; ++c) {
                 const int buf = c & 1;
                 mbar_wait(&acc_empty[buf], ((c >> 1) & 1) ^ 1);      // drained (first two uses pass immediately)
                 tc_fence_after_sync();
                 const uint32_t d_main = tmem_base + buf * 128;
-                for (int i = 0; i < promo && kb < total_kb; ++i, ++kb) {
-                    const int s = kb % STAGES;
-                    const uint32_t ph = (kb / STAGES) & 1;
+                for (int i = 0; i < promo && it < total_kb; ++i, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
                     mbar_wait(&split_bar[s], ph);
                     tc_fence_after_sync();
-                    const uint64_t a_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_A)));
-                    const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_B)));
-                    const uint64_t alo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_ALO)));
-                    const uint64_t blo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_BLO)));
+                    uint64_t a_desc, b_desc, alo_desc, blo_desc;
+                    if constexpr (kTN) {
+                        // MN-major tf32: 128-byte atoms of 32 columns 4096 B apart (LBO); swizzle pattern of 4 reduction
+                        // rows = 512 B (SBO); layout SWIZZLE_128B_BASE32B as written by TMA's SWIZZLE_128B_ATOM_32B
+                        constexpr uint32_t lbo = 4096, sbo = 512;
+                        a_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_A)), lbo, sbo, 1);
+                        b_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_B)), lbo, sbo, 1);
+                        alo_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_ALO)), lbo, sbo, 1);
+                        blo_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_BLO)), lbo, sbo, 1);
+                    } else {
+                        a_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_A)));
+                        b_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_B)));
+                        alo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_ALO)));
+                        blo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_BLO)));
+                    }
 #pragma unroll
                     for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
-                        const uint64_t koff = static_cast<uint64_t>(k * 2);
+                        // one UMMA_K step: 32 bytes along a K-major row, or 8 rows (1024 B) of an MN-major tile
+                        const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
                         umma<true>(d_main, a_desc + koff, b_desc + koff, idesc, (i | k) != 0);
-                        umma<true>(d_small, alo_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                        umma<true>(d_small, alo_desc + koff, b_desc + koff, idesc, (it | k) != 0);
                         umma<true>(d_small, a_desc + koff, blo_desc + koff, idesc, 1u);
                     }
                     umma_commit(&empty_bar[s]);
@@ -133,29 +189,15 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
             }
         }
     } else if (warp < 6) {
-        // ===================================================================== A splitter (warps 2..5)
-        // elementwise on the raw tile bytes, so the 128B swizzle written by TMA is irrelevant here
+        // ===================================================================== operand splitter (warps 2..5)
         const int tid = threadIdx.x - 64;
         const bool raw_hi = (p.flags & GRL_X3_RAW_HI) != 0;
-        for (int kb = 0; kb < total_kb; ++kb) {
-            const int s = kb % STAGES;
-            const uint32_t ph = (kb / STAGES) & 1;
+        for (int it = 0; it < total_kb; ++it) {
+            const int s = it % STAGES;
+            const uint32_t ph = (it / STAGES) & 1;
             mbar_wait(&full_bar[s], ph);
-            uint4* a = reinterpret_cast<uint4*>(tile(s, T_A));
-            uint4* alo = reinterpret_cast<uint4*>(tile(s, T_ALO));
-#pragma unroll
-            for (int i = 0; i < Cfg::TILE_BYTES / 16 / 128; ++i) {
-                const int idx = i * 128 + tid;
-                const uint4 v = a[idx];
-                const uint4 hi = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
-                uint4 lo;
-                lo.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x));
-                lo.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y));
-                lo.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z));
-                lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
-                if (!raw_hi) a[idx] = hi;
-                alo[idx] = lo;
-            }
+            split_tile(tile(s, T_A), tile(s, T_ALO), tid, raw_hi);
+            if constexpr (kTN) split_tile(tile(s, T_B), tile(s, T_BLO), tid, raw_hi);
             fence_proxy_async_smem();
             mbar_arrive(&split_bar[s]);
         }
@@ -181,24 +223,29 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
             tc_fence_before_sync();
             mbar_arrive(&acc_empty[buf]);
         }
-        // correction terms (complete: the last acc_full commit covers every earlier MMA)
+        if (n_chunks > 0) {
+            // correction terms (complete: the last acc_full commit covers every earlier MMA)
 #pragma unroll
-        for (int j = 0; j < Cfg::BLOCK_N; j += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32(lane_base + 256 + j, r);
-            tmem_ld_wait();
+            for (int j = 0; j < Cfg::BLOCK_N; j += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(lane_base + 256 + j, r);
+                tmem_ld_wait();
 #pragma unroll
-            for (int t = 0; t < 32; ++t) acc[j + t] += __uint_as_float(r[t]);
+                for (int t = 0; t < 32; ++t) acc[j + t] += __uint_as_float(r[t]);
+            }
         }
         const int row = m0 + quarter * 32 + lane;
         if (row < p.M) {
-            const bool vec_ok = epilogue_vec_ok(p);
+            GemmParams q = p;
+            if constexpr (kTN)   // partial tile of split blockIdx.y -> its slab of the workspace
+                q.C = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.ldc;
+            const bool vec_ok = epilogue_vec_ok(q);
 #pragma unroll
             for (int j = 0; j < Cfg::BLOCK_N; j += 4) {
                 const int col = n0 + j;
                 if (col < p.N) {
                     float v[4] = {acc[j], acc[j + 1], acc[j + 2], acc[j + 3]};
-                    epilogue_store4(p, row, col, v, vec_ok);
+                    epilogue_store4(q, row, col, v, vec_ok);
                 }
             }
         }
@@ -209,6 +256,18 @@ gemm_nt_x3_kernel(const GemmParams p, const int promo, const __grid_constant__ C
 }
 
 static int g_x3_promo = 2;
+
+template <bool kTN>
+static int ensure_smem_attr() {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_x3_kernel<kTN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             X3Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+        attr_set = true;
+    }
+    return 0;
+}
 
 int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     using Cfg = X3Cfg;
@@ -225,28 +284,79 @@ int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     }
     p.kblocks0 = (a.K0 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K;
     p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_nt_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
-        attr_set = true;
-    }
+    if ((rc = ensure_smem_attr<false>())) return rc;
     const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
-    gemm_nt_x3_kernel<<<tiles_m * tiles_n, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, tA0, tB0, tBlo0, tA1, tB1,
-                                                                              tBlo1);
-    GRL_LAUNCH_CHECK("gemm_nt_x3_kernel");
+    gemm_x3_kernel<false><<<tiles_m * tiles_n, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, 0, tA0, tB0, tBlo0, tA1,
+                                                                                   tB1, tBlo1);
+    GRL_LAUNCH_CHECK("gemm_x3_kernel<NT>");
     return 0;
+}
+
+// out[i] = sum_s ws[s][i]   (deterministic split-K reduction; float4 lanes)
+__global__ void reduce_splits_kernel(const float* __restrict__ ws, float* __restrict__ out, int64_t n, int splits) {
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float s = 0.0f;
+        for (int k = 0; k < splits; ++k) s += ws[static_cast<int64_t>(k) * n + i];
+        out[i] = s;
+    }
 }
 
 }  // namespace grl
 
-// Tuning / experiment knobs of the TF32X3 kernel (host call): promo = K-blocks (of 32) accumulated in TMEM before
+using namespace grl;
+
+// Tuning / experiment knob of the TF32X3 kernels (host call): promo = K-blocks (of 32) accumulated in TMEM before
 // the partial sum is promoted to fp32 registers (>= 1).
 extern "C" int grl_gemm_x3_set_promo(int promo) {
     if (promo < 1 || promo > 1 << 20) {
-        grl::set_error("grl_gemm_x3_set_promo: promo=%d must be >= 1", promo);
+        set_error("grl_gemm_x3_set_promo: promo=%d must be >= 1", promo);
         return GRL_E_BADARG;
     }
-    grl::g_x3_promo = promo;
+    g_x3_promo = promo;
+    return 0;
+}
+
+extern "C" size_t grl_gemm_tn_workspace_bytes(int Ma, int Nb) {
+    // splits * tiles <= kNumSMs and Ma*Nb <= tiles * 128*128, so splits*Ma*Nb <= kNumSMs * 128*128 (or Ma*Nb if 1 split)
+    const size_t one = static_cast<size_t>(Ma) * Nb, cap = static_cast<size_t>(kNumSMs) * 128 * 128;
+    return sizeof(float) * (one > cap ? one : cap);
+}
+
+extern "C" int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int Ma,
+                           int Nb, int64_t R, void* workspace, size_t workspace_bytes, void* stream) {
+    using Cfg = X3Cfg;
+    GRL_CHECK_ARG(A && B && C && workspace, GRL_E_BADARG, "grl_gemm_tn: null pointer");
+    GRL_CHECK_ARG(Ma > 0 && Nb > 0 && R > 0 && R < (1LL << 31), GRL_E_BADARG, "grl_gemm_tn: bad shape");
+    GRL_CHECK_ARG(lda >= Ma && ldb >= Nb && ldc == Nb, GRL_E_BADARG, "grl_gemm_tn: bad leading dimension (C must be dense)");
+    GRL_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && aligned_to(A, 16) && aligned_to(B, 16), GRL_E_ALIGN,
+                  "grl_gemm_tn: operands need 16-byte aligned base pointers and row pitches");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CUtensorMap tA, tB;
+    int rc;
+    // [R, cols] row-major; box = {32 columns, 32 rows}
+    if ((rc = make_tmap_sw128(&tA, A, 4, R, Ma, lda, Cfg::BLOCK_K, true))) return rc;
+    if ((rc = make_tmap_sw128(&tB, B, 4, R, Nb, ldb, Cfg::BLOCK_K, true))) return rc;
+    GemmParams p{};
+    p.M = Ma; p.N = Nb; p.ldc = Nb; p.C = workspace;
+    p.kblocks0 = static_cast<int>((R + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K);
+    p.kblocks1 = 0;
+    const int tiles = ((Ma + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M) * ((Nb + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N);
+    int splits = kNumSMs / tiles;
+    if (splits < 1) splits = 1;
+    if (splits > p.kblocks0) splits = p.kblocks0;
+    const int kb_per_split = (p.kblocks0 + splits - 1) / splits;
+    splits = (p.kblocks0 + kb_per_split - 1) / kb_per_split;          // no empty split
+    const size_t need = sizeof(float) * static_cast<size_t>(Ma) * Nb * splits;
+    GRL_CHECK_ARG(workspace_bytes >= need, GRL_E_WORKSPACE, "grl_gemm_tn: workspace %zu < %zu", workspace_bytes, need);
+    if ((rc = ensure_smem_attr<true>())) return rc;
+    gemm_x3_kernel<true><<<dim3(tiles, splits), Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, kb_per_split, tA, tB, tB,
+                                                                                    tA, tB, tB);
+    GRL_LAUNCH_CHECK("gemm_x3_kernel<TN>");
+    const int64_t n = static_cast<int64_t>(Ma) * Nb;
+    int blocks = static_cast<int>((n + 255) / 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    reduce_splits_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(workspace), C, n, splits);
+    GRL_LAUNCH_CHECK("reduce_splits_kernel");
     return 0;
 }

@@ -112,13 +112,17 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor_sw128(uint32_t smem_addr) {
 // MN-major operand with 128-byte swizzle: the contiguous (MN) direction holds 128-byte atoms of 64 bf16 / 32 fp32;
 // 8 K-rows form one 1024-byte swizzle pattern.  LBO = byte distance between successive MN atoms (64/32 elements apart),
 // SBO = byte distance between successive groups of 8 K-rows.
-__device__ __forceinline__ uint64_t umma_desc_mnmajor_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout_type: 2 = SWIZZLE_128B (16-bit operands: 8 K-rows per swizzle pattern, SBO = 1024),
+//              1 = SWIZZLE_128B_BASE32B (the ONLY layout for MN-major tf32 operands, written by TMA's
+//                  SWIZZLE_128B_ATOM_32B: 4 K-rows per pattern, SBO = 512).
+__device__ __forceinline__ uint64_t umma_desc_mnmajor_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                            uint32_t layout_type) {
     uint64_t d = 0;
     d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
     d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
     d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
     d |= static_cast<uint64_t>(1) << 46;
-    d |= static_cast<uint64_t>(2) << 61;
+    d |= static_cast<uint64_t>(layout_type & 7u) << 61;
     return d;
 }
 

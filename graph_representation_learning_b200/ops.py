@@ -179,13 +179,31 @@ def gemm_nt(a_list: Sequence[torch.Tensor], b_list: Sequence[torch.Tensor], out_
     return C
 
 
-def gemm_tn_library(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
-    """dW = a^T @ b with fp32 output (reduction over the node dimension, both operands MN-major).
+_tn_workspace = {}
 
-    TRANSITIONAL (DESIGN.md "GEMM status"): cuBLAS via torch.mm until the MN-major tcgen05 kernel lands."""
+
+def gemm_tn(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """dW[Ma, Nb] = a[R, Ma]^T @ b[R, Nb], fp32 output: the weight-gradient contraction over the node dimension.
+
+    fp32 operands: MN-major TF32X3 tcgen05 kernel with split-K (csrc/gemm_x3_tcgen05.cu, grl_gemm_tn).
+    bf16 operands: TRANSITIONAL (DESIGN.md "GEMM status") cuBLAS via torch.mm until the bf16 MN-major kernel lands."""
     if a.dtype != torch.float32:
         return torch.mm(a.t(), b, out_dtype=torch.float32)
-    return torch.mm(a.t(), b)
+    a, b = _tma_ready(a), _tma_ready(b)
+    R, Ma = a.shape
+    Nb = b.shape[1]
+    C = torch.empty(Ma, Nb, dtype=torch.float32, device=a.device)
+    lib = _lib.load()
+    ws_bytes = lib.grl_gemm_tn_workspace_bytes(Ma, Nb)
+    key = (a.device, torch.cuda.current_stream(a.device).cuda_stream)
+    ws = _tn_workspace.get(key)
+    if ws is None or ws.numel() < ws_bytes:          # one reusable split-K workspace per (device, stream)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=a.device)
+        _tn_workspace[key] = ws
+    _lib.check(lib.grl_gemm_tn(a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), C.data_ptr(), Nb, Ma, Nb, R,
+                               ws.data_ptr(), ws.numel(), _lib.stream_ptr(a.device)), "grl_gemm_tn")
+    _lib.count_launch(2)
+    return C
 
 
 # ----------------------------------------------------------------------------------------------
@@ -258,7 +276,7 @@ class _LinearAct(torch.autograd.Function):
         d_weight = d_bias = None
         if ctx.needs_input_grad[0]:
             # fp32 master gradient whatever the compute dtype; [K, N] for h_weights, [N, K] for nn.Linear
-            parts = [gemm_tn_library(x, dZ) if weight_is_kn else gemm_tn_library(dZ, x) for x in xs]
+            parts = [gemm_tn(x, dZ) if weight_is_kn else gemm_tn(dZ, x) for x in xs]
             d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
         if has_bias and ctx.needs_input_grad[1]:
             d_bias = colsum(dZ)

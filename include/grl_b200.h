@@ -161,6 +161,13 @@ int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo,
 /* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
  * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2. */
 int grl_gemm_x3_set_promo(int promo);
+/* Weight-gradient GEMM ("TN", reduction over the node dimension R, both operands MN-major fp32 activations):
+ *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]        fp32-grade TF32X3 on tcgen05, split-K over R, deterministic reduce.
+ * Replaces autograd's dW = new_V^T * dOut / dOut^T * X of gnn/models/networks/robust_gcn.py:50 and of every
+ * nn.Linear on the path.  C dense (ldc == Nb); lda/ldb multiples of 4, bases 16-byte aligned. */
+size_t grl_gemm_tn_workspace_bytes(int Ma, int Nb);
+int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                int Ma, int Nb, int64_t R, void* workspace, size_t workspace_bytes, void* stream);
 /* hi = src with the 13 low mantissa bits cleared (exactly representable in tf32), lo = src - hi. */
 int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst,
                    int64_t rows, int cols, void* stream);

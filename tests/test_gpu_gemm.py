@@ -96,3 +96,32 @@ def test_gemm_large_k_tail_and_m_tail_fp32_grade():
     # unaligned input (ld = 4369): re-laid internally, same result
     out2 = ops.gemm_nt([buf[:, :K].contiguous().to(dev)], [W.to(dev)])
     assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("R,Ma,Nb", [(1000, 256, 128), (128, 128, 128), (33, 40, 24), (5000, 1792, 256), (777, 53, 1280),
+                                     (20000, 300, 256)])
+def test_gemm_tn_weight_gradient(R, Ma, Nb):
+    """dW = A^T B over the node dimension (MN-major operands, split-K, deterministic reduce), fp32-grade."""
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(R + Ma + Nb)
+    a = torch.randn(R, Ma, generator=gen)
+    b = torch.randn(R, Nb, generator=gen)
+    ref = a.double().t() @ b.double()
+    out = ops.gemm_tn(a.to(dev), b.to(dev))
+    assert out.shape == (Ma, Nb) and out.dtype == torch.float32
+    assert rel_err(out.cpu(), ref) < 2e-6
+    again = ops.gemm_tn(a.to(dev), b.to(dev))
+    assert torch.equal(out, again)          # split-K partials are reduced in a fixed order
+
+
+def test_gemm_tn_strided_operands_emb1_like():
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(8)
+    R, K, N = 3000, 4369, 256
+    buf = torch.rand(R, 4376, generator=gen)
+    dz = torch.randn(R, N, generator=gen)
+    ref = dz.double().t() @ buf[:, :K].double()
+    out = ops.gemm_tn(dz.to(dev), buf.to(dev)[:, :K])          # nn.Linear layout [out, in]
+    assert rel_err(out.cpu(), ref) < 2e-6

@@ -37,6 +37,10 @@ def parse_args():
     ap.add_argument("--cpu-batch", type=int, default=8, help="graphs per step of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="bracket ONE extra train step (after the timed region) with cudaProfilerStart/Stop for "
+                         "`ncu --profile-from-start off`; numbers printed by such a run are not bench values")
     return ap.parse_args()
 
 
@@ -187,6 +191,13 @@ def run_b200(args):
     # (1) device-resident inputs: the whole forward([V, A]) API call incl. the CSR/CSC pack of the dense fp16 A
     ms_step, launches, clocks = timed(lambda: step.run_train_step(batch_dev), args.steps, args.warmup)
     value = world * B / (ms_step * 1e-3)
+
+    if args.profile_step:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step.run_train_step(batch_dev)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
 
     # (2) end to end: pinned HOST buffers -> H2D inside the timed region, loss read back to the host
     e2e = None

@@ -42,6 +42,7 @@ SIGNATURES = {
     "grl_dropedge_weights": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_uint64, c_uint64, c_void_p, c_void_p]),
     "grl_spmm_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,
                              c_int, c_int, c_void_p]),
+    "grl_spmm_set_tile_mode": (c_int, [c_int]),
     "grl_spmm_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int,
                              c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "grl_bias_act_dropout_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int,

@@ -24,28 +24,29 @@ struct GemmParams {
     uint64_t seed, stream_id;
 };
 
-// Fused epilogue for 4 consecutive columns [col, col+4) of one output row held in registers.
+// Fused epilogue for 4 consecutive columns [col, col+4) of one output row held in registers (bias already added).
 // Same Philox indexing (row*N + col) as grl_bias_act_dropout_fwd, so fused and unfused paths agree bit for bit.
 __device__ __forceinline__ void epilogue_store4(const GemmParams& p, int row, int col, float (&v)[4], bool vec_ok) {
-    if (p.flags & GRL_EPI_BIAS) {
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-            if (col + t < p.N) v[t] += __ldg(p.bias + col + t);
-    }
     if (p.flags & GRL_EPI_RELU) {
 #pragma unroll
         for (int t = 0; t < 4; ++t) v[t] = fmaxf(v[t], 0.0f);
     }
     if (p.flags & GRL_EPI_DROPOUT) {
         const int64_t e0 = static_cast<int64_t>(row) * p.N + col;
+        bool keep[4];
+        if (p.mask) {
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {
-            if (col + t < p.N) {
-                const bool keep = p.mask ? (p.mask[e0 + t] != 0)
-                                         : (Philox::word(p.seed, p.stream_id, static_cast<uint64_t>(e0 + t)) >= p.thresh);
-                v[t] = keep ? v[t] * p.scale : 0.0f;
-            }
+            for (int t = 0; t < 4; ++t) keep[t] = (col + t < p.N) && p.mask[e0 + t] != 0;
+        } else if ((e0 & 3) == 0) {       // the 4 elements share one Philox block (always when N % 4 == 0)
+            const uint4 d = Philox::draw(p.seed, p.stream_id, static_cast<uint64_t>(e0) >> 2);
+            keep[0] = d.x >= p.thresh; keep[1] = d.y >= p.thresh; keep[2] = d.z >= p.thresh; keep[3] = d.w >= p.thresh;
+        } else {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                keep[t] = Philox::word(p.seed, p.stream_id, static_cast<uint64_t>(e0 + t)) >= p.thresh;
         }
+#pragma unroll
+        for (int t = 0; t < 4; ++t) v[t] = keep[t] ? v[t] * p.scale : 0.0f;
     }
     if (p.out_bf16) {
         __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.C) + static_cast<int64_t>(row) * p.ldc + col;
@@ -76,6 +77,36 @@ __device__ __forceinline__ void epilogue_store4(const GemmParams& p, int row, in
 __device__ __forceinline__ bool epilogue_vec_ok(const GemmParams& p) {
     const int eb = p.out_bf16 ? 2 : 4;
     return (p.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.C) % (4 * eb)) == 0);
+}
+
+// Epilogue of one warp over ITS 32 accumulator rows, staged in shared memory as fp32 [128][BLOCK_N + 4] (the pad keeps
+// the row-per-thread staging stores and the row-contiguous reads below bank-conflict free).  A compact loop -- the
+// fully unrolled register version was 10k straight-line instructions per warp and ran out of the instruction cache --
+// and every global store is one contiguous 512-byte (fp32) / 256-byte (bf16) row segment per warp.
+template <int BLOCK_N>
+__device__ __forceinline__ void epilogue_warp_rows(const GemmParams& p, const float* stage, int warp_row0, int m0, int n0,
+                                                   int lane) {
+    constexpr int PITCH = BLOCK_N + 4;
+    const bool vec_ok = epilogue_vec_ok(p);
+#pragma unroll 1
+    for (int cpass = 0; cpass < BLOCK_N; cpass += 128) {
+        const int cl = cpass + lane * 4;
+        const int col = n0 + cl;
+        if (cl >= BLOCK_N || col >= p.N) continue;
+        float b4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (p.flags & GRL_EPI_BIAS) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (col + t < p.N) b4[t] = __ldg(p.bias + col + t);
+        }
+        const int rows = min(32, p.M - (m0 + warp_row0));
+#pragma unroll 2
+        for (int rr = 0; rr < rows; ++rr) {
+            const float4 t4 = *reinterpret_cast<const float4*>(stage + (warp_row0 + rr) * PITCH + cl);
+            float v[4] = {t4.x + b4[0], t4.y + b4[1], t4.z + b4[2], t4.w + b4[3]};
+            epilogue_store4(p, m0 + warp_row0 + rr, col, v, vec_ok);
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -119,6 +150,31 @@ inline int make_tmap_sw128(CUtensorMap* out, const void* ptr, int elem_bytes, in
         set_error("cuTensorMapEncodeTiled failed (%d): ptr=%p rows=%lld cols=%lld ld=%lld elem=%d box_rows=%d",
                   static_cast<int>(r), ptr, static_cast<long long>(rows), static_cast<long long>(cols),
                   static_cast<long long>(ld), elem_bytes, box_rows);
+        return GRL_E_BADARG;
+    }
+    return 0;
+}
+
+// Plain (un-swizzled) 2-D tile map over a row-major [rows, cols] matrix: box = box_cols x box_rows elements, rows and
+// columns past the tensor are zero-filled.  Used by the SpMM kernels to stage one graph's feature slab in shared memory.
+inline int make_tmap_plain(CUtensorMap* out, const void* ptr, int elem_bytes, int64_t rows, int64_t cols, int64_t ld,
+                           int box_cols, int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return GRL_E_UNSUP;
+    }
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * elem_bytes};
+    const cuuint32_t box[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    CUresult r = enc(out, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(plain) failed (%d): ptr=%p rows=%lld cols=%lld ld=%lld elem=%d box=%dx%d",
+                  static_cast<int>(r), ptr, static_cast<long long>(rows), static_cast<long long>(cols),
+                  static_cast<long long>(ld), elem_bytes, box_cols, box_rows);
         return GRL_E_BADARG;
     }
     return 0;

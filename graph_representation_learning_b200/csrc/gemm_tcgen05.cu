@@ -118,25 +118,22 @@ gemm_nt_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA0, con
         mbar_wait(accum_bar, 0);
         tc_fence_after_sync();
         const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
-        const int row = m0 + quarter * 32 + lane;
-        const bool row_ok = row < p.M;
-        const bool vec_ok = epilogue_vec_ok(p);
+        // accumulator complete => every TMA load was consumed: the operand stages are free to stage the tile
+        float* stage = reinterpret_cast<float*>(tiles);
+        constexpr int PITCH = BLOCK_N + 4;
+        float* my_row = stage + (quarter * 32 + lane) * PITCH;
 #pragma unroll 1
         for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
             if (n0 + c0 >= p.N) break;                      // warp-uniform
             uint32_t r[32];
             tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + c0, r);
             tmem_ld_wait();
-            if (!row_ok) continue;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                const int col = n0 + c0 + j;
-                if (col >= p.N) break;
-                float v[4] = {__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                              __uint_as_float(r[j + 3])};
-                epilogue_store4(p, row, col, v, vec_ok);
-            }
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<uint4*>(my_row + c0 + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
         }
+        __syncwarp();
+        epilogue_warp_rows<BLOCK_N>(p, stage, quarter * 32, m0, n0, lane);
     }
     tc_fence_before_sync();
     __syncthreads();

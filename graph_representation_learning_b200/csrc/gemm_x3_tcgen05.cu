@@ -234,21 +234,19 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
                 for (int t = 0; t < 32; ++t) acc[j + t] += __uint_as_float(r[t]);
             }
         }
-        const int row = m0 + quarter * 32 + lane;
-        if (row < p.M) {
-            GemmParams q = p;
-            if constexpr (kTN)   // partial tile of split blockIdx.y -> its slab of the workspace
-                q.C = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.ldc;
-            const bool vec_ok = epilogue_vec_ok(q);
+        // Stage this warp's 32 rows in the (now idle) operand buffers, then run the compact coalesced epilogue.
+        // Every MMA has completed (last acc_full), hence every TMA load and splitter write was consumed: smem is free.
+        float* stage = reinterpret_cast<float*>(tiles);
+        constexpr int PITCH = Cfg::BLOCK_N + 4;
+        float* my_row = stage + (quarter * 32 + lane) * PITCH;
 #pragma unroll
-            for (int j = 0; j < Cfg::BLOCK_N; j += 4) {
-                const int col = n0 + j;
-                if (col < p.N) {
-                    float v[4] = {acc[j], acc[j + 1], acc[j + 2], acc[j + 3]};
-                    epilogue_store4(q, row, col, v, vec_ok);
-                }
-            }
-        }
+        for (int j = 0; j < Cfg::BLOCK_N; j += 4)
+            *reinterpret_cast<float4*>(my_row + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+        __syncwarp();
+        GemmParams q = p;
+        if constexpr (kTN)   // partial tile of split blockIdx.y -> its slab of the workspace
+            q.C = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.ldc;
+        epilogue_warp_rows<Cfg::BLOCK_N>(q, stage, quarter * 32, m0, n0, lane);
     }
     tc_fence_before_sync();
     __syncthreads();

@@ -117,6 +117,11 @@ int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
                  const void* X, int64_t ldx, void* Y, int64_t ldy, int dtype,
                  int B, int N, int L, int F, void* stream);
 
+/* Kernel selection knob of grl_spmm_fwd (host call, process-global; experiments and tests):
+ *   0 = auto (shared-memory slab kernel when one graph's [N, chunk] feature slab fits, else the L2 gather kernel),
+ *  -1 = always the gather kernel,  4 / 8 / 16 = slab kernel with that many bytes per lane (falls back if it does not fit). */
+int grl_spmm_set_tile_mode(int mode);
+
 /* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.
  *   dX[b*N+j, 0:F] = sum_{k in column (b*N+j)} w[perm[k]] * dY[rowidx[k], 0:F]
  * dY: [R, F] (ld = lddy), dX: [B*N, F] (ld = lddx); accumulate != 0 adds into dX. */

@@ -85,6 +85,100 @@ spmm_rows_kernel(const int32_t* __restrict__ ptr, const int32_t* __restrict__ id
     }
 }
 
+// Forward aggregation, one warp per NODE: all (L+1) typed rows of a node are contiguous in CSR, so the warp fetches
+// the node's (L+2) row pointers with one load and up to 64 (column, weight) pairs with two coalesced loads, turns
+// each column into a ready-made 16-byte-unit row offset in its own lane, and then walks the entries with two
+// shuffles + one address add per entry.  The per-row bookkeeping of spmm_rows_kernel (53 issued instructions per
+// entry, 63 % issue-slot utilisation in ncu: the kernel was issue-bound, not HBM-bound) is amortised over ~50 entries.
+template <typename T, int CHUNKS>
+__global__ void __launch_bounds__(256)
+spmm_nodes_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ w,
+                  const T* __restrict__ X, uint32_t ldx16, T* __restrict__ Y, int64_t ldy, int64_t n_nodes,
+                  int nodes_per_graph, int Lp1) {
+    constexpr int E = Vec16<T>::kElems;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    const uint4* xlane = reinterpret_cast<const uint4*>(X) + lane;      // 16-byte units
+
+    for (int64_t node = warp; node < n_nodes; node += n_warps) {
+        const int64_t r0 = node * Lp1;
+        const int32_t rp = (lane <= Lp1) ? __ldg(rowptr + r0 + lane) : 0;
+        const int32_t e0 = __shfl_sync(0xffffffffu, rp, 0);
+        const int32_t total = __shfl_sync(0xffffffffu, rp, Lp1) - e0;
+        const uint32_t base = static_cast<uint32_t>((node / nodes_per_graph) * nodes_per_graph);
+        // this lane's two entries: (row offset in 16-byte units, weight); weight 0 = dropped or out of range
+        uint32_t o0 = 0, o1 = 0;
+        float w0 = 0.0f, w1 = 0.0f;
+        if (lane < total) {
+            o0 = (base + static_cast<uint32_t>(__ldg(col + e0 + lane))) * ldx16;
+            w0 = __ldg(w + e0 + lane);
+        }
+        if (lane + 32 < total) {
+            o1 = (base + static_cast<uint32_t>(__ldg(col + e0 + 32 + lane))) * ldx16;
+            w1 = __ldg(w + e0 + 32 + lane);
+        }
+        T* out = Y + r0 * ldy + lane * E;
+        for (int t = 0; t < Lp1; ++t, out += ldy) {
+            const int beg = __shfl_sync(0xffffffffu, rp, t) - e0;
+            const int end = __shfl_sync(0xffffffffu, rp, t + 1) - e0;
+            float acc[CHUNKS][E];
+#pragma unroll
+            for (int c = 0; c < CHUNKS; ++c)
+#pragma unroll
+                for (int k = 0; k < E; ++k) acc[c][k] = 0.0f;
+            for (int k0 = beg; k0 < end; k0 += 4) {
+                float v[4][CHUNKS][E];
+                float wt[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int k = k0 + u;
+                    uint32_t off;
+                    if (k < 64) {                                   // warp-uniform
+                        off = __shfl_sync(0xffffffffu, k < 32 ? o0 : o1, k & 31);
+                        wt[u] = __shfl_sync(0xffffffffu, k < 32 ? w0 : w1, k & 31);
+                    } else if (k < end) {                           // rare: > 64 entries on one node
+                        off = (base + static_cast<uint32_t>(__ldg(col + e0 + k))) * ldx16;
+                        wt[u] = __ldg(w + e0 + k);
+                    } else {
+                        off = 0;
+                        wt[u] = 0.0f;
+                    }
+                    if (k >= end) wt[u] = 0.0f;
+                    if (wt[u] != 0.0f) {                            // dropped edges (weight 0) are never fetched
+#pragma unroll
+                        for (int c = 0; c < CHUNKS; ++c) {
+                            const uint4 q = __ldg(xlane + off + c * 32);
+                            if constexpr (E == 4) {
+                                v[u][c][0] = __uint_as_float(q.x); v[u][c][1] = __uint_as_float(q.y);
+                                v[u][c][2] = __uint_as_float(q.z); v[u][c][3] = __uint_as_float(q.w);
+                            } else {
+                                const uint32_t ww[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    v[u][c][2 * i] = __uint_as_float(ww[i] << 16);
+                                    v[u][c][2 * i + 1] = __uint_as_float(ww[i] & 0xFFFF0000u);
+                                }
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (wt[u] != 0.0f) {
+#pragma unroll
+                        for (int c = 0; c < CHUNKS; ++c)
+#pragma unroll
+                            for (int k = 0; k < E; ++k) acc[c][k] = fmaf(wt[u], v[u][c][k], acc[c][k]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < CHUNKS; ++c) Vec16<T>::store_streaming(out + c * 32 * E, acc[c]);
+        }
+    }
+}
+
 // Generic width fallback (F not a multiple of 32*16 bytes): lanes stride over columns.
 template <typename T, bool kTransposed, bool kAccumulate>
 __global__ void __launch_bounds__(256)
@@ -114,6 +208,12 @@ spmm_rows_generic_kernel(const int32_t* __restrict__ ptr, const int32_t* __restr
     }
 }
 
+// grl_spmm_set_tile_mode: 0 auto, -1 node-per-warp gather kernel only, -2 legacy row-per-warp kernel,
+// 8/16/32 shared-memory slab kernel with that many lanes per node group
+int g_spmm_mode = 0;
+int try_launch_spmm_tile(const int32_t* rowptr, const int32_t* col, const float* w, const void* X, int64_t ldx, void* Y,
+                         int64_t ldy, int dtype, int B, int N, int L, int F, cudaStream_t st);   // spmm_tile.cu
+
 template <typename T, bool kTransposed>
 static int launch_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* widx, const float* w, const void* Xv,
                        int64_t ldx, void* Yv, int64_t ldy, int64_t n_rows, int rows_per_graph, int cols_per_graph, int F,
@@ -133,6 +233,25 @@ static int launch_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* wi
 #define GRL_SPMM_CASE(C, ACC)                                                                             \
     spmm_rows_kernel<T, C, kTransposed, ACC><<<grid, 256, 0, st>>>(ptr, idx, widx, w, X, ldx, Y, ldy, n_rows, \
                                                                   rows_per_graph, cols_per_graph)
+    if (vec_ok && !kTransposed && !accumulate && g_spmm_mode != -2 && rows_per_graph / cols_per_graph < 32 &&
+        static_cast<uint64_t>(n_rows / (rows_per_graph / cols_per_graph)) * static_cast<uint64_t>(ldx) * sizeof(T) / 16 <
+            (1ull << 32)) {
+        const int Lp1 = rows_per_graph / cols_per_graph;
+        const int64_t n_nodes = n_rows / Lp1;
+        int64_t nb = (n_nodes + 7) / 8;
+        if (nb > cap) nb = cap;
+        if (nb < 1) nb = 1;
+        const uint32_t ldx16 = static_cast<uint32_t>(ldx * sizeof(T) / 16);
+        const int chunks = F / chunk;
+#define GRL_NODE_CASE(C) \
+    spmm_nodes_kernel<T, C><<<static_cast<int>(nb), 256, 0, st>>>(ptr, idx, w, X, ldx16, Y, ldy, n_nodes, cols_per_graph, Lp1)
+        if (chunks == 1) GRL_NODE_CASE(1);
+        else if (chunks == 2) GRL_NODE_CASE(2);
+        else GRL_NODE_CASE(4);
+#undef GRL_NODE_CASE
+        GRL_LAUNCH_CHECK("spmm_nodes_kernel");
+        return 0;
+    }
     if (vec_ok) {
         const int chunks = F / chunk;
         if (accumulate) {
@@ -198,6 +317,15 @@ extern "C" int grl_dropedge_weights(const float* val, const uint8_t* mask, int64
     return 0;
 }
 
+extern "C" int grl_spmm_set_tile_mode(int mode) {
+    if (mode != 0 && mode != -1 && mode != -2 && mode != 8 && mode != 16 && mode != 32) {
+        set_error("grl_spmm_set_tile_mode: mode %d not in {0 auto, -1 gather, -2 legacy rows, 8, 16, 32}", mode);
+        return GRL_E_BADARG;
+    }
+    g_spmm_mode = mode;
+    return 0;
+}
+
 extern "C" int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w, const void* X, int64_t ldx,
                             void* Y, int64_t ldy, int dtype, int B, int N, int L, int F, void* stream) {
     GRL_CHECK_ARG(rowptr && col && w && X && Y, GRL_E_BADARG, "grl_spmm_fwd: null pointer");
@@ -205,6 +333,10 @@ extern "C" int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const flo
     GRL_CHECK_ARG(ldx >= F && ldy >= F, GRL_E_BADARG, "grl_spmm_fwd: leading dimension < F");
     const int64_t R = static_cast<int64_t>(B) * N * (L + 1);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (g_spmm_mode >= 0 && (dtype == GRL_F32 || dtype == GRL_BF16)) {
+        const int rc = try_launch_spmm_tile(rowptr, col, w, X, ldx, Y, ldy, dtype, B, N, L, F, st);
+        if (rc != 1) return rc;       // launched (0) or failed; 1 = slab does not fit -> gather kernel
+    }
     if (dtype == GRL_F32)
         return launch_spmm<float, false>(rowptr, col, nullptr, w, X, ldx, Y, ldy, R, N * (L + 1), N, F, false, st);
     if (dtype == GRL_BF16)

@@ -118,8 +118,9 @@ int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
                  int B, int N, int L, int F, void* stream);
 
 /* Kernel selection knob of grl_spmm_fwd (host call, process-global; experiments and tests):
- *   0 = auto (shared-memory slab kernel when one graph's [N, chunk] feature slab fits, else the L2 gather kernel),
- *  -1 = always the gather kernel,  4 / 8 / 16 = slab kernel with that many bytes per lane (falls back if it does not fit). */
+ *   0 = auto,  -1 = node-per-warp gather kernel,  -2 = legacy row-per-warp gather kernel,
+ *   8 / 16 / 32 = shared-memory slab kernel with that many lanes (of 16 bytes) per node group (falls back to the
+ *   gather kernel when one graph's slab does not fit in shared memory). */
 int grl_spmm_set_tile_mode(int mode);
 
 /* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.

@@ -9,5 +9,8 @@ from .graph import PackedGraphBatch  # noqa: F401
 from .networks import (BaseNetwork, GraphCNNDropEdge, GraphConv, NodeSelfAtten, RanPACLayer,  # noqa: F401
                        make_linear_relu)
 
-__all__ = ["GraphCNNDropEdge", "GraphConv", "NodeSelfAtten", "RanPACLayer", "make_linear_relu", "BaseNetwork",
+from .cl_warper import GNNLearningWarper  # noqa: F401,E402
+from .collate import EdgeListCollate, NumpyPadding  # noqa: F401,E402
+
+__all__ = ["GNNLearningWarper", "NumpyPadding", "EdgeListCollate", "GraphCNNDropEdge", "GraphConv", "NodeSelfAtten", "RanPACLayer", "make_linear_relu", "BaseNetwork",
            "PackedGraphBatch", "GrlError", "LIB_PATH"]

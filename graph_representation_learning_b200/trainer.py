@@ -62,20 +62,34 @@ class FlatGradBucket:
 
 class KVTrainStep:
     def __init__(self, model: nn.Module, max_grad_norm: float = 5.0, optimizer_type: str = "Adam",
-                 optimizer_kwargs: Optional[Dict[str, Any]] = None, device: Optional[torch.device] = None):
+                 optimizer_kwargs: Optional[Dict[str, Any]] = None, device: Optional[torch.device] = None,
+                 criterion: Optional[nn.Module] = None, optimizer_factory=None):
+        """``optimizer_factory(params) -> torch.optim.Optimizer`` (e.g. ``BuitlinOptimizer.get_optimizer``) overrides
+        ``optimizer_type`` / ``optimizer_kwargs``; ``criterion(pred, target)`` defaults to the CE of the KV task."""
         self.model = model
         self.device = device or next(model.parameters()).device
-        self.criterion = CrossEntropyLoss()
+        self.criterion = criterion if criterion is not None else CrossEntropyLoss()
+        if isinstance(self.criterion, nn.Module):
+            self.criterion = self.criterion.to(self.device)
         self.max_grad_norm = max_grad_norm
         self.bucket = FlatGradBucket(model)
-        kwargs = dict(optimizer_kwargs or {})
-        kwargs.pop("lr", None)  # the reference never forwards lr (builtin_optimizer.py:10,18-23)
-        if optimizer_type == "Adam" and self.device.type == "cuda":
-            kwargs.setdefault("fused", True)
-        self.optimizer = getattr(torch.optim, optimizer_type)(self.bucket.params, **kwargs)
+        if optimizer_factory is not None:
+            self.optimizer = optimizer_factory(self.bucket.params)
+        else:
+            kwargs = dict(optimizer_kwargs or {})
+            kwargs.pop("lr", None)  # the reference never forwards lr (builtin_optimizer.py:10,18-23)
+            if optimizer_type == "Adam" and self.device.type == "cuda":
+                kwargs.setdefault("fused", True)
+            self.optimizer = getattr(torch.optim, optimizer_type)(self.bucket.params, **kwargs)
 
     def _to_device(self, batch_sample: Dict[str, torch.Tensor]) -> Tuple[list, torch.Tensor]:
-        V = batch_sample["textline_encoding"].to(self.device, non_blocking=True)
+        if "adjacency_matrix" not in batch_sample and "edges" in batch_sample:      # EdgeListCollate host batch
+            from .collate import EdgeListCollate
+            batch_sample = EdgeListCollate.to_device(batch_sample, self.device)
+        V = batch_sample["textline_encoding"]
+        if not V.is_floating_point():
+            V = V.float()                               # kv_procedure.py:117 (.float() of whatever the dataset gave)
+        V = V.to(self.device, non_blocking=True)
         A = batch_sample["adjacency_matrix"]
         if isinstance(A, torch.Tensor):
             A = A.to(self.device, non_blocking=True)   # fp16 stays fp16: the CSR pack reads it directly
@@ -104,3 +118,104 @@ class KVTrainStep:
         self.model.eval()
         loss, pred = self.step_process(batch_sample)
         return loss, pred.argmax(dim=-1)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# getattr-by-name factories of the reference trainer (losses / optimizers / lr_schedulers), restated
+# ----------------------------------------------------------------------------------------------------------
+class BuitlinOptimizer:
+    """gnn/trainer/optimizers/builtin_optimizer.py:8-26 (the class name is the reference's spelling).  ``lr`` is kept
+    on the object and NOT forwarded to torch.optim, exactly like the reference: Adam starts at its default 1e-3 and
+    the scheduler overwrites ``param_groups[*]["lr"]`` at the end of each epoch."""
+
+    def __init__(self, type_optimizer: str, lr: float, **kwargs: Any):
+        self.learning_rate = lr
+        self.type_optimizer = type_optimizer
+        self.optimizer_args = kwargs
+
+    @classmethod
+    def _from_config(cls, opt: Dict[str, Any]) -> "BuitlinOptimizer":
+        return cls(**opt)
+
+    def get_optimizer(self, parameters) -> torch.optim.Optimizer:
+        optimizer = getattr(torch.optim, self.type_optimizer)(parameters, **self.optimizer_args)
+        if hasattr(self.learning_rate, "prepare"):
+            self.learning_rate.prepare(optimizer)
+        return optimizer
+
+
+class DecayLearningRate:
+    """gnn/trainer/lr_schedulers/decay_lr.py:6-25: lr * (1 - epoch / (num_epochs + 1)) ** factor, set per epoch."""
+
+    def __init__(self, lr: float = 0.002, factor: float = 0.9, num_epochs: int = 100):
+        self.lr = lr
+        self.initial_lr = lr
+        self.factor = factor
+        self.epochs = num_epochs
+
+    @classmethod
+    def _from_config(cls, config: Dict[str, Any]) -> "DecayLearningRate":
+        return cls(**config)
+
+    def _step_lr(self, epoch: int, step: Optional[int] = None) -> float:
+        rate = (1.0 - epoch / float(self.epochs + 1)) ** self.factor
+        self.lr = self.initial_lr * rate
+        return self.lr
+
+
+LOSSES = {"CrossEntropyLoss": CrossEntropyLoss}
+OPTIMIZERS = {"BuitlinOptimizer": BuitlinOptimizer}
+LR_SCHEDULERS = {"DecayLearningRate": DecayLearningRate}
+
+
+def from_registry(registry: Dict[str, Any], kind: str, type_name: Optional[str], args: Optional[Dict[str, Any]]):
+    """``getattr(<package>, cfg.type)._from_config(cfg.args)`` of base_procedure.py:95-140; None type -> None"""
+    if not type_name:
+        return None
+    if type_name not in registry:
+        raise ValueError(f"unknown {kind} {type_name!r}; available: {sorted(registry)}")
+    cls = registry[type_name]
+    args = dict(args or {})
+    return cls._from_config(args) if hasattr(cls, "_from_config") else cls(**args)
+
+
+class Dictlist(dict):
+    """gnn/utils/metric_tracker.py:6-29: running lists per key, averages rounded to 3 decimals."""
+
+    def _update(self, dict_item: Dict[str, Any]) -> None:
+        for key, value in dict_item.items():
+            self.setdefault(key, []).append(value)
+
+    def _avg(self, key: str) -> float:
+        vals = self[key]
+        return round(sum(vals) / len(vals), 3)
+
+    def _result(self) -> Dict[str, Any]:
+        return {key: self._avg(key) for key in self.keys()}
+
+
+def macro_scores(pred: torch.Tensor, target: torch.Tensor, ignore: Tuple[Any, ...] = (-100,),
+                 item_name: str = "Node classification") -> Dict[str, float]:
+    """Macro precision / recall / F1 / support of ``classification_report(..., zero_division=0)["macro avg"]`` as
+    KVProcedure._get_metric_scores computes it (kv_procedure.py:61-104): entries whose label is in ``ignore`` are
+    dropped, the average runs over the classes present in labels OR predictions.  One confusion matrix on the device
+    and a single small D2H copy instead of sklearn over host lists."""
+    pred, target = pred.reshape(-1), target.reshape(-1)
+    keep = torch.ones_like(target, dtype=torch.bool)
+    for v in ignore:
+        if v is not None:
+            keep &= target != v
+    pred, target = pred[keep], target[keep]
+    names = ("precision", "recall", "f1-score", "support")
+    if target.numel() == 0:
+        return {f"{item_name}_{k}": 0.0 for k in names}
+    C = int(max(int(pred.max()), int(target.max()))) + 1
+    cm = torch.bincount(target * C + pred, minlength=C * C).view(C, C).double()
+    tp, n_true, n_pred = cm.diagonal(), cm.sum(1), cm.sum(0)
+    present = (n_true + n_pred) > 0
+    prec = torch.where(n_pred > 0, tp / n_pred.clamp_min(1), torch.zeros_like(tp))
+    rec = torch.where(n_true > 0, tp / n_true.clamp_min(1), torch.zeros_like(tp))
+    f1 = torch.where((prec + rec) > 0, 2 * prec * rec / (prec + rec).clamp_min(1e-300), torch.zeros_like(tp))
+    k = present.sum().clamp_min(1)
+    vals = torch.stack([prec[present].sum() / k, rec[present].sum() / k, f1[present].sum() / k, n_true.sum()]).tolist()
+    return {f"{item_name}_{n}": float(v) for n, v in zip(names, vals)}

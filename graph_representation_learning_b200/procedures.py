@@ -255,7 +255,7 @@ class KVProcedure(BaseProcedure):
         if want_metrics:
             y = batch_sample["node_label"].to(self.device, non_blocking=True)
             scores = self._get_metric_scores(pred.argmax(dim=-1), y, item_name="Node classification")
-            scores["loss"] = float(loss)
+            scores["loss"] = float(loss.detach())
         return loss, scores
 
     def _run_train_step(self, batch_sample) -> Dict[str, Any]:
@@ -276,7 +276,7 @@ class KVProcedure(BaseProcedure):
         loss, pred = self.step.step_process(batch_sample)
         y = batch_sample["node_label"].to(self.device)
         scores = self._get_metric_scores(pred.argmax(dim=-1), y, item_name="Node classification")
-        scores["loss"] = float(loss)
+        scores["loss"] = float(loss.detach())
         return scores, pred.argmax(dim=-1).reshape(-1), y.reshape(-1)
 
     def cosine_schedule_lambda(self, step: int, epoch: int, total_steps: int, base_value: float, max_value: float,

@@ -1,0 +1,114 @@
+"""GPU tests of the callers around the kernels: collate -> device CSR, KVProcedure / GNNLearningWarper train,
+KVInference predict -- all through the CUDA model (C-ABI kernels)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from _golden import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+REFERENCE_KEYS = {"emb1.0.weight", "emb1.0.bias", "gcn1.h_weights", "gcn1.bias", "gcn2.h_weights", "gcn2.bias",
+                  "gcn3.h_weights", "gcn3.bias", "emb2.0.weight", "emb2.0.bias", "self_atten.gamma",
+                  "self_atten.f.0.weight", "self_atten.f.0.bias", "self_atten.g.0.weight", "self_atten.g.0.bias",
+                  "self_atten.h.0.weight", "self_atten.h.0.bias", "w_rand.projection.weight", "classifier.weight",
+                  "classifier.bias"}
+
+
+def _samples(seed=3, sizes=(17, 30, 22, 30, 9, 26), D=24, C=5):
+    rng = np.random.default_rng(seed)
+    out = []
+    for n in sizes:
+        A = (rng.random((n, 6, n)) < 0.15).astype(np.float16)
+        out.append({"textline_encoding": rng.random((n, D), dtype=np.float32), "adjacency_matrix": A,
+                    "node_label": rng.integers(0, C, n).astype(np.int64)})
+    return out
+
+
+def test_edge_list_collate_packs_the_same_graph_as_the_dense_collate():
+    from graph_representation_learning_b200 import GraphCNNDropEdge, PackedGraphBatch
+    from graph_representation_learning_b200 import collate as C
+    dev = torch.device("cuda:0")
+    samples = _samples()
+    dense = C.load_collate_processors({"NumpyPadding": {"name_value_pairs": {
+        "textline_encoding": 0.0, "adjacency_matrix": 0.0, "node_label": -100.0}, "only_selected_items": True}})(
+        [dict(s) for s in samples])
+    host = C.EdgeListCollate(num_edges=6)([dict(s) for s in samples])
+    packed = C.EdgeListCollate.to_device(host, dev)
+    g_edge, g_dense = packed["adjacency_matrix"], PackedGraphBatch.from_dense(dense["adjacency_matrix"].to(dev))
+    for name in ("rowptr", "col", "val", "colptr", "rowidx", "perm"):
+        assert torch.equal(getattr(g_edge, name), getattr(g_dense, name)), name            # integer work: bit-exact
+    assert torch.equal(packed["node_label"].cpu(), dense["node_label"])
+    assert torch.equal(packed["textline_encoding"].cpu(), dense["textline_encoding"])
+    assert packed["textline_encoding"].stride(1) % 4 == 0                                  # pitch kept through H2D
+    torch.manual_seed(0)
+    model = GraphCNNDropEdge(24, 5, 6, net_size=64).to(dev).eval()
+    with torch.no_grad():
+        a = model([packed["textline_encoding"], g_edge])
+        b = model([dense["textline_encoding"].to(dev), dense["adjacency_matrix"].to(dev)])
+    assert torch.equal(a, b)
+
+
+def _cfg(tmp_path, **over):
+    data = {"num_documents": 24, "n_min": 20, "n_max": 40, "input_dim": 48, "num_classes": 6, "batch_size": 8,
+            "shuffle": False, "drop_last": True, "pin_memory": True,
+            "data_collate": {"NumpyPadding": {"name_value_pairs": {"textline_encoding": 0.0, "adjacency_matrix": 0.0,
+                                                                   "node_label": -100.0}, "only_selected_items": True}}}
+    cfg = {"output_dir": str(tmp_path), "num_gpus": 1, "num_epochs": 3, "seed": 5,
+           "data_config": {"dataset": {"type": "SyntheticDocumentDataset", "args": {"node_label_padding_value": -100,
+                                                                                    "other_class_index": None}},
+                           "training": dict(data, seed=1), "validation": dict(data, seed=2, batch_size=4)}}
+    cfg.update(over)
+    return cfg
+
+
+def test_warper_trains_the_cuda_model_and_writes_a_reference_compatible_checkpoint(tmp_path):
+    from graph_representation_learning_b200 import GNNLearningWarper, GraphCNNDropEdge, _lib
+    torch.manual_seed(1)
+    model = GraphCNNDropEdge(48, 6, 6, net_size=64)
+    w = GNNLearningWarper(model, config=_cfg(tmp_path))
+    n0 = _lib.launches()
+    first = w.trainer._optimize_per_epoch(0)["loss"]
+    f1 = w.train()
+    assert _lib.launches() - n0 > 100                     # our kernels ran, not a fallback
+    assert 0.0 <= f1 <= 1.0
+    ckpt = torch.load(os.path.join(str(tmp_path), "GNN-B200", "models", "model_latest.pt"), weights_only=False)
+    assert set(ckpt) == {"epoch", "config", "meta_data", "state_dict"}
+    assert set(ckpt["state_dict"]) == REFERENCE_KEYS      # loadable by the reference's load_state_dict(strict=False)
+    assert ckpt["meta_data"]["loss"] <= first + 1e-3      # saved only when the validation loss improved
+    assert w.trainer.global_step == 4 * 3 and next(model.parameters()).is_cuda
+
+
+def test_kv_inference_batched_equals_per_document_on_the_cuda_model(tmp_path):
+    from graph_representation_learning_b200 import GNNLearningWarper, GraphCNNDropEdge
+    feats = {}
+
+    def featurizer(doc):
+        key = id(doc)
+        n = len(doc)
+        r = np.random.default_rng(n * 7 + int(doc[0]["text"][1:]))
+        f = {"textline_encoding": r.random((n, 24), dtype=np.float32)}
+        A = (r.random((n, 6, n)) < 0.2).astype(np.float16)
+        if n % 2:
+            f["adjacency_matrix"] = A
+        else:
+            s, l, e = np.nonzero(A)
+            f["edges"] = np.stack([s, l, e], 1).astype(np.int32)
+        feats[key] = f
+        return f
+
+    docs = [[{"text": f"t{k}", "location": [[0, 0]] * 4} for _ in range(n)] for k, n in enumerate((12, 15, 12, 15, 15, 8))]
+    torch.manual_seed(2)
+    model = GraphCNNDropEdge(24, 5, 6, net_size=64)
+    cfg = _cfg(tmp_path, is_train=False, procedure={"type": "KVInference", "args": {}})
+    ids = {i: (f"field{i}", "key" if i % 2 else "value") for i in range(1, 5)}
+    batched = GNNLearningWarper(model, config=cfg, featurizer=featurizer, id_to_class=ids).predict(docs)
+    single = GNNLearningWarper(model, config=cfg, featurizer=featurizer, id_to_class=ids, max_batch_documents=1).predict(
+        [[dict(b) for b in d] for d in docs])
+    for a, b in zip(batched, single):
+        assert len(a) == len(b)
+        for x, y in zip(a, b):
+            assert x["formal_key"] == y["formal_key"] and x["key_type"] == y["key_type"]
+            assert abs(x["confidence"] - y["confidence"]) < 1e-5

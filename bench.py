@@ -205,13 +205,39 @@ def run_b200(args):
         host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in batch_dev.items()}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
 
-        def e2e_step():
-            loss = step.run_train_step(host)
-            return float(loss)                               # D2H read of the step's result (4 bytes)
+        from graph_representation_learning_b200.trainer import DevicePrefetcher
+        pinned_loss = torch.zeros(64, dtype=torch.float32).pin_memory()
+
+        def e2e_run(steps, warmup):
+            """the public step API over a host loader: H2D of every step's inputs (pinned -> device, one batch ahead on
+            a copy stream) and a D2H read of every step's loss, all inside the timed region"""
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            seen = []
+            for i, dev_batch in enumerate(DevicePrefetcher((host for _ in range(warmup + steps)), dev)):
+                if i == warmup:
+                    e0.record()
+                loss = step.run_train_step(dev_batch)
+                pinned_loss[i % 64].copy_(loss, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                if seen:                                   # read the previous step's loss on the host
+                    pev, pi = seen[-1]
+                    pev.synchronize()
+                    float(pinned_loss[pi % 64])
+                seen.append((ev, i))
+            e1.record()
+            barrier()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t) / steps
         e_steps = max(3, min(args.steps, 10))
-        ms_e2e, _, _ = timed(e2e_step, e_steps, 2)
+        ms_e2e = e2e_run(e_steps, 2)
         e2e = {"value": world * B / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-               "ms_per_step": ms_e2e, "steps": e_steps}
+               "ms_per_step": ms_e2e, "steps": e_steps,
+               "how": "KVTrainStep.run_train_step over DevicePrefetcher(host loader): pinned host V/A/y -> device one "
+                      "batch ahead on a copy stream, dense fp16 adjacency packed to CSR on the device, loss read back"}
 
     # (3) roofline of the aggregation kernel (gcn1 SpMM, DropEdge weights applied), timed alone with CUDA events
     pk = peaks()

@@ -219,3 +219,63 @@ def macro_scores(pred: torch.Tensor, target: torch.Tensor, ignore: Tuple[Any, ..
     k = present.sum().clamp_min(1)
     vals = torch.stack([prec[present].sum() / k, rec[present].sum() / k, f1[present].sum() / k, n_true.sum()]).tolist()
     return {f"{item_name}_{n}": float(v) for n, v in zip(names, vals)}
+
+
+class DevicePrefetcher:
+    """Iterates a host loader one batch ahead: batch i+1 is copied host -> device (from pinned memory, on a side
+    stream) and, for ``EdgeListCollate`` batches, packed into CSR/CSC there while the main stream runs step i.
+    Yields device batches in the dict format ``KVTrainStep`` takes.  The reference moves every batch synchronously
+    inside the step (kv_procedure.py:116-123); this is the same copy, overlapped."""
+
+    def __init__(self, loader, device: torch.device):
+        self.loader = loader
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+
+    def _load(self, batch):
+        with torch.cuda.stream(self.stream):
+            if "adjacency_matrix" not in batch and "edges" in batch:
+                from .collate import EdgeListCollate
+                out = EdgeListCollate.to_device(batch, self.device)
+            else:
+                out = {}
+                for k, v in batch.items():
+                    if isinstance(v, torch.Tensor):
+                        if k == "textline_encoding":
+                            if not v.is_floating_point():
+                                v = v.float()
+                            # land the features with a 16-byte row pitch (TMA reads them in place); the re-lay of an
+                            # unaligned width (4369) happens here, on the copy stream, not inside the step
+                            D, m = v.shape[-1], 16 // v.element_size()
+                            if D % m:
+                                buf = torch.empty(*v.shape[:-1], (D + m - 1) // m * m, dtype=v.dtype, device=self.device)
+                                buf[..., :D].copy_(v, non_blocking=True)
+                                out[k] = buf[..., :D]
+                                continue
+                        out[k] = v.to(self.device, non_blocking=True)
+                    else:
+                        out[k] = v
+        return out
+
+    def __iter__(self):
+        main = torch.cuda.current_stream(self.device)
+        it = iter(self.loader)
+        try:
+            nxt = self._load(next(it))
+        except StopIteration:
+            return
+        while nxt is not None:
+            main.wait_stream(self.stream)                 # batch i is on the device
+            cur = nxt
+            for v in cur.values():                        # allocated on the side stream, consumed on the main one
+                if isinstance(v, torch.Tensor):
+                    v.record_stream(main)
+                elif hasattr(v, "rowptr"):
+                    for t in (v.rowptr, v.col, v.val, v.colptr, v.rowidx, v.perm):
+                        if t is not None:
+                            t.record_stream(main)
+            try:
+                nxt = self._load(next(it))                # enqueue the copy of batch i+1 before step i is launched
+            except StopIteration:
+                nxt = None
+            yield cur

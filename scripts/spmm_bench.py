@@ -56,7 +56,22 @@ def main():
         ms = e0.elapsed_time(e1) / args.iters
         out[mode] = {"ms": round(ms, 4), "GBps": round(alg / ms / 1e6, 1), "max_abs_diff_vs_first": err}
     lib.grl_spmm_set_tile_mode(0)
-    print(json.dumps({"shape": vars(args), "nnz": g.nnz, "alg_bytes": alg, "fwd": out}))
+    # transposed (gradient) kernel: dX = A'^T dY over CSC + perm
+    dY = torch.randn(g.num_rows, args.F, device=dev, dtype=dt)
+    dX = torch.empty(g.num_nodes, args.F, device=dev, dtype=dt)
+    for _ in range(3):
+        ops.spmm_bwd_(g, w, dY, dX)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.iters):
+        ops.spmm_bwd_(g, w, dY, dX)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.iters
+    alg_bwd = 4 * (g.num_nodes + 1) + 12 * g.nnz + dY.numel() * es + dX.numel() * es
+    bwd = {"ms": round(ms, 4), "GBps": round(alg_bwd / ms / 1e6, 1), "alg_bytes": alg_bwd}
+    print(json.dumps({"shape": vars(args), "nnz": g.nnz, "alg_bytes": alg, "fwd": out, "bwd": bwd}))
 
 
 if __name__ == "__main__":

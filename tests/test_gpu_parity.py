@@ -120,26 +120,28 @@ def test_spmm_fwd_bwd_against_dense_matmul(dev, F, dtype):
                                            (2, 513, 256, 0.02)])
 def test_spmm_forward_kernels_agree_bit_for_bit(dev, dtype, B, N, F, density):
     """gather (node-per-warp), legacy (row-per-warp) and the TMA-staged shared-memory slab kernels sum every typed row
-    in CSR order, so they must agree exactly -- including rows longer than the register-staged 2*GL / 64 entries
+    in CSR order (dropped entries skipped), so they must agree exactly -- including nodes with more entries than one
+    staged batch (density 0.6: the slab-v2 multi-batch path), rows longer than the register-staged 2*GL / 64 entries
     (density 0.6), empty typed rows (density 0), and N that is not a multiple of the TMA box."""
     from graph_representation_learning_b200 import PackedGraphBatch, _lib, ops
     gen = torch.Generator().manual_seed(N * 7 + F)
     A = (torch.rand(B, N, 6, N, generator=gen) < density).half()
     g = PackedGraphBatch.from_dense(A.to(dev))
-    w = g.edge_weights(0.3, seed=5, stream_id=3)
     X = torch.randn(B * N, F, generator=gen).to(dev, dtype)
     lib = _lib.load()
-    outs = {}
-    try:
-        for mode in (-2, -1, 8, 16, 32, 0):
-            _lib.check(lib.grl_spmm_set_tile_mode(mode), "grl_spmm_set_tile_mode")
-            Y = torch.full((g.num_rows, F), float("nan"), device=dev, dtype=dtype)
-            ops.spmm_fwd_(g, w, X, Y)
-            outs[mode] = Y
-    finally:
-        lib.grl_spmm_set_tile_mode(0)
-    for mode, Y in outs.items():
-        assert torch.equal(Y, outs[-2]), f"mode {mode} differs from the row kernel"
+    for p_drop in (0.3, 0.9, 0.0):          # 0.9: typed rows whose entries are ALL dropped must still be written as zeros
+        w = g.edge_weights(p_drop, seed=5, stream_id=3)
+        outs = {}
+        try:
+            for mode in (-2, -1, 8, 16, 32, 108, 116, 132, 0):
+                _lib.check(lib.grl_spmm_set_tile_mode(mode), "grl_spmm_set_tile_mode")
+                Y = torch.full((g.num_rows, F), float("nan"), device=dev, dtype=dtype)
+                ops.spmm_fwd_(g, w, X, Y)
+                outs[mode] = Y
+        finally:
+            lib.grl_spmm_set_tile_mode(0)
+        for mode, Y in outs.items():
+            assert torch.equal(Y, outs[-2]), f"mode {mode} differs from the row kernel (p_drop={p_drop})"
     assert lib.grl_spmm_set_tile_mode(5) == -1
 
 

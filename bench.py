@@ -250,15 +250,22 @@ def run_b200(args):
     es = X.element_size()
     alg_bytes = 4 * (g.num_rows + 1) + 8 * g.nnz + X.numel() * es + Y.numel() * es   # SURVEY 8d bytes_compulsory (+w)
     achieved = alg_bytes / (ms_spmm * 1e-3) / 1e9
-    roofline = {"kernel": "spmm_rows_kernel (gcn1 aggregation, fwd)", "bound": "hbm", "achieved": achieved,
-                "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None,
+    traffic, traffic_bwd = None, None               # ncu dram__bytes_read+write per launch (profiles/, cfg2 shape only)
+    tpath = os.path.join(ROOT, "profiles", "spmm_traffic.json")
+    if wl.name.startswith("cfg2") and B == wl.B and os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        traffic, traffic_bwd = tj["fwd"]["dram_bytes_per_launch"], tj["bwd"]["dram_bytes_per_launch"]
+    roofline = {"kernel": "spmm_slab2_kernel (gcn1 aggregation fwd over the DropEdge node streams)", "bound": "hbm",
+                "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+                "traffic": traffic,
                 "peak_source": pk["source"], "ms_per_launch": ms_spmm, "algorithmic_bytes": alg_bytes}
     dYt = torch.randn(g.num_rows, S, device=dev, dtype=wl.dtype)
     dX = torch.empty(B * wl.N, S, device=dev, dtype=wl.dtype)
     ms_bwd, _, _ = timed(lambda: ops.spmm_bwd_(g, w, dYt, dX), 20, 5)
     alg_bwd = 4 * (g.num_nodes + 1) + 12 * g.nnz + dYt.numel() * es + dX.numel() * es
     roofline["bwd"] = {"kernel": "spmm_rows_kernel<transposed>", "achieved": alg_bwd / (ms_bwd * 1e-3) / 1e9,
-                       "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"], "ms_per_launch": ms_bwd}
+                       "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"], "ms_per_launch": ms_bwd,
+                       "algorithmic_bytes": alg_bwd, "traffic": traffic_bwd}
     del X, Y, dYt, dX
 
     # (4) CPU baseline: the oracle port on a bounded sample of the same workload (rank 0, N=1 only)

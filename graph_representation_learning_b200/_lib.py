@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libgrl_b200.so")
 
 GRL_F32, GRL_BF16, GRL_F16 = 0, 1, 2
 EPI_BIAS, EPI_RELU, EPI_DROPOUT = 1, 2, 4
+GRL_E_BADARG, GRL_E_ALIGN, GRL_E_UNSUP, GRL_E_WORKSPACE = -1, -2, -3, -4
 
 _DTYPES = {torch.float32: GRL_F32, torch.bfloat16: GRL_BF16, torch.float16: GRL_F16}
 
@@ -40,6 +41,10 @@ SIGNATURES = {
     "grl_csr_transpose": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),
     "grl_dropedge_weights": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_uint64, c_uint64, c_void_p, c_void_p]),
+    "grl_dropedge_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_uint64,
+                                    c_void_p, c_void_p, c_void_p, c_void_p]),
+    "grl_spmm_fwd_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,
+                                    c_int, c_int, c_void_p]),
     "grl_spmm_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,
                              c_int, c_int, c_void_p]),
     "grl_spmm_set_tile_mode": (c_int, [c_int]),

@@ -213,8 +213,7 @@ spmm_rows_generic_kernel(const int32_t* __restrict__ ptr, const int32_t* __restr
 int g_spmm_mode = 0;
 int try_launch_spmm_tile(const int32_t* rowptr, const int32_t* col, const float* w, const void* X, int64_t ldx, void* Y,
                          int64_t ldy, int dtype, int B, int N, int L, int F, cudaStream_t st);   // spmm_tile.cu
-int try_launch_spmm_slab2(const int32_t* rowptr, const int32_t* col, const float* w, const void* X, int64_t ldx, void* Y,
-                          int64_t ldy, int dtype, int B, int N, int L, int F, int gl_req, cudaStream_t st);  // spmm_slab2.cu
+extern int g_slab2_gl;    // spmm_slab2.cu
 
 template <typename T, bool kTransposed>
 static int launch_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* widx, const float* w, const void* Xv,
@@ -326,7 +325,8 @@ extern "C" int grl_spmm_set_tile_mode(int mode) {
                   "108/116/132 slab v2}", mode);
         return GRL_E_BADARG;
     }
-    g_spmm_mode = mode;
+    g_spmm_mode = mode > 100 ? 0 : mode;             // 108/116/132 only steer grl_spmm_fwd_stream
+    g_slab2_gl = mode > 100 ? mode - 100 : 0;
     return 0;
 }
 
@@ -338,12 +338,7 @@ extern "C" int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const flo
     const int64_t R = static_cast<int64_t>(B) * N * (L + 1);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (g_spmm_mode >= 0 && (dtype == GRL_F32 || dtype == GRL_BF16)) {
-        int rc = 1;
-        if (g_spmm_mode == 0 || g_spmm_mode > 100)       // slab v2 (spmm_slab2.cu): auto or forced group width
-            rc = try_launch_spmm_slab2(rowptr, col, w, X, ldx, Y, ldy, dtype, B, N, L, F,
-                                       g_spmm_mode > 100 ? g_spmm_mode - 100 : 0, st);
-        else                                             // 8 / 16 / 32: first-generation slab kernel (spmm_tile.cu)
-            rc = try_launch_spmm_tile(rowptr, col, w, X, ldx, Y, ldy, dtype, B, N, L, F, st);
+        const int rc = try_launch_spmm_tile(rowptr, col, w, X, ldx, Y, ldy, dtype, B, N, L, F, st);
         if (rc != 1) return rc;       // launched (0) or failed; 1 = slab does not fit -> gather kernel
     }
     if (dtype == GRL_F32)

@@ -33,6 +33,7 @@ class PackedGraphBatch:
     colptr: Optional[torch.Tensor] = None   # int32 [B*N+1]
     rowidx: Optional[torch.Tensor] = None   # int32 [nnz]   global CSR row of each CSC entry
     perm: Optional[torch.Tensor] = None     # int32 [nnz]   CSR position of each CSC entry
+    _eval_weights: Optional[torch.Tensor] = None   # cached edge_weights(p=0) (val + its node streams)
 
     @property
     def num_nodes(self) -> int:
@@ -147,18 +148,31 @@ class PackedGraphBatch:
         """Per-entry weights of one layer: ``val * keep / (1-p)`` (reference: nn.Dropout(p=0.3) on A',
         gnn/models/networks/drop_robust_gcn.py:38,76,80,85).  ``mask`` (uint8 [nnz], CSR order) injects
         the keep bits for parity tests; otherwise Philox(seed, stream_id, entry)."""
-        if p == 0.0 and mask is None:
-            return self.val
+        if p == 0.0 and mask is None and self._eval_weights is not None:
+            return self._eval_weights
         if mask is not None:
             _lib.require_cuda(mask, "edge mask")
             if mask.dtype != torch.uint8 or mask.numel() != self.nnz:
                 raise _lib.GrlError("edge mask must be uint8 with one entry per stored non-zero")
             mask = mask.contiguous()
         w = torch.empty_like(self.val)
-        _lib.check(_lib.load().grl_dropedge_weights(self.val.data_ptr(), _lib.ptr(mask), self.nnz, float(p),
-                                                    int(seed) & (2**64 - 1), int(stream_id), w.data_ptr(),
-                                                    _lib.stream_ptr(self.device)), "grl_dropedge_weights")
+        if self.L + 1 < 127 and self.N < (1 << 24) - 2:
+            # forward fast path: the same w plus the compacted, row-tagged node streams of csrc/spmm_slab2.cu
+            ew = torch.empty(max(self.nnz, 1), 2, dtype=torch.int32, device=self.device)
+            nodeinfo = torch.empty(self.num_nodes, 2, dtype=torch.int32, device=self.device)
+            _lib.check(_lib.load().grl_dropedge_stream(self.rowptr.data_ptr(), self.col.data_ptr(), self.val.data_ptr(),
+                                                       _lib.ptr(mask), self.num_nodes, self.L, float(p),
+                                                       int(seed) & (2**64 - 1), int(stream_id), w.data_ptr(),
+                                                       ew.data_ptr(), nodeinfo.data_ptr(), _lib.stream_ptr(self.device)),
+                       "grl_dropedge_stream")
+            w._grl_stream = (nodeinfo, ew)       # rides along with the weight tensor (ops.spmm_fwd_ looks for it)
+        else:
+            _lib.check(_lib.load().grl_dropedge_weights(self.val.data_ptr(), _lib.ptr(mask), self.nnz, float(p),
+                                                        int(seed) & (2**64 - 1), int(stream_id), w.data_ptr(),
+                                                        _lib.stream_ptr(self.device)), "grl_dropedge_weights")
         _lib.count_launch(1)
+        if p == 0.0 and mask is None:
+            self._eval_weights = w               # eval: one stream per batch, shared by the three layers
         return w
 
     def to_dense(self, w: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -104,7 +104,7 @@ class GraphConv(nn.Module):
             g = self.preprocess_adj(A)
         else:
             g = PackedGraphBatch.from_dense(A.reshape(B, N, self.L + 1, N), self_loop=False)
-        w = g.val if edge_weights is None else edge_weights
+        w = g.edge_weights(0.0) if edge_weights is None else edge_weights
         out = ops.graph_conv([_flat(V)], g, w, self.h_weights, self.bias)
         return out.view(B, N, self.C)
 

@@ -30,12 +30,26 @@ def _row_major_2d(t: torch.Tensor, name: str) -> int:
     return t.stride(0) if t.shape[0] > 1 else max(t.stride(0), t.shape[1])
 
 
+_spmm_stream_enabled = [True]     # tests / A-B scripts switch the node-stream kernel off to reach the gather kernels
+
+
 def spmm_fwd_(g: PackedGraphBatch, w: torch.Tensor, X: torch.Tensor, Y: torch.Tensor) -> None:
     """Y[r, :F] = sum_e w[e] X[base(r)+col[e], :F];  Y is a [R, F] view (possibly a column slice)."""
     ldx, ldy = _row_major_2d(X, "X"), _row_major_2d(Y, "Y")
     F = X.shape[1]
     if X.shape[0] != g.num_nodes or Y.shape[0] != g.num_rows or Y.shape[1] != F or X.dtype != Y.dtype:
         raise _lib.GrlError(f"spmm_fwd shape mismatch: X {tuple(X.shape)} Y {tuple(Y.shape)} for {g.num_nodes} nodes")
+    stream = getattr(w, "_grl_stream", None)
+    if stream is not None and _spmm_stream_enabled[0]:
+        # node-stream slab kernel (csrc/spmm_slab2.cu); GRL_E_UNSUP = the graph's slab does not fit -> gather kernels
+        nodeinfo, ew = stream
+        rc = _lib.load().grl_spmm_fwd_stream(nodeinfo.data_ptr(), ew.data_ptr(), X.data_ptr(), ldx, Y.data_ptr(), ldy,
+                                             _lib.dtype_code(X), g.B, g.N, g.L, F, _lib.stream_ptr(X.device))
+        if rc == 0:
+            _lib.count_launch(1)
+            return
+        if rc != _lib.GRL_E_UNSUP:
+            _lib.check(rc, "grl_spmm_fwd_stream")
     _lib.check(_lib.load().grl_spmm_fwd(g.rowptr.data_ptr(), g.col.data_ptr(), w.data_ptr(), X.data_ptr(), ldx,
                                         Y.data_ptr(), ldy, _lib.dtype_code(X), g.B, g.N, g.L, F,
                                         _lib.stream_ptr(X.device)), "grl_spmm_fwd")

@@ -105,6 +105,24 @@ int grl_csr_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, i
 int grl_dropedge_weights(const float* val, const uint8_t* mask, int64_t nnz, float p,
                          uint64_t seed, uint64_t stream_id, float* w, void* stream);
 
+/* DropEdge + node-stream pack (the forward fast path; one call per GraphConv layer).  Same keep bits and the same
+ * w[e] as grl_dropedge_weights for the same (mask | seed, stream_id); in addition the KEPT entries of all (L+1) typed
+ * rows of a node are written, in CSR order, as one stream per node:
+ *   ew[start + k] = { (t << 24) | col , bits of w }   k in [0, kept),   nodeinfo[node] = { start = rowptr[node*(L+1)], kept }
+ * t = typed row of the entry (0 = self loop).  ew: uint2 [nnz], nodeinfo: int32 [n_nodes][2], both 8-byte aligned.
+ * Requires L + 1 < 127 and N < 2^24 - 2.  Replaces nn.Dropout(p=0.3) on A'  drop_robust_gcn.py:38,76,80,85. */
+int grl_dropedge_stream(const int32_t* rowptr, const int32_t* col, const float* val, const uint8_t* mask,
+                        int64_t n_nodes, int L, float p, uint64_t seed, uint64_t stream_id,
+                        float* w, void* ew, int32_t* nodeinfo, void* stream);
+
+/* Aggregation over the node streams of grl_dropedge_stream (same result as grl_spmm_fwd, bit for bit):
+ * one CTA stages the [N, chunk] feature slab of a graph in shared memory with TMA (double-buffered when two fit) and
+ * walks the streams of its nodes.  Returns GRL_E_UNSUP when one graph's slab does not fit in shared memory or the
+ * X / Y pitches are not 16-byte multiples -- the caller then uses grl_spmm_fwd.
+ * Replaces torch.matmul(A, V)  gnn/models/networks/robust_gcn.py:45-47. */
+int grl_spmm_fwd_stream(const int32_t* nodeinfo, const void* ew, const void* X, int64_t ldx, void* Y, int64_t ldy,
+                        int dtype, int B, int N, int L, int F, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Segmented SpMM (aggregation).  Replaces torch.matmul(A, V.view(-1,N,F)).view(-1,N,(L+1)F)
  * gnn/models/networks/robust_gcn.py:45-47.
@@ -119,8 +137,9 @@ int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
 
 /* Kernel selection knob of grl_spmm_fwd (host call, process-global; experiments and tests):
  *   0 = auto,  -1 = node-per-warp gather kernel,  -2 = legacy row-per-warp gather kernel,
- *   8 / 16 / 32 = shared-memory slab kernel with that many lanes (of 16 bytes) per node group (falls back to the
- *   gather kernel when one graph's slab does not fit in shared memory). */
+ *   8 / 16 / 32 = first-generation shared-memory slab kernel with that many lanes (of 16 bytes) per node group (falls
+ *   back to the gather kernel when one graph's slab does not fit in shared memory);
+ *   108 / 116 / 132 = force that group width in grl_spmm_fwd_stream (grl_spmm_fwd stays on auto). */
 int grl_spmm_set_tile_mode(int mode);
 
 /* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.

@@ -20,7 +20,7 @@ def main():
     ap.add_argument("--F", type=int, default=256)
     ap.add_argument("--degree", type=float, default=8.0)
     ap.add_argument("--dtype", default="f32")
-    ap.add_argument("--modes", default="-2,-1,8,16,32")
+    ap.add_argument("--modes", default="-2,-1,16,100")
     ap.add_argument("--iters", type=int, default=20)
     args = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -37,7 +37,8 @@ def main():
     ref = None
     out = {}
     for mode in [int(m) for m in args.modes.split(",")]:
-        _lib.check(lib.grl_spmm_set_tile_mode(mode), "set_tile_mode")
+        ops._spmm_stream_enabled[0] = mode >= 100         # 100 / 108 / 116 / 132: node-stream slab kernel
+        _lib.check(lib.grl_spmm_set_tile_mode(0 if mode == 100 else mode), "set_tile_mode")
         Y = torch.full((g.num_rows, args.F), float("nan"), device=dev, dtype=dt)
         ops.spmm_fwd_(g, w, X, Y)
         torch.cuda.synchronize()
@@ -56,6 +57,18 @@ def main():
         ms = e0.elapsed_time(e1) / args.iters
         out[mode] = {"ms": round(ms, 4), "GBps": round(alg / ms / 1e6, 1), "max_abs_diff_vs_first": err}
     lib.grl_spmm_set_tile_mode(0)
+    ops._spmm_stream_enabled[0] = True
+    # the per-layer DropEdge + node-stream pack that feeds the stream kernel
+    for _ in range(3):
+        g.edge_weights(0.3, seed=1, stream_id=1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.iters):
+        g.edge_weights(0.3, seed=1, stream_id=1)
+    e1.record()
+    torch.cuda.synchronize()
+    out["dropedge_stream_ms"] = round(e0.elapsed_time(e1) / args.iters, 4)
     # transposed (gradient) kernel: dX = A'^T dY over CSC + perm
     dY = torch.randn(g.num_rows, args.F, device=dev, dtype=dt)
     dX = torch.empty(g.num_nodes, args.F, device=dev, dtype=dt)

@@ -131,15 +131,19 @@ def test_spmm_forward_kernels_agree_bit_for_bit(dev, dtype, B, N, F, density):
     lib = _lib.load()
     for p_drop in (0.3, 0.9, 0.0):          # 0.9: typed rows whose entries are ALL dropped must still be written as zeros
         w = g.edge_weights(p_drop, seed=5, stream_id=3)
+        assert getattr(w, "_grl_stream", None) is not None
         outs = {}
         try:
-            for mode in (-2, -1, 8, 16, 32, 108, 116, 132, 0):
-                _lib.check(lib.grl_spmm_set_tile_mode(mode), "grl_spmm_set_tile_mode")
+            for mode in (-2, -1, 8, 16, 32, 0, 108, 116, 132, 100):
+                stream_kernel = mode >= 100              # node-stream slab kernel (100 = its own choice of group width)
+                ops._spmm_stream_enabled[0] = stream_kernel
+                _lib.check(lib.grl_spmm_set_tile_mode(0 if mode == 100 else mode), "grl_spmm_set_tile_mode")
                 Y = torch.full((g.num_rows, F), float("nan"), device=dev, dtype=dtype)
                 ops.spmm_fwd_(g, w, X, Y)
                 outs[mode] = Y
         finally:
             lib.grl_spmm_set_tile_mode(0)
+            ops._spmm_stream_enabled[0] = True
         for mode, Y in outs.items():
             assert torch.equal(Y, outs[-2]), f"mode {mode} differs from the row kernel (p_drop={p_drop})"
     assert lib.grl_spmm_set_tile_mode(5) == -1

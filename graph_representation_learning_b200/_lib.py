@@ -54,6 +54,11 @@ SIGNATURES = {
                                          c_uint32, c_float, c_void_p, c_uint64, c_uint64, c_void_p]),
     "grl_bias_act_dropout_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64,
                                          c_int, c_uint32, c_float, c_void_p]),
+    "grl_selfatten_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                  c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "grl_selfatten_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                  c_void_p]),
     "grl_colsum": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "grl_gemm_nt": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int,
                             c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int,

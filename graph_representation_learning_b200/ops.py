@@ -323,14 +323,51 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
     return linear_act([new_v], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
 
 
+class _SelfAttention(torch.autograd.Function):
+    """gamma * (softmax(f g^T) h) + V per graph (csrc/attention.cu).  f, g: [B, N, d]; h, V: [B, N, H]."""
+
+    @staticmethod
+    def forward(ctx, f, g, h, gamma, V):
+        B, N, H = h.shape
+        D = f.shape[2]
+        f, g, h, V = f.contiguous(), g.contiguous(), h.contiguous(), V.contiguous()
+        gam = gamma.detach().float().contiguous()
+        out = torch.empty_like(V)
+        need_grad = any(ctx.needs_input_grad)
+        Np = (N + 63) // 64 * 64
+        tiled = (H, D) in ((64, 16), (128, 16), (256, 32))      # csrc/attention.cu instantiations; else generic kernels
+        o = torch.empty(B * N, H, dtype=torch.float32, device=V.device) if need_grad else None
+        P = torch.empty(B, N, Np, dtype=torch.float32, device=V.device) if (need_grad or not tiled) else None
+        _lib.check(_lib.load().grl_selfatten_fwd(f.data_ptr(), g.data_ptr(), h.data_ptr(), V.data_ptr(), gam.data_ptr(),
+                                                 out.data_ptr(), _lib.ptr(o), _lib.ptr(P), _lib.dtype_code(V), B, N, H, D,
+                                                 Np, _lib.stream_ptr(V.device)), "grl_selfatten_fwd")
+        _lib.count_launch(1)
+        if need_grad:
+            ctx.save_for_backward(f, g, h, gam, o, P)
+        return out
+
+    @staticmethod
+    def backward(ctx, dOut):
+        f, g, h, gam, o, P = ctx.saved_tensors
+        B, N, H = h.shape
+        D = f.shape[2]
+        Np = P.shape[2]
+        dOut = dOut.contiguous()
+        dS = torch.empty_like(P)
+        df, dg, dh = torch.empty_like(f), torch.empty_like(g), torch.empty_like(h)
+        n_qb = (N + 63) // 64
+        part = torch.empty(B * n_qb, H, dtype=torch.float32, device=h.device)
+        _lib.check(_lib.load().grl_selfatten_bwd(dOut.data_ptr(), P.data_ptr(), o.data_ptr(), f.data_ptr(), g.data_ptr(),
+                                                 h.data_ptr(), gam.data_ptr(), dS.data_ptr(), df.data_ptr(),
+                                                 dg.data_ptr(), dh.data_ptr(), part.data_ptr(), _lib.dtype_code(h), B, N,
+                                                 H, D, Np, _lib.stream_ptr(h.device)), "grl_selfatten_bwd")
+        _lib.count_launch(2)
+        dgamma = colsum(part)                     # deterministic reduction of the per-block partial sums
+        return df, dg, dh, dgamma, dOut
+
+
 def self_attention(f_out: torch.Tensor, g_out: torch.Tensor, h_out: torch.Tensor, gamma: torch.Tensor,
                    V: torch.Tensor) -> torch.Tensor:
     """NodeSelfAtten core (reference robust_gcn.py:94-96): gamma * (softmax(f g^T) h) + V, per graph,
-    unscaled and unmasked.
-
-    TRANSITIONAL (DESIGN.md "attention status"): dense library bmm + softmax; the streaming-softmax
-    kernel replaces it behind this same function.
-    """
-    s = torch.softmax(torch.bmm(f_out, g_out.transpose(1, 2)).float(), dim=-1).to(h_out.dtype)
-    o = torch.bmm(s, h_out)
-    return gamma.to(o.dtype) * o + V
+    unscaled and unmasked, on the tiled fp32 kernels of csrc/attention.cu (eval never writes an N x N tensor)."""
+    return _SelfAttention.apply(f_out, g_out, h_out, gamma, V)

@@ -197,6 +197,24 @@ int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float*
 int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst,
                    int64_t rows, int cols, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * NodeSelfAtten core (per graph, dense, unscaled, unmasked; exact two-pass softmax, fp32 arithmetic):
+ *   out = gamma * (softmax(f g^T, dim=-1) h) + V
+ * Replaces torch.matmul / Softmax(-1) / torch.matmul of NodeSelfAtten.forward
+ * gnn/models/networks/robust_gcn.py:94-96 and their autograd.
+ * f, g: [B*N, D] (the ReLU'd projections, contiguous); h, V, out: [B*N, H] contiguous; gamma: float [H]; dtype f32 / bf16.
+ * Supported (H, D): (64, 16), (128, 16), (256, 32)  -- D = H / 8 of the model, H = net_size / 2.
+ * Training: pass o_save (float [B*N, H], = P h before gamma) and P_save (float [B, N, Np], Np = N rounded up to 64;
+ * columns >= N are written as zeros); eval: pass NULL for both and nothing of size N^2 is written.
+ * Backward: dS is a float [B, N, Np] scratch, dgamma_part a float [B * ceil(N/64), H] buffer of per-block partial sums
+ * (the caller reduces it, e.g. with grl_colsum); df, dg: [B*N, D]; dh: [B*N, H]; d(V) = dOut.
+ * ------------------------------------------------------------------------------------------ */
+int grl_selfatten_fwd(const void* f, const void* g, const void* h, const void* V, const float* gamma, void* out,
+                      float* o_save, float* P_save, int dtype, int B, int N, int H, int D, int Np, void* stream);
+int grl_selfatten_bwd(const void* dOut, const float* P, const float* o, const void* f, const void* g, const void* h,
+                      const float* gamma, float* dS, void* df, void* dg, void* dh, float* dgamma_part,
+                      int dtype, int B, int N, int H, int D, int Np, void* stream);
+
 /* column sums  out[c] = sum_m X[m, c]  (bias gradient), fp32 output; out must be zeroed by the caller. */
 int grl_colsum(const void* X, int64_t ldx, int dtype, int64_t M, int C, float* out, void* stream);
 

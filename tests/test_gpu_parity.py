@@ -329,3 +329,39 @@ def test_no_cpu_fallback(dev):
     model = GraphCNNDropEdge(16, 4, 6, net_size=32)
     with pytest.raises(GrlError):
         model([torch.rand(1, 5, 16), torch.zeros(1, 5, 6, 5)])
+
+
+# ---------------------------------------------------------------------------------------- NodeSelfAtten core
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,N,H,D", [(3, 150, 128, 16), (2, 77, 256, 32), (2, 500, 128, 16), (2, 50, 32, 4), (3, 9, 16, 2),
+                                     (1, 64, 128, 16)])
+def test_self_attention_matches_reference_math(dev, dtype, B, N, H, D):
+    """gamma * (softmax(f g^T) h) + V and every gradient against an fp64 restatement of robust_gcn.py:94-96
+    (tiled kernels for (128,16) / (256,32), generic kernels otherwise; N not a multiple of the 64-row tile)."""
+    from graph_representation_learning_b200 import ops
+    gen = torch.Generator().manual_seed(B * 1000 + N + H)
+    f = torch.rand(B, N, D, generator=gen) * 1.5
+    g = torch.rand(B, N, D, generator=gen) * 1.5
+    h = torch.rand(B, N, H, generator=gen)
+    V = torch.randn(B, N, H, generator=gen)
+    gamma = torch.randn(H, generator=gen)
+    dOut = torch.randn(B, N, H, generator=gen)
+    if dtype == torch.bfloat16:
+        f, g, h, V, dOut = (t.bfloat16().float() for t in (f, g, h, V, dOut))
+    ref_in = [t.double().requires_grad_(True) for t in (f, g, h, gamma, V)]
+    s = torch.softmax(torch.matmul(ref_in[0], ref_in[1].transpose(1, 2)), dim=-1)
+    ref_out = ref_in[3] * torch.matmul(s, ref_in[2]) + ref_in[4]
+    ref_out.backward(dOut.double())
+
+    ins = [t.to(dev, dtype).requires_grad_(True) for t in (f, g, h)] + [gamma.to(dev).requires_grad_(True)] + \
+          [V.to(dev, dtype).requires_grad_(True)]
+    out = ops.self_attention(*ins)
+    out.backward(dOut.to(dev, dtype))
+    tol_o, tol_g = (TOL_OUT, TOL_GRAD) if dtype == torch.float32 else (TOL_BF16, 2 * TOL_BF16)
+    assert rel_err(out.detach().float().cpu(), ref_out.detach()) < tol_o
+    for name, a, r in zip("f g h gamma V".split(), ins, ref_in):
+        assert rel_err(a.grad.float().cpu(), r.grad) < tol_g, name
+    # eval: no N x N tensor is saved, same output
+    with torch.no_grad():
+        out2 = ops.self_attention(*[t.detach() for t in ins])
+    assert torch.equal(out2, out.detach())

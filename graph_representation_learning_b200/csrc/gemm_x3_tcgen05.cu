@@ -19,8 +19,9 @@
 //                       Both operands MN-major activations, both split in shared memory; split-K over R
 //                       (blockIdx.y), partial tiles to a workspace that grl_gemm_tn reduces deterministically.
 //
-// Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = operand splitter,
-// 6..9 = accumulator drain + fused epilogue.
+// Warp roles (448 threads): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = operand splitter,
+// 6..13 = accumulator drain + fused epilogue (two warps per TMEM lane quarter, 64 columns each).  The kernel is
+// persistent: the TMA / split / MMA pipeline runs into the next tile while the drain warps finish the current one.
 #include "gemm_common.cuh"
 
 namespace grl {
@@ -31,9 +32,14 @@ struct X3Cfg {
     static constexpr int TILE_BYTES = 128 * 128;                    // every operand tile is 16 KB
     static constexpr int STAGE_BYTES = 4 * TILE_BYTES;              // A | B(_hi) | B_lo | A_lo
     static constexpr int STAGES = 3;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static constexpr int DRAIN_WARPS = 8;                           // two per TMEM lane quarter: 64 columns each
+    static constexpr int DRAIN_COLS = BLOCK_N / (DRAIN_WARPS / 4);
+    static constexpr int EPI_COLS = 16;                             // columns transposed per pass
+    static constexpr int EPI_PITCH = EPI_COLS + 4;                  // floats (conflict-free STS.128 rows)
+    static constexpr int EPI_BYTES = DRAIN_WARPS * 32 * EPI_PITCH * 4;   // one 32 x 16 transposition buffer per drain warp
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
     static constexpr int TMEM_COLS = 512;                           // main0 | main1 | small | (unused)
-    static constexpr int THREADS = 320;
+    static constexpr int THREADS = 64 + 128 + 32 * DRAIN_WARPS;
 };
 
 #define GRL_X3_RAW_HI (1u << 8)   // experiment: trust the tensor core to ignore the 13 low bits (no in-place hi write)
@@ -58,9 +64,48 @@ __device__ __forceinline__ void split_tile(uint8_t* raw, uint8_t* lo_tile, int t
     }
 }
 
+// Epilogue of one drain warp over ITS 32 accumulator rows x DRAIN_COLS columns held in registers (one row per lane):
+// 16-column chunks are transposed through a private 32 x 20 fp32 buffer so that every global store instruction writes
+// eight 64-byte row segments.  Private buffer + registers only: the operand stages keep streaming the NEXT tile.
+__device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const float (&acc)[X3Cfg::DRAIN_COLS], float* buf,
+                                                   int row0, int n0, int lane) {
+    constexpr int PITCH = X3Cfg::EPI_PITCH, CH = X3Cfg::EPI_COLS;
+    const bool vec_ok = epilogue_vec_ok(p);
+    const int rsub = lane >> 2, c4 = (lane & 3) * 4;
+    const int rows = min(32, p.M - row0);
+#pragma unroll
+    for (int c0 = 0; c0 < X3Cfg::DRAIN_COLS; c0 += CH) {
+        if (n0 + c0 >= p.N) break;                                  // warp-uniform
+        __syncwarp();                                               // readers of the previous chunk are done
+#pragma unroll
+        for (int j = 0; j < CH; j += 4)
+            *reinterpret_cast<float4*>(buf + lane * PITCH + j) = make_float4(acc[c0 + j], acc[c0 + j + 1], acc[c0 + j + 2], acc[c0 + j + 3]);
+        __syncwarp();
+        const int col = n0 + c0 + c4;
+        if (col < p.N) {
+            float b4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            if (p.flags & GRL_EPI_BIAS) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (col + t < p.N) b4[t] = __ldg(p.bias + col + t);
+            }
+#pragma unroll
+            for (int rr = rsub; rr < 32; rr += 8) {
+                if (rr < rows) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(buf + rr * PITCH + c4);
+                    float v[4] = {t4.x + b4[0], t4.y + b4[1], t4.z + b4[2], t4.w + b4[3]};
+                    epilogue_store4(p, row0 + rr, col, v, vec_ok);
+                }
+            }
+        }
+    }
+}
+
+// Persistent: a CTA walks output tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the TMA / split / MMA pipeline runs
+// ahead into the next tile while the drain warps finish the epilogue of the current one.
 template <bool kTN>
 __global__ void __launch_bounds__(X3Cfg::THREADS, 1)
-gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
+gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, const int n_tiles,
                const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmB0,
                const __grid_constant__ CUtensorMap tmBlo0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ CUtensorMap tmBlo1) {
@@ -69,18 +114,18 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    float* epi_buf = reinterpret_cast<float*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
     uint64_t* full_bar = bars;                     // [STAGES] TMA bytes landed
     uint64_t* empty_bar = bars + STAGES;           // [STAGES] MMAs reading the stage retired
     uint64_t* split_bar = bars + 2 * STAGES;       // [STAGES] hi / lo tiles written by the splitter warps
     uint64_t* acc_full = bars + 3 * STAGES;        // [2] chunk accumulator complete
     uint64_t* acc_empty = bars + 3 * STAGES + 2;   // [2] chunk accumulator drained
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
+    uint64_t* small_empty = bars + 3 * STAGES + 4; // correction accumulator of the previous tile read out
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 5);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
-    const int m0 = (blockIdx.x / tiles_n) * Cfg::BLOCK_M;
-    const int n0 = (blockIdx.x % tiles_n) * Cfg::BLOCK_N;
     // K-block range of this CTA: everything for NT; one slice of the reduction for TN (split-K over blockIdx.y)
     const int all_kb = p.kblocks0 + p.kblocks1;
     const int kb_begin = kTN ? static_cast<int>(blockIdx.y) * kb_per_split : 0;
@@ -107,8 +152,9 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
-            mbar_init(&acc_empty[b], 128);
+            mbar_init(&acc_empty[b], 32 * Cfg::DRAIN_WARPS);
         }
+        mbar_init(small_empty, 32 * Cfg::DRAIN_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -120,27 +166,31 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
     if (warp == 0) {
         // ===================================================================== TMA producer (one lane)
         if (lane == 0) {
-            for (int it = 0; it < total_kb; ++it) {
-                const int kb = kb_begin + it;
-                const int s = it % STAGES;
-                const uint32_t ph = (it / STAGES) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                if constexpr (kTN) {
-                    // operands are [R, Ma] / [R, Nb] row-major: 4 boxes of {32 columns (128 B), 32 reduction rows}
-                    mbar_expect_tx(&full_bar[s], 2 * Cfg::TILE_BYTES);
-                    const int r0 = kb * Cfg::BLOCK_K;
+            int it = 0;                                            // K-blocks issued so far, over all tiles of this CTA
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+                for (int kk = 0; kk < total_kb; ++kk, ++it) {
+                    const int kb = kb_begin + kk;
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    if constexpr (kTN) {
+                        // operands are [R, Ma] / [R, Nb] row-major: 4 boxes of {32 columns (128 B), 32 reduction rows}
+                        mbar_expect_tx(&full_bar[s], 2 * Cfg::TILE_BYTES);
+                        const int r0 = kb * Cfg::BLOCK_K;
 #pragma unroll
-                    for (int a = 0; a < 4; ++a) {
-                        tma_load_2d(tile(s, T_A) + a * 4096, &tmA0, &full_bar[s], m0 + a * 32, r0);
-                        tma_load_2d(tile(s, T_B) + a * 4096, &tmB0, &full_bar[s], n0 + a * 32, r0);
+                        for (int a = 0; a < 4; ++a) {
+                            tma_load_2d(tile(s, T_A) + a * 4096, &tmA0, &full_bar[s], m0 + a * 32, r0);
+                            tma_load_2d(tile(s, T_B) + a * 4096, &tmB0, &full_bar[s], n0 + a * 32, r0);
+                        }
+                    } else {
+                        mbar_expect_tx(&full_bar[s], 3 * Cfg::TILE_BYTES);
+                        const bool seg1 = kb >= p.kblocks0;
+                        const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
+                        tma_load_2d(tile(s, T_A), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
+                        tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
+                        tma_load_2d(tile(s, T_BLO), seg1 ? &tmBlo1 : &tmBlo0, &full_bar[s], k_elem, n0);
                     }
-                } else {
-                    mbar_expect_tx(&full_bar[s], 3 * Cfg::TILE_BYTES);
-                    const bool seg1 = kb >= p.kblocks0;
-                    const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
-                    tma_load_2d(tile(s, T_A), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
-                    tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
-                    tma_load_2d(tile(s, T_BLO), seg1 ? &tmBlo1 : &tmBlo0, &full_bar[s], k_elem, n0);
                 }
             }
         }
@@ -149,104 +199,114 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc(2, Cfg::BLOCK_M, Cfg::BLOCK_N, kTN ? 1 : 0, kTN ? 1 : 0);
             const uint32_t d_small = tmem_base + 256;
-            int it = 0;
-            for (int c = 0; c < n_chunks; ++c) {
-                const int buf = c & 1;
-                mbar_wait(&acc_empty[buf], ((c >> 1) & 1) ^ 1);      // drained (first two uses pass immediately)
+            int it = 0, cg = 0, tl = 0;                            // K-blocks, chunks, tiles issued by this CTA
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+                mbar_wait(small_empty, (tl & 1) ^ 1);              // previous tile's correction sums were read out
                 tc_fence_after_sync();
-                const uint32_t d_main = tmem_base + buf * 128;
-                for (int i = 0; i < promo && it < total_kb; ++i, ++it) {
-                    const int s = it % STAGES;
-                    const uint32_t ph = (it / STAGES) & 1;
-                    mbar_wait(&split_bar[s], ph);
+                int kk = 0;
+                for (int c = 0; c < n_chunks; ++c, ++cg) {
+                    const int buf = cg & 1;
+                    mbar_wait(&acc_empty[buf], ((cg >> 1) & 1) ^ 1);   // drained (first two uses pass immediately)
                     tc_fence_after_sync();
-                    uint64_t a_desc, b_desc, alo_desc, blo_desc;
-                    if constexpr (kTN) {
-                        // MN-major tf32: 128-byte atoms of 32 columns 4096 B apart (LBO); swizzle pattern of 4 reduction
-                        // rows = 512 B (SBO); layout SWIZZLE_128B_BASE32B as written by TMA's SWIZZLE_128B_ATOM_32B
-                        constexpr uint32_t lbo = 4096, sbo = 512;
-                        a_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_A)), lbo, sbo, 1);
-                        b_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_B)), lbo, sbo, 1);
-                        alo_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_ALO)), lbo, sbo, 1);
-                        blo_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_BLO)), lbo, sbo, 1);
-                    } else {
-                        a_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_A)));
-                        b_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_B)));
-                        alo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_ALO)));
-                        blo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_BLO)));
-                    }
+                    const uint32_t d_main = tmem_base + buf * 128;
+                    for (int i = 0; i < promo && kk < total_kb; ++i, ++kk, ++it) {
+                        const int s = it % STAGES;
+                        const uint32_t ph = (it / STAGES) & 1;
+                        mbar_wait(&split_bar[s], ph);
+                        tc_fence_after_sync();
+                        uint64_t a_desc, b_desc, alo_desc, blo_desc;
+                        if constexpr (kTN) {
+                            // MN-major tf32: 128-byte atoms of 32 columns 4096 B apart (LBO); swizzle pattern of 4
+                            // reduction rows = 512 B (SBO); layout SWIZZLE_128B_BASE32B as written by TMA's ATOM_32B
+                            constexpr uint32_t lbo = 4096, sbo = 512;
+                            a_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_A)), lbo, sbo, 1);
+                            b_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_B)), lbo, sbo, 1);
+                            alo_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_ALO)), lbo, sbo, 1);
+                            blo_desc = umma_desc_mnmajor_sw128(smem_u32(tile(s, T_BLO)), lbo, sbo, 1);
+                        } else {
+                            a_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_A)));
+                            b_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_B)));
+                            alo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_ALO)));
+                            blo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_BLO)));
+                        }
 #pragma unroll
-                    for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
-                        // one UMMA_K step: 32 bytes along a K-major row, or 8 rows (1024 B) of an MN-major tile
-                        const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
-                        umma<true>(d_main, a_desc + koff, b_desc + koff, idesc, (i | k) != 0);
-                        umma<true>(d_small, alo_desc + koff, b_desc + koff, idesc, (it | k) != 0);
-                        umma<true>(d_small, a_desc + koff, blo_desc + koff, idesc, 1u);
+                        for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                            // one UMMA_K step: 32 bytes along a K-major row, or 8 rows (1024 B) of an MN-major tile
+                            const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
+                            umma<true>(d_main, a_desc + koff, b_desc + koff, idesc, (i | k) != 0);
+                            umma<true>(d_small, alo_desc + koff, b_desc + koff, idesc, (kk | k) != 0);
+                            umma<true>(d_small, a_desc + koff, blo_desc + koff, idesc, 1u);
+                        }
+                        umma_commit(&empty_bar[s]);
                     }
-                    umma_commit(&empty_bar[s]);
+                    umma_commit(&acc_full[buf]);
                 }
-                umma_commit(&acc_full[buf]);
             }
         }
     } else if (warp < 6) {
         // ===================================================================== operand splitter (warps 2..5)
         const int tid = threadIdx.x - 64;
         const bool raw_hi = (p.flags & GRL_X3_RAW_HI) != 0;
-        for (int it = 0; it < total_kb; ++it) {
-            const int s = it % STAGES;
-            const uint32_t ph = (it / STAGES) & 1;
-            mbar_wait(&full_bar[s], ph);
-            split_tile(tile(s, T_A), tile(s, T_ALO), tid, raw_hi);
-            if constexpr (kTN) split_tile(tile(s, T_B), tile(s, T_BLO), tid, raw_hi);
-            fence_proxy_async_smem();
-            mbar_arrive(&split_bar[s]);
+        int it = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            for (int kk = 0; kk < total_kb; ++kk, ++it) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);
+                split_tile(tile(s, T_A), tile(s, T_ALO), tid, raw_hi);
+                if constexpr (kTN) split_tile(tile(s, T_B), tile(s, T_BLO), tid, raw_hi);
+                fence_proxy_async_smem();
+                mbar_arrive(&split_bar[s]);
+            }
         }
     } else {
-        // ===================================================================== drain + epilogue (warps 6..9)
-        const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
-        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-        float acc[Cfg::BLOCK_N];
+        // ===================================================================== drain + epilogue (warps 6..13)
+        // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter take 64 accumulator columns each
+        const int quarter = warp & 3, half = (warp - 6) >> 2;
+        const int colbase = half * Cfg::DRAIN_COLS;
+        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + colbase;
+        float* my_buf = epi_buf + (warp - 6) * 32 * Cfg::EPI_PITCH;
+        int cg = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+            float acc[Cfg::DRAIN_COLS];
 #pragma unroll
-        for (int j = 0; j < Cfg::BLOCK_N; ++j) acc[j] = 0.0f;
-        for (int c = 0; c < n_chunks; ++c) {
-            const int buf = c & 1;
-            mbar_wait(&acc_full[buf], (c >> 1) & 1);
-            tc_fence_after_sync();
-#pragma unroll
-            for (int j = 0; j < Cfg::BLOCK_N; j += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32(lane_base + buf * 128 + j, r);
+            for (int j = 0; j < Cfg::DRAIN_COLS; ++j) acc[j] = 0.0f;
+            for (int c = 0; c < n_chunks; ++c, ++cg) {
+                const int buf = cg & 1;
+                mbar_wait(&acc_full[buf], (cg >> 1) & 1);
+                tc_fence_after_sync();
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + buf * 128, r0);
+                tmem_ld_32x32(lane_base + buf * 128 + 32, r1);
                 tmem_ld_wait();
+                tc_fence_before_sync();
+                mbar_arrive(&acc_empty[buf]);                // the data is in registers: release the accumulator first
 #pragma unroll
-                for (int t = 0; t < 32; ++t) acc[j + t] += __uint_as_float(r[t]);
+                for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
             }
-            tc_fence_before_sync();
-            mbar_arrive(&acc_empty[buf]);
-        }
-        if (n_chunks > 0) {
-            // correction terms (complete: the last acc_full commit covers every earlier MMA)
-#pragma unroll
-            for (int j = 0; j < Cfg::BLOCK_N; j += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32(lane_base + 256 + j, r);
+            if (n_chunks > 0) {
+                // correction terms (complete: the last acc_full commit covers every earlier MMA of the tile)
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + 256, r0);
+                tmem_ld_32x32(lane_base + 256 + 32, r1);
                 tmem_ld_wait();
+                tc_fence_before_sync();
+                mbar_arrive(small_empty);                    // the MMA warp may start the next tile's corrections
 #pragma unroll
-                for (int t = 0; t < 32; ++t) acc[j + t] += __uint_as_float(r[t]);
+                for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
+            } else {
+                mbar_arrive(small_empty);
             }
+            GemmParams q = p;
+            if constexpr (kTN)   // partial tile of split blockIdx.y -> its slab of the workspace
+                q.C = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.ldc;
+            if (m0 + quarter * 32 < p.M) epilogue_from_regs(q, acc, my_buf, m0 + quarter * 32, n0 + colbase, lane);
         }
-        // Stage this warp's 32 rows in the (now idle) operand buffers, then run the compact coalesced epilogue.
-        // Every MMA has completed (last acc_full), hence every TMA load and splitter write was consumed: smem is free.
-        float* stage = reinterpret_cast<float*>(tiles);
-        constexpr int PITCH = Cfg::BLOCK_N + 4;
-        float* my_row = stage + (quarter * 32 + lane) * PITCH;
-#pragma unroll
-        for (int j = 0; j < Cfg::BLOCK_N; j += 4)
-            *reinterpret_cast<float4*>(my_row + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
-        __syncwarp();
-        GemmParams q = p;
-        if constexpr (kTN)   // partial tile of split blockIdx.y -> its slab of the workspace
-            q.C = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.ldc;
-        epilogue_warp_rows<Cfg::BLOCK_N>(q, stage, quarter * 32, m0, n0, lane);
     }
     tc_fence_before_sync();
     __syncthreads();
@@ -254,6 +314,7 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split,
 }
 
 static int g_x3_promo = 2;
+static int g_x3_persistent = 1;   // 0: one CTA per tile (A/B experiments via grl_gemm_x3_set_promo(-1 / -2))
 
 template <bool kTN>
 static int ensure_smem_attr() {
@@ -284,8 +345,10 @@ int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
     if ((rc = ensure_smem_attr<false>())) return rc;
     const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
-    gemm_x3_kernel<false><<<tiles_m * tiles_n, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, 0, tA0, tB0, tBlo0, tA1,
-                                                                                   tB1, tBlo1);
+    const int n_tiles = tiles_m * tiles_n;
+    const int grid = g_x3_persistent ? (n_tiles < kNumSMs ? n_tiles : kNumSMs) : n_tiles;   // one CTA per SM, tiles strided
+    gemm_x3_kernel<false><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, 0, n_tiles, tA0, tB0, tBlo0, tA1, tB1,
+                                                                      tBlo1);
     GRL_LAUNCH_CHECK("gemm_x3_kernel<NT>");
     return 0;
 }
@@ -307,6 +370,10 @@ using namespace grl;
 // Tuning / experiment knob of the TF32X3 kernels (host call): promo = K-blocks (of 32) accumulated in TMEM before
 // the partial sum is promoted to fp32 registers (>= 1).
 extern "C" int grl_gemm_x3_set_promo(int promo) {
+    if (promo == -1 || promo == -2) {             // experiment switch: -1 = one CTA per tile, -2 = persistent (default)
+        g_x3_persistent = promo == -2;
+        return 0;
+    }
     if (promo < 1 || promo > 1 << 20) {
         set_error("grl_gemm_x3_set_promo: promo=%d must be >= 1", promo);
         return GRL_E_BADARG;
@@ -348,8 +415,8 @@ extern "C" int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t 
     const size_t need = sizeof(float) * static_cast<size_t>(Ma) * Nb * splits;
     GRL_CHECK_ARG(workspace_bytes >= need, GRL_E_WORKSPACE, "grl_gemm_tn: workspace %zu < %zu", workspace_bytes, need);
     if ((rc = ensure_smem_attr<true>())) return rc;
-    gemm_x3_kernel<true><<<dim3(tiles, splits), Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, kb_per_split, tA, tB, tB,
-                                                                                    tA, tB, tB);
+    gemm_x3_kernel<true><<<dim3(tiles, splits), Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, kb_per_split, tiles, tA,
+                                                                                    tB, tB, tA, tB, tB);
     GRL_LAUNCH_CHECK("gemm_x3_kernel<TN>");
     const int64_t n = static_cast<int64_t>(Ma) * Nb;
     int blocks = static_cast<int>((n + 255) / 256);

@@ -68,3 +68,40 @@ def make_batch(wl: Workload, seed: int, device, features: str = "dense", B: Opti
         raise ValueError(features)
     y = torch.randint(0, wl.output_dim, (B, N), generator=gen, device=dev)
     return V, A, y
+
+
+CONFIGS["cfg4"] = Workload("cfg4: 1 graph x 1M nodes, degree 16/type, S=256, fp32, no attention", 1, 1_000_000,
+                           degree=16.0, use_attention=False)
+
+
+def make_edge_batch(wl: Workload, seed: int, device, B: Optional[int] = None, N: Optional[int] = None,
+                    feature_dtype: torch.dtype = torch.float32, features: bool = True):
+    """Same graph distribution as ``make_batch`` without the O(N^2) dense adjacency (cfg4: one 1M-node graph, cfg5:
+    10 000-node documents): for every (graph, node, type) a Poisson(degree) number of neighbours j != i, uniform.
+    Returns (V [B,N,input_dim] or None, edges int32 [E,4] = (b, i, l, j), y [B,N]) on ``device``; duplicate
+    (b,i,l,j) are possible with probability ~degree^2 / 2N per row and stay separate entries, as the pack defines."""
+    B = wl.B if B is None else B
+    N = wl.N if N is None else N
+    L = wl.num_edges
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev).manual_seed(seed)
+    parts = []
+    for b in range(B):
+        k = torch.poisson(torch.full((N * L,), float(wl.degree), device=dev), generator=gen).to(torch.int64)
+        k.clamp_(max=N - 1)
+        src = torch.repeat_interleave(torch.arange(N * L, device=dev), k)        # (i, l) flattened
+        i, l = src // L, src % L
+        j = (i + 1 + torch.randint(0, max(N - 1, 1), (src.numel(),), generator=gen, device=dev)) % N
+        parts.append(torch.stack([torch.full_like(i, b), i, l, j], dim=1).to(torch.int32))
+    edges = torch.cat(parts, dim=0)
+    V = None
+    if features:
+        ld = (wl.input_dim + 7) // 8 * 8
+        Vp = torch.empty(B, N, ld, device=dev, dtype=feature_dtype)
+        for b in range(B):
+            for r0 in range(0, N, 65536):                                        # bounded fp32 temporary
+                r1 = min(N, r0 + 65536)
+                Vp[b, r0:r1] = torch.rand(r1 - r0, ld, generator=gen, device=dev, dtype=torch.float32).to(feature_dtype)
+        V = Vp[:, :, :wl.input_dim]
+    y = torch.randint(0, wl.output_dim, (B, N), generator=gen, device=dev)
+    return V, edges, y

@@ -334,7 +334,7 @@ def test_no_cpu_fallback(dev):
 # ---------------------------------------------------------------------------------------- NodeSelfAtten core
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,N,H,D", [(3, 150, 128, 16), (2, 77, 256, 32), (2, 500, 128, 16), (2, 50, 32, 4), (3, 9, 16, 2),
-                                     (1, 64, 128, 16)])
+                                     (1, 64, 128, 16), (1, 2100, 128, 16)])
 def test_self_attention_matches_reference_math(dev, dtype, B, N, H, D):
     """gamma * (softmax(f g^T) h) + V and every gradient against an fp64 restatement of robust_gcn.py:94-96
     (tiled kernels for (128,16) / (256,32), generic kernels otherwise; N not a multiple of the 64-row tile)."""
@@ -365,3 +365,52 @@ def test_self_attention_matches_reference_math(dev, dtype, B, N, H, D):
     with torch.no_grad():
         out2 = ops.self_attention(*[t.detach() for t in ins])
     assert torch.equal(out2, out.detach())
+
+
+# ---------------------------------------------------------------------------------------- large graphs (cfg4 / cfg5 sizes)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_spmm_large_graph_against_sparse_library_and_adjoint(dev, dtype):
+    """One 150 000-node graph (the slab does not fit: gather kernels), packed from an edge list with duplicates.
+    Checker: torch.sparse on the same device in fp64 (test infrastructure only), plus the size-independent adjoint
+    identity <dY, A X> == <A^T dY, X> that ties the transposed kernel to the forward one."""
+    from graph_representation_learning_b200 import PackedGraphBatch, ops, synthetic
+    wl = synthetic.Workload("large", 1, 150_000, input_dim=8, degree=12.0)
+    _, edges, _ = synthetic.make_edge_batch(wl, 5, dev, features=False)
+    g = PackedGraphBatch.from_edges(edges, 1, wl.N, wl.num_edges)
+    assert g.nnz == edges.shape[0] + wl.N
+    F = 128
+    gen = torch.Generator(device=dev).manual_seed(3)
+    X = torch.randn(wl.N, F, device=dev, generator=gen).to(dtype)
+    dY = torch.randn(g.num_rows, F, device=dev, generator=gen).to(dtype)
+    w = g.edge_weights(0.3, seed=9, stream_id=2)
+    Y = torch.empty(g.num_rows, F, device=dev, dtype=dtype)
+    ops.spmm_fwd_(g, w, X, Y)
+    dX = torch.empty(wl.N, F, device=dev, dtype=dtype)
+    ops.spmm_bwd_(g, w, dY, dX)
+    A = torch.sparse_csr_tensor(g.rowptr.long(), g.col.long(), w.double(), size=(g.num_rows, wl.N))
+    ref_Y = torch.sparse.mm(A, X.double())
+    ref_dX = torch.sparse.mm(A.to_sparse_coo().t().coalesce(), dY.double())
+    tol = TOL_OUT if dtype == torch.float32 else TOL_BF16
+    assert rel_err(Y.float().cpu(), ref_Y.cpu()) < tol
+    assert rel_err(dX.float().cpu(), ref_dX.cpu()) < tol
+    lhs = float((dY.double() * Y.double()).sum())
+    rhs = float((dX.double() * X.double()).sum())
+    assert abs(lhs - rhs) <= (1e-5 if dtype == torch.float32 else 2e-2) * max(abs(lhs), abs(rhs), 1.0)
+
+
+def test_model_eval_on_edge_list_equals_dense_path(dev):
+    """from_edges (cfg4 / cfg5 entry) and from_dense (the reference collate's format) give the same packed graph and
+    bit-identical eval logits."""
+    from graph_representation_learning_b200 import GraphCNNDropEdge, PackedGraphBatch, synthetic
+    wl = synthetic.Workload("eq", 3, 130, input_dim=40, output_dim=7, net_size=256)
+    V, A, _ = synthetic.make_batch(wl, 11, dev)
+    b, i, l, j = torch.nonzero(A, as_tuple=True)
+    edges = torch.stack([b, i, l, j], 1).to(torch.int32)
+    edges = edges[torch.randperm(edges.shape[0], device=dev)]                    # the pack must not depend on edge order
+    g_d, g_e = PackedGraphBatch.from_dense(A), PackedGraphBatch.from_edges(edges, wl.B, wl.N, wl.num_edges)
+    for name in ("rowptr", "col", "val", "colptr", "rowidx", "perm"):
+        assert torch.equal(getattr(g_d, name), getattr(g_e, name)), name
+    torch.manual_seed(2)
+    model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size).to(dev).eval()
+    with torch.no_grad():
+        assert torch.equal(model([V, g_d]), model([V, g_e]))

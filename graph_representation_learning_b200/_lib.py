@@ -59,6 +59,14 @@ SIGNATURES = {
     "grl_selfatten_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_void_p]),
+    "grl_reduce_workspace_bytes": (c_size_t, []),
+    "grl_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p,
+                           c_void_p]),
+    "grl_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p,
+                           c_void_p, c_int64, c_void_p]),
+    "grl_l2_norm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "grl_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float, c_float,
+                              c_float, c_int64, c_void_p, c_float, c_void_p]),
     "grl_colsum": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "grl_gemm_nt": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int,
                             c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int,

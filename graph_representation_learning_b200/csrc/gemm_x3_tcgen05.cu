@@ -382,10 +382,34 @@ extern "C" int grl_gemm_x3_set_promo(int promo) {
     return 0;
 }
 
+// Split-K plan of the TN kernel: all tiles * splits CTAs run in waves of kNumSMs, a CTA costs its K-blocks plus a fixed
+// prologue + drain + epilogue (~12 K-blocks of time).  One wave with fewer CTAs than SMs can lose to two fuller waves
+// (gcn3 dW: 56 tiles -> 2 splits = 112 CTAs = 2000 K-blocks each, against 5 splits = 280 CTAs = 2 waves of 800).
+static int tn_plan_splits(int tiles, int kblocks) {
+    constexpr int kOverheadKb = 12, kMaxSplits = 16;
+    int cap = kNumSMs / tiles;
+    if (cap < kMaxSplits) cap = kMaxSplits;
+    if (cap > kblocks) cap = kblocks;
+    if (cap < 1) cap = 1;
+    int64_t best_cost = -1;
+    int best = 1;
+    for (int sp = 1; sp <= cap; ++sp) {
+        const int64_t waves = (static_cast<int64_t>(tiles) * sp + kNumSMs - 1) / kNumSMs;
+        const int64_t cost = waves * ((kblocks + sp - 1) / sp + kOverheadKb);
+        if (best_cost < 0 || cost * 100 < best_cost * 98) {      // a larger split count must win by 2 %
+            best_cost = cost;
+            best = sp;
+        }
+    }
+    return best;
+}
+
 extern "C" size_t grl_gemm_tn_workspace_bytes(int Ma, int Nb) {
-    // splits * tiles <= kNumSMs and Ma*Nb <= tiles * 128*128, so splits*Ma*Nb <= kNumSMs * 128*128 (or Ma*Nb if 1 split)
-    const size_t one = static_cast<size_t>(Ma) * Nb, cap = static_cast<size_t>(kNumSMs) * 128 * 128;
-    return sizeof(float) * (one > cap ? one : cap);
+    // one [Ma, Nb] fp32 slab per split; splits <= max(16, kNumSMs / tiles)
+    const int tiles = ((Ma + 127) / 128) * ((Nb + 127) / 128);
+    int cap = kNumSMs / (tiles > 0 ? tiles : 1);
+    if (cap < 16) cap = 16;
+    return sizeof(float) * static_cast<size_t>(Ma) * Nb * cap;
 }
 
 extern "C" int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int Ma,
@@ -407,9 +431,7 @@ extern "C" int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t 
     p.kblocks0 = static_cast<int>((R + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K);
     p.kblocks1 = 0;
     const int tiles = ((Ma + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M) * ((Nb + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N);
-    int splits = kNumSMs / tiles;
-    if (splits < 1) splits = 1;
-    if (splits > p.kblocks0) splits = p.kblocks0;
+    int splits = tn_plan_splits(tiles, p.kblocks0);
     const int kb_per_split = (p.kblocks0 + splits - 1) / splits;
     splits = (p.kblocks0 + kb_per_split - 1) / kb_per_split;          // no empty split
     const size_t need = sizeof(float) * static_cast<size_t>(Ma) * Nb * splits;

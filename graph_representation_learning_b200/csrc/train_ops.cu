@@ -1,0 +1,211 @@
+// Loss and optimizer kernels of the KV train step (all deterministic: fixed-order reductions, no atomics).
+//
+//   grl_ce_fwd / grl_ce_bwd   nn.CrossEntropyLoss()(pred.transpose(1, 2), target) with ignore_index and optional class
+//                             weights -- gnn/trainer/losses/cross_entropy_loss.py:19-35 (mean over the non-ignored
+//                             nodes, weighted mean when weights are given) and its gradient.
+//   grl_l2_norm               total gradient norm of clip_grad_norm_ -- gnn/trainer/training_procedures/kv_procedure.py:161.
+//   grl_adam_step             torch.optim.Adam.step (the optimizer BuitlinOptimizer builds by name,
+//                             gnn/trainer/optimizers/builtin_optimizer.py:22-26) over ONE flat parameter / gradient /
+//                             moment buffer, with the clip coefficient min(1, max_norm / (norm + 1e-6)) applied on the
+//                             fly from the device-resident norm (no host sync between clip and step).
+#include "common.cuh"
+
+namespace grl {
+
+constexpr int kTrainThreads = 256;
+
+// one warp per row; per-block partial sums (loss * w, w) in block order -> partial[2 * blockIdx.x + {0, 1}]
+__global__ void __launch_bounds__(kTrainThreads)
+ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target,
+              const float* __restrict__ weight, int64_t ignore_index, int64_t M, int C, float* __restrict__ lse,
+              float* __restrict__ partial) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    float loss_sum = 0.f, w_sum = 0.f;
+    for (int64_t r = warp; r < M; r += n_warps) {
+        const float* x = logits + r * ld;
+        float m = -INFINITY;
+        for (int c = lane; c < C; c += 32) m = fmaxf(m, x[c]);
+        for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        float s = 0.f;
+        for (int c = lane; c < C; c += 32) s += expf(x[c] - m);
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float l = m + logf(s);
+        if (lane == 0) lse[r] = l;
+        const int64_t y = target[r];
+        if (y != ignore_index && y >= 0 && y < C) {
+            const float w = weight ? weight[y] : 1.0f;
+            loss_sum += w * (l - x[y]);
+            w_sum += w;
+        }
+    }
+    __shared__ float sl[kTrainThreads / 32], sw[kTrainThreads / 32];
+    if (lane == 0) { sl[wib] = loss_sum; sw[wib] = w_sum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < kTrainThreads / 32; ++k) { a += sl[k]; b += sw[k]; }
+        partial[2 * blockIdx.x] = a;
+        partial[2 * blockIdx.x + 1] = b;
+    }
+}
+
+// out[0] = sum(loss) / sum(w), out[1] = sum(w)   (one block; fixed order)
+__global__ void __launch_bounds__(kTrainThreads)
+ce_finish_kernel(const float* __restrict__ partial, int n_blocks, float* __restrict__ out) {
+    __shared__ float sa[kTrainThreads], sb[kTrainThreads];
+    float a = 0.f, b = 0.f;
+    for (int k = threadIdx.x; k < n_blocks; k += kTrainThreads) { a += partial[2 * k]; b += partial[2 * k + 1]; }
+    sa[threadIdx.x] = a; sb[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = kTrainThreads / 2; o >= 1; o >>= 1) {
+        if (threadIdx.x < o) { sa[threadIdx.x] += sa[threadIdx.x + o]; sb[threadIdx.x] += sb[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out[0] = sa[0] / sb[0]; out[1] = sb[0]; }
+}
+
+// dlogits[r][c] = g * w_y / sum(w) * (softmax(x)[c] - [c == y]);  0 for ignored rows
+__global__ void __launch_bounds__(kTrainThreads)
+ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target,
+              const float* __restrict__ weight, int64_t ignore_index, int64_t M, int C, const float* __restrict__ lse,
+              const float* __restrict__ loss_out, const float* __restrict__ grad_out, float* __restrict__ dlogits,
+              int64_t ldd) {
+    const int64_t total = M * C;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    const float g = grad_out[0] / loss_out[1];
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int64_t r = t / C;
+        const int c = static_cast<int>(t - r * C);
+        const int64_t y = target[r];
+        float v = 0.f;
+        if (y != ignore_index && y >= 0 && y < C) {
+            const float w = weight ? weight[y] : 1.0f;
+            v = g * w * (expf(logits[r * ld + c] - lse[r]) - (c == y ? 1.0f : 0.0f));
+        }
+        dlogits[r * ldd + c] = v;
+    }
+}
+
+// partial[blockIdx.x] = sum of squares of this block's grid-stride share (fixed order)
+__global__ void __launch_bounds__(kTrainThreads)
+sumsq_kernel(const float* __restrict__ x, int64_t n, float* __restrict__ partial) {
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    float s = 0.f;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) s = fmaf(x[i], x[i], s);
+    __shared__ float sh[kTrainThreads];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = kTrainThreads / 2; o >= 1; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+
+__global__ void __launch_bounds__(kTrainThreads)
+norm_finish_kernel(const float* __restrict__ partial, int n_blocks, float* __restrict__ out) {
+    __shared__ double sh[kTrainThreads];
+    double s = 0.0;
+    for (int k = threadIdx.x; k < n_blocks; k += kTrainThreads) s += static_cast<double>(partial[k]);
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = kTrainThreads / 2; o >= 1; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[0] = static_cast<float>(sqrt(sh[0]));
+}
+
+// torch.optim.Adam (amsgrad = False, maximize = False), single-tensor formulas:
+//   g += wd * p;  m.lerp_(g, 1 - b1);  v = b2 * v + (1 - b2) * g * g;
+//   p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)
+// g is first scaled by the clip coefficient min(1, max_norm / (norm + 1e-6)) (clip_grad_norm_) and written back.
+__global__ void __launch_bounds__(kTrainThreads)
+adam_step_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
+                 float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
+                 const float* __restrict__ norm, float max_norm) {
+    float coef = 1.0f;
+    if (norm && max_norm > 0.0f) coef = fminf(max_norm / (norm[0] + 1e-6f), 1.0f);
+    const float step_size = lr / bc1;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float gi = g[i] * coef;
+        g[i] = gi;
+        const float pi = p[i];
+        if (wd != 0.0f) gi = fmaf(wd, pi, gi);
+        const float mi = m[i] + (gi - m[i]) * (1.0f - b1);
+        const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        p[i] = pi - step_size * (mi / denom);
+    }
+}
+
+static int grid_for(int64_t n_items, int per_block) {
+    int64_t b = (n_items + per_block - 1) / per_block;
+    if (b > kNumSMs * 8) b = kNumSMs * 8;
+    if (b < 1) b = 1;
+    return static_cast<int>(b);
+}
+
+}  // namespace grl
+
+using namespace grl;
+
+extern "C" size_t grl_reduce_workspace_bytes(void) { return sizeof(float) * 2 * kNumSMs * 8; }
+
+extern "C" int grl_ce_fwd(const float* logits, int64_t ld, const int64_t* target, const float* weight,
+                          int64_t ignore_index, int64_t M, int C, float* lse, float* loss_out, void* workspace,
+                          void* stream) {
+    GRL_CHECK_ARG(logits && target && lse && loss_out && workspace, GRL_E_BADARG, "grl_ce_fwd: null pointer");
+    GRL_CHECK_ARG(M > 0 && C > 0 && ld >= C, GRL_E_BADARG, "grl_ce_fwd: bad shape");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int blocks = grid_for(M, kTrainThreads / 32);
+    float* partial = static_cast<float*>(workspace);
+    ce_fwd_kernel<<<blocks, kTrainThreads, 0, st>>>(logits, ld, target, weight, ignore_index, M, C, lse, partial);
+    GRL_LAUNCH_CHECK("ce_fwd_kernel");
+    ce_finish_kernel<<<1, kTrainThreads, 0, st>>>(partial, blocks, loss_out);
+    GRL_LAUNCH_CHECK("ce_finish_kernel");
+    return 0;
+}
+
+extern "C" int grl_ce_bwd(const float* logits, int64_t ld, const int64_t* target, const float* weight,
+                          int64_t ignore_index, int64_t M, int C, const float* lse, const float* loss_out,
+                          const float* grad_out, float* dlogits, int64_t ldd, void* stream) {
+    GRL_CHECK_ARG(logits && target && lse && loss_out && grad_out && dlogits, GRL_E_BADARG, "grl_ce_bwd: null pointer");
+    GRL_CHECK_ARG(M > 0 && C > 0 && ld >= C && ldd >= C, GRL_E_BADARG, "grl_ce_bwd: bad shape");
+    ce_bwd_kernel<<<grid_for(M * C, kTrainThreads), kTrainThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        logits, ld, target, weight, ignore_index, M, C, lse, loss_out, grad_out, dlogits, ldd);
+    GRL_LAUNCH_CHECK("ce_bwd_kernel");
+    return 0;
+}
+
+extern "C" int grl_l2_norm(const float* x, int64_t n, float* out, void* workspace, void* stream) {
+    GRL_CHECK_ARG(x && out && workspace, GRL_E_BADARG, "grl_l2_norm: null pointer");
+    GRL_CHECK_ARG(n > 0, GRL_E_BADARG, "grl_l2_norm: n <= 0");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int blocks = grid_for(n, kTrainThreads * 4);
+    float* partial = static_cast<float*>(workspace);
+    sumsq_kernel<<<blocks, kTrainThreads, 0, st>>>(x, n, partial);
+    GRL_LAUNCH_CHECK("sumsq_kernel");
+    norm_finish_kernel<<<1, kTrainThreads, 0, st>>>(partial, blocks, out);
+    GRL_LAUNCH_CHECK("norm_finish_kernel");
+    return 0;
+}
+
+extern "C" int grl_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                             float eps, float weight_decay, int64_t step, const float* grad_norm, float max_norm,
+                             void* stream) {
+    GRL_CHECK_ARG(p && g && m && v, GRL_E_BADARG, "grl_adam_step: null pointer");
+    GRL_CHECK_ARG(n > 0 && step >= 1, GRL_E_BADARG, "grl_adam_step: n <= 0 or step < 1");
+    const double bc1 = 1.0 - pow(static_cast<double>(beta1), static_cast<double>(step));
+    const double bc2 = 1.0 - pow(static_cast<double>(beta2), static_cast<double>(step));
+    adam_step_kernel<<<grid_for(n, kTrainThreads * 4), kTrainThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, static_cast<float>(bc1), static_cast<float>(sqrt(bc2)),
+        grad_norm, max_norm);
+    GRL_LAUNCH_CHECK("adam_step_kernel");
+    return 0;
+}

@@ -265,9 +265,7 @@ class KVProcedure(BaseProcedure):
         with torch.set_grad_enabled(True):
             loss, scores = self._step_process(batch_sample, want)
             loss.backward()
-            self.step.bucket.all_reduce_mean()
-            self.step.bucket.clip_(self.step.max_grad_norm)
-            self.optimizer.step()
+            self.step.clip_and_step()
         return scores
 
     @torch.no_grad()

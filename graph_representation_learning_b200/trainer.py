@@ -20,8 +20,55 @@ import torch.distributed as dist
 from torch import nn
 
 
+_ws_cache: Dict[Any, torch.Tensor] = {}
+
+
+def _reduce_workspace(device: torch.device) -> torch.Tensor:
+    """scratch for the block partial sums of the loss / norm reductions (one per device and stream)"""
+    from . import _lib
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None:
+        ws = torch.empty(_lib.load().grl_reduce_workspace_bytes(), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    """mean (weighted) cross entropy over the rows whose label is not ignore_index -- csrc/train_ops.cu"""
+
+    @staticmethod
+    def forward(ctx, logits2d, target1d, weight, ignore_index):
+        from . import _lib
+        M, C = logits2d.shape
+        dev = logits2d.device
+        lse = torch.empty(M, dtype=torch.float32, device=dev)
+        out = torch.empty(2, dtype=torch.float32, device=dev)
+        _lib.check(_lib.load().grl_ce_fwd(logits2d.data_ptr(), logits2d.stride(0), target1d.data_ptr(), _lib.ptr(weight),
+                                          int(ignore_index), M, C, lse.data_ptr(), out.data_ptr(),
+                                          _reduce_workspace(dev).data_ptr(), _lib.stream_ptr(dev)), "grl_ce_fwd")
+        _lib.count_launch(2)
+        ctx.save_for_backward(logits2d, target1d, weight, lse, out)
+        ctx.ignore_index = int(ignore_index)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        from . import _lib
+        logits2d, target1d, weight, lse, out = ctx.saved_tensors
+        M, C = logits2d.shape
+        d = torch.empty(M, C, dtype=torch.float32, device=logits2d.device)
+        g = grad_out.detach().reshape(1).float().contiguous()
+        _lib.check(_lib.load().grl_ce_bwd(logits2d.data_ptr(), logits2d.stride(0), target1d.data_ptr(), _lib.ptr(weight),
+                                          ctx.ignore_index, M, C, lse.data_ptr(), out.data_ptr(), g.data_ptr(),
+                                          d.data_ptr(), C, _lib.stream_ptr(d.device)), "grl_ce_bwd")
+        _lib.count_launch(1)
+        return d, None, None, None
+
+
 class CrossEntropyLoss(nn.Module):
-    """gnn/trainer/losses/cross_entropy_loss.py:9-35"""
+    """gnn/trainer/losses/cross_entropy_loss.py:9-35.  CUDA fp32 logits run the kernels of csrc/train_ops.cu; anything
+    else (the CPU tensors of the host-logic tests) goes through nn.CrossEntropyLoss like the reference."""
 
     def __init__(self, weight=None):
         super().__init__()
@@ -29,6 +76,15 @@ class CrossEntropyLoss(nn.Module):
         self.criterion = nn.CrossEntropyLoss(w)
 
     def forward(self, pred: torch.Tensor, target: torch.Tensor, **kwargs) -> torch.Tensor:
+        if pred.is_cuda and pred.dtype == torch.float32 and pred.dim() >= 2 and target.dtype == torch.int64:
+            C = pred.shape[-1]
+            logits2d = pred.reshape(-1, C)
+            if logits2d.stride(1) != 1:
+                logits2d = logits2d.contiguous()
+            w = self.criterion.weight
+            if w is not None:
+                w = w.to(device=pred.device, dtype=torch.float32).contiguous()
+            return _CrossEntropyFn.apply(logits2d, target.reshape(-1).contiguous(), w, self.criterion.ignore_index)
         return self.criterion(pred.transpose(1, 2), target)
 
 
@@ -53,11 +109,113 @@ class FlatGradBucket:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
             self.flat.div_(dist.get_world_size())
 
+    def norm(self) -> torch.Tensor:
+        """total 2-norm of the gradients as a device scalar (deterministic two-stage reduction on CUDA)"""
+        if self.flat.is_cuda:
+            from . import _lib
+            out = torch.empty(1, dtype=torch.float32, device=self.flat.device)
+            _lib.check(_lib.load().grl_l2_norm(self.flat.data_ptr(), self.flat.numel(), out.data_ptr(),
+                                               _reduce_workspace(self.flat.device).data_ptr(),
+                                               _lib.stream_ptr(self.flat.device)), "grl_l2_norm")
+            _lib.count_launch(2)
+            return out[0]
+        return torch.linalg.vector_norm(self.flat)
+
     def clip_(self, max_norm: float) -> torch.Tensor:
-        total = torch.linalg.vector_norm(self.flat)
+        """clip_grad_norm_ (kv_procedure.py:161): scale by min(1, max_norm / (norm + 1e-6)); returns the norm"""
+        total = self.norm()
         coef = torch.clamp(max_norm / (total + 1e-6), max=1.0)
         self.flat.mul_(coef)
         return total
+
+
+class FlatAdam(torch.optim.Optimizer):
+    """torch.optim.Adam (amsgrad=False) over ONE flat parameter / moment buffer: a single kernel per step
+    (csrc/train_ops.cu grl_adam_step), optionally with the clip_grad_norm_ scaling folded in from a device-resident
+    norm.  ``param_groups`` / ``state_dict()`` keep torch.optim.Adam's layout (per-parameter ``step`` / ``exp_avg`` /
+    ``exp_avg_sq``, here views of the flat buffers), so schedulers that poke ``param_groups[*]["lr"]`` and the
+    checkpoint handler work unchanged.  Parameters are re-pointed at views of the flat buffer."""
+
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0,
+                 amsgrad: bool = False, flat_grad: Optional[torch.Tensor] = None, **ignored: Any):
+        if amsgrad:
+            raise ValueError("FlatAdam implements amsgrad=False only")
+        super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
+        self._params = [p for g in self.param_groups for p in g["params"]]
+        if not self._params or not all(p.is_cuda and p.dtype == torch.float32 for p in self._params):
+            raise ValueError("FlatAdam needs fp32 CUDA parameters")
+        dev = self._params[0].device
+        self._sizes = [p.numel() for p in self._params]
+        n = sum(self._sizes)
+        self.flat_p = torch.empty(n, dtype=torch.float32, device=dev)
+        self.flat_m = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.flat_v = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.flat_g = flat_grad if flat_grad is not None else torch.zeros(n, dtype=torch.float32, device=dev)
+        self._own_grad = flat_grad is None
+        self._step = 0
+        self._adopt_params()
+
+    def _views(self, flat):
+        off = 0
+        for p, k in zip(self._params, self._sizes):
+            yield p, flat[off:off + k].view_as(p)
+            off += k
+
+    def _adopt_params(self) -> None:
+        with torch.no_grad():
+            for p, view in self._views(self.flat_p):
+                if p.data.data_ptr() != view.data_ptr():
+                    view.copy_(p.data)
+                    p.data = view
+
+    def _publish_state(self) -> None:
+        step = torch.tensor(float(self._step))
+        for (p, m), (_, v) in zip(self._views(self.flat_m), self._views(self.flat_v)):
+            self.state[p] = {"step": step.clone(), "exp_avg": m, "exp_avg_sq": v}
+
+    @torch.no_grad()
+    def step(self, closure=None, grad_norm: Optional[torch.Tensor] = None, max_norm: float = 0.0):
+        from . import _lib
+        loss = closure() if closure is not None else None
+        self._adopt_params()                     # a .to() / load that re-allocated a parameter is folded back in
+        if self._own_grad:                       # gradients are not views of one bucket: gather them
+            for p, view in self._views(self.flat_g):
+                if p.grad is None:
+                    view.zero_()
+                elif p.grad.data_ptr() != view.data_ptr():
+                    view.copy_(p.grad)
+        self._step += 1
+        lib, off = _lib.load(), 0
+        for g in self.param_groups:
+            k = sum(p.numel() for p in g["params"])
+            b1, b2 = g["betas"]
+            sl = slice(off, off + k)
+            _lib.check(lib.grl_adam_step(self.flat_p[sl].data_ptr(), self.flat_g[sl].data_ptr(),
+                                         self.flat_m[sl].data_ptr(), self.flat_v[sl].data_ptr(), k, float(g["lr"]),
+                                         float(b1), float(b2), float(g["eps"]), float(g["weight_decay"]), self._step,
+                                         _lib.ptr(grad_norm), float(max_norm), _lib.stream_ptr(self.flat_p.device)),
+                       "grl_adam_step")
+            _lib.count_launch(1)
+            off += k
+        if not self.state:
+            self._publish_state()
+        else:
+            for st in self.state.values():
+                st["step"] += 1
+        return loss
+
+    def load_state_dict(self, state_dict) -> None:
+        super().load_state_dict(state_dict)
+        steps = [int(st["step"]) for st in self.state.values() if "step" in st]
+        self._step = max(steps) if steps else 0
+        with torch.no_grad():
+            for (p, m), (_, v) in zip(self._views(self.flat_m), self._views(self.flat_v)):
+                st = self.state.get(p)
+                if st:
+                    m.copy_(st["exp_avg"])
+                    v.copy_(st["exp_avg_sq"])
+        if self.state:
+            self._publish_state()
 
 
 class KVTrainStep:
@@ -78,9 +236,14 @@ class KVTrainStep:
         else:
             kwargs = dict(optimizer_kwargs or {})
             kwargs.pop("lr", None)  # the reference never forwards lr (builtin_optimizer.py:10,18-23)
-            if optimizer_type == "Adam" and self.device.type == "cuda":
-                kwargs.setdefault("fused", True)
-            self.optimizer = getattr(torch.optim, optimizer_type)(self.bucket.params, **kwargs)
+            if optimizer_type == "Adam" and self.device.type == "cuda" and not kwargs.get("amsgrad"):
+                kwargs.pop("fused", None)
+                self.optimizer = FlatAdam(self.bucket.params, flat_grad=self.bucket.flat, **kwargs)
+            else:
+                self.optimizer = getattr(torch.optim, optimizer_type)(self.bucket.params, **kwargs)
+        if isinstance(self.optimizer, FlatAdam) and self.optimizer._own_grad:
+            # a factory-built FlatAdam: let it read the bucket directly instead of gathering p.grad every step
+            self.optimizer.flat_g, self.optimizer._own_grad = self.bucket.flat, False
 
     def _to_device(self, batch_sample: Dict[str, torch.Tensor]) -> Tuple[list, torch.Tensor]:
         if "adjacency_matrix" not in batch_sample and "edges" in batch_sample:      # EdgeListCollate host batch
@@ -108,10 +271,20 @@ class KVTrainStep:
         with torch.set_grad_enabled(True):
             loss, _ = self.step_process(batch_sample)
             loss.backward()
-            self.bucket.all_reduce_mean()
-            self.bucket.clip_(self.max_grad_norm)
-            self.optimizer.step()
+            self.clip_and_step()
         return loss.detach()
+
+    def clip_and_step(self) -> torch.Tensor:
+        """gradient all-reduce (N > 1) -> clip_grad_norm_ -> optimizer.step (kv_procedure.py:161-162); returns the
+        gradient norm as a device scalar.  With FlatAdam the clip scaling is folded into the step kernel."""
+        self.bucket.all_reduce_mean()
+        if isinstance(self.optimizer, FlatAdam):
+            total = self.bucket.norm()
+            self.optimizer.step(grad_norm=total.reshape(1), max_norm=float(self.max_grad_norm))
+        else:
+            total = self.bucket.clip_(self.max_grad_norm)
+            self.optimizer.step()
+        return total
 
     @torch.no_grad()
     def run_val_step(self, batch_sample: Dict[str, torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -138,7 +311,15 @@ class BuitlinOptimizer:
         return cls(**opt)
 
     def get_optimizer(self, parameters) -> torch.optim.Optimizer:
-        optimizer = getattr(torch.optim, self.type_optimizer)(parameters, **self.optimizer_args)
+        parameters = list(parameters)
+        args = dict(self.optimizer_args)
+        if (self.type_optimizer == "Adam" and parameters and isinstance(parameters[0], torch.Tensor)
+                and all(p.is_cuda and p.dtype == torch.float32 for p in parameters) and not args.get("amsgrad")):
+            for k in ("fused", "foreach", "capturable", "differentiable", "maximize"):
+                args.pop(k, None)
+            optimizer = FlatAdam(parameters, **args)         # same update rule, one kernel over a flat buffer
+        else:
+            optimizer = getattr(torch.optim, self.type_optimizer)(parameters, **args)
         if hasattr(self.learning_rate, "prepare"):
             self.learning_rate.prepare(optimizer)
         return optimizer

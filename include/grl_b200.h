@@ -215,6 +215,29 @@ int grl_selfatten_bwd(const void* dOut, const float* P, const float* o, const vo
                       const float* gamma, float* dS, void* df, void* dg, void* dh, float* dgamma_part,
                       int dtype, int B, int N, int H, int D, int Np, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Loss and optimizer of the KV train step (deterministic reductions; csrc/train_ops.cu).
+ * workspace: grl_reduce_workspace_bytes() bytes of scratch for the block partial sums.
+ * grl_ce_fwd:  loss_out[0] = sum_i w[y_i] (lse_i - x[i, y_i]) / sum_i w[y_i],  loss_out[1] = sum_i w[y_i] over the rows
+ *              with y_i != ignore_index (w = 1 when weight == NULL); lse[i] saved for the backward.
+ *              Replaces nn.CrossEntropyLoss()(pred.transpose(1, 2), target)  gnn/trainer/losses/cross_entropy_loss.py:19-35.
+ * grl_ce_bwd:  dlogits = grad_out[0] / loss_out[1] * w[y] * (softmax(x) - onehot(y)), 0 on ignored rows.
+ * grl_l2_norm: out[0] = ||x||_2 (the total norm of clip_grad_norm_  kv_procedure.py:161 over the flat gradient bucket).
+ * grl_adam_step: torch.optim.Adam.step (amsgrad = False) over flat p / g / m / v of n floats at 1-based `step`;
+ *              g is first multiplied by min(1, max_norm / (grad_norm[0] + 1e-6)) when grad_norm != NULL and
+ *              max_norm > 0 (clip fused into the step, no host sync) and written back.
+ *              Replaces the optimizer BuitlinOptimizer builds  gnn/trainer/optimizers/builtin_optimizer.py:22-26.
+ * ------------------------------------------------------------------------------------------ */
+size_t grl_reduce_workspace_bytes(void);
+int grl_ce_fwd(const float* logits, int64_t ld, const int64_t* target, const float* weight, int64_t ignore_index,
+               int64_t M, int C, float* lse, float* loss_out, void* workspace, void* stream);
+int grl_ce_bwd(const float* logits, int64_t ld, const int64_t* target, const float* weight, int64_t ignore_index,
+               int64_t M, int C, const float* lse, const float* loss_out, const float* grad_out,
+               float* dlogits, int64_t ldd, void* stream);
+int grl_l2_norm(const float* x, int64_t n, float* out, void* workspace, void* stream);
+int grl_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                  float eps, float weight_decay, int64_t step, const float* grad_norm, float max_norm, void* stream);
+
 /* column sums  out[c] = sum_m X[m, c]  (bias gradient), fp32 output; out must be zeroed by the caller. */
 int grl_colsum(const void* X, int64_t ldx, int dtype, int64_t M, int C, float* out, void* stream);
 

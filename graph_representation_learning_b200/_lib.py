@@ -73,13 +73,18 @@ SIGNATURES = {
                             c_void_p, c_int64, c_int, c_int, c_int, c_int,
                             c_void_p, c_uint32, c_float, c_void_p, c_uint64, c_uint64, c_void_p]),
     "grl_gemm_x3_set_promo": (c_int, [c_int]),
+    "grl_gemm_bc_set_promo": (c_int, [c_int]),
     "grl_gemm_tn_workspace_bytes": (c_size_t, [c_int, c_int]),
     "grl_gemm_tn": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int64,
                             c_void_p, c_size_t, c_void_p]),
     "grl_split_tf32": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "grl_split_act_mn": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "grl_gemm_tn_bc": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p,
+                               c_int, c_void_p, c_size_t, c_void_p]),
+    "grl_split_tf32_mix": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
 }
 
-GEMM_BF16, GEMM_TF32, GEMM_TF32X3 = 0, 1, 2
+GEMM_BF16, GEMM_TF32, GEMM_TF32X3, GEMM_TF32_BF16C = 0, 1, 2, 3
 
 _lib = None
 

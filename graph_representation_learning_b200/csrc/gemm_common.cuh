@@ -7,7 +7,7 @@
 
 namespace grl {
 
-enum GemmMode { kBF16 = 0, kTF32 = 1, kTF32X3 = 2 };
+enum GemmMode { kBF16 = 0, kTF32 = 1, kTF32X3 = 2, kTF32BC = 3 };
 
 struct GemmParams {
     int M, N;
@@ -187,5 +187,6 @@ struct GemmArgs {
 };
 
 int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_x3_tcgen05.cu
+int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_bc_tcgen05.cu
 
 }  // namespace grl

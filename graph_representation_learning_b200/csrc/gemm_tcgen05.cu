@@ -207,9 +207,9 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
                            void* stream) {
     GRL_CHECK_ARG(A0 && B0 && C, GRL_E_BADARG, "grl_gemm_nt: null pointer");
     GRL_CHECK_ARG(M > 0 && N > 0 && K0 > 0 && K1 >= 0, GRL_E_BADARG, "grl_gemm_nt: bad shape M=%d N=%d K0=%d K1=%d", M, N, K0, K1);
-    GRL_CHECK_ARG(mode >= kBF16 && mode <= kTF32X3, GRL_E_BADARG, "grl_gemm_nt: bad mode %d", mode);
+    GRL_CHECK_ARG(mode >= kBF16 && mode <= kTF32BC, GRL_E_BADARG, "grl_gemm_nt: bad mode %d", mode);
     GRL_CHECK_ARG(K1 == 0 || (A1 && B1), GRL_E_BADARG, "grl_gemm_nt: second K segment without operands");
-    GRL_CHECK_ARG(mode != kTF32X3 || (B0_lo && (K1 == 0 || B1_lo)), GRL_E_BADARG, "grl_gemm_nt: TF32X3 needs the low parts of B");
+    GRL_CHECK_ARG(mode < kTF32X3 || (B0_lo && (K1 == 0 || B1_lo)), GRL_E_BADARG, "grl_gemm_nt: TF32X3 / TF32_BF16C need the low / packed parts of B");
     GRL_CHECK_ARG(out_dtype == GRL_F32 || out_dtype == GRL_BF16, GRL_E_UNSUP, "grl_gemm_nt: output dtype %d", out_dtype);
     GRL_CHECK_ARG(!(flags & GRL_EPI_BIAS) || bias, GRL_E_BADARG, "grl_gemm_nt: BIAS flag without bias");
     GRL_CHECK_ARG(p >= 0.0f && p < 1.0f, GRL_E_BADARG, "grl_gemm_nt: p outside [0,1)");
@@ -220,7 +220,7 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
     GRL_CHECK_ARG(lda0 % ld_mult == 0 && ldb0 % ld_mult == 0 && (K1 == 0 || (lda1 % ld_mult == 0 && ldb1 % ld_mult == 0)),
                   GRL_E_ALIGN, "grl_gemm_nt: leading dimensions must be multiples of %lld elements (16 bytes)", (long long)ld_mult);
     GRL_CHECK_ARG(aligned_to(A0, 16) && aligned_to(B0, 16) && (K1 == 0 || (aligned_to(A1, 16) && aligned_to(B1, 16))) &&
-                      (mode != kTF32X3 || (aligned_to(B0_lo, 16) && (K1 == 0 || aligned_to(B1_lo, 16)))),
+                      (mode < kTF32X3 || (aligned_to(B0_lo, 16) && (K1 == 0 || aligned_to(B1_lo, 16)))),
                   GRL_E_ALIGN, "grl_gemm_nt: operand base pointers must be 16-byte aligned");
     GRL_CHECK_ARG(lda0 >= K0 && ldb0 >= K0 && (K1 == 0 || (lda1 >= K1 && ldb1 >= K1)), GRL_E_BADARG, "grl_gemm_nt: ld < K");
 
@@ -234,6 +234,7 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
     switch (mode) {
         case kBF16: return wide ? launch_gemm<kBF16, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kBF16, 128>(ga, gp, st) : launch_gemm<kBF16, 64>(ga, gp, st));
         case kTF32: return wide ? launch_gemm<kTF32, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kTF32, 128>(ga, gp, st) : launch_gemm<kTF32, 64>(ga, gp, st));
+        case kTF32BC: return launch_gemm_bc(ga, gp, st);
         default:    return launch_gemm_x3(ga, gp, st);
     }
 }

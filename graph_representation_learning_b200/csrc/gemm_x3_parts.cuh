@@ -1,0 +1,65 @@
+// Pieces shared by the fp32-grade GEMM kernels (gemm_x3_tcgen05.cu: three tf32 products; gemm_bc_tcgen05.cu: tf32 main
+// product + bf16 correction product with the activation operand in TMEM): tile configuration, the register epilogue of
+// the drain warps, the split-K plan and reduction of the weight-gradient kernels.
+#pragma once
+#include "gemm_common.cuh"
+
+namespace grl {
+using namespace sm100;
+
+struct X3Cfg {
+    static constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 32, UMMA_K = 8;
+    static constexpr int TILE_BYTES = 128 * 128;                    // every operand tile is 16 KB
+    static constexpr int STAGE_BYTES = 4 * TILE_BYTES;              // A | B(_hi) | B_lo | A_lo
+    static constexpr int STAGES = 3;
+    static constexpr int DRAIN_WARPS = 8;                           // two per TMEM lane quarter: 64 columns each
+    static constexpr int DRAIN_COLS = BLOCK_N / (DRAIN_WARPS / 4);
+    static constexpr int EPI_COLS = 16;                             // columns transposed per pass
+    static constexpr int EPI_PITCH = EPI_COLS + 4;                  // floats (conflict-free STS.128 rows)
+    static constexpr int EPI_BYTES = DRAIN_WARPS * 32 * EPI_PITCH * 4;   // one 32 x 16 transposition buffer per drain warp
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+    static constexpr int TMEM_COLS = 512;                           // main0 | main1 | small | (unused)
+    static constexpr int THREADS = 64 + 128 + 32 * DRAIN_WARPS;
+};
+
+// Epilogue of one drain warp over ITS 32 accumulator rows x DRAIN_COLS columns held in registers (one row per lane):
+// 16-column chunks are transposed through a private 32 x 20 fp32 buffer so that every global store instruction writes
+// eight 64-byte row segments.  Private buffer + registers only: the operand stages keep streaming the NEXT tile.
+__device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const float (&acc)[X3Cfg::DRAIN_COLS], float* buf,
+                                                   int row0, int n0, int lane) {
+    constexpr int PITCH = X3Cfg::EPI_PITCH, CH = X3Cfg::EPI_COLS;
+    const bool vec_ok = epilogue_vec_ok(p);
+    const int rsub = lane >> 2, c4 = (lane & 3) * 4;
+    const int rows = min(32, p.M - row0);
+#pragma unroll
+    for (int c0 = 0; c0 < X3Cfg::DRAIN_COLS; c0 += CH) {
+        if (n0 + c0 >= p.N) break;                                  // warp-uniform
+        __syncwarp();                                               // readers of the previous chunk are done
+#pragma unroll
+        for (int j = 0; j < CH; j += 4)
+            *reinterpret_cast<float4*>(buf + lane * PITCH + j) = make_float4(acc[c0 + j], acc[c0 + j + 1], acc[c0 + j + 2], acc[c0 + j + 3]);
+        __syncwarp();
+        const int col = n0 + c0 + c4;
+        if (col < p.N) {
+            float b4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            if (p.flags & GRL_EPI_BIAS) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (col + t < p.N) b4[t] = __ldg(p.bias + col + t);
+            }
+#pragma unroll
+            for (int rr = rsub; rr < 32; rr += 8) {
+                if (rr < rows) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(buf + rr * PITCH + c4);
+                    float v[4] = {t4.x + b4[0], t4.y + b4[1], t4.z + b4[2], t4.w + b4[3]};
+                    epilogue_store4(p, row0 + rr, col, v, vec_ok);
+                }
+            }
+        }
+    }
+}
+
+int tn_plan_splits(int tiles, int kblocks);                                                        // gemm_x3_tcgen05.cu
+int launch_reduce_splits(const float* ws, float* out, int64_t n, int splits, cudaStream_t st);      // gemm_x3_tcgen05.cu
+
+}  // namespace grl

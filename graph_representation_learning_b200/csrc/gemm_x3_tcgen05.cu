@@ -22,25 +22,10 @@
 // Warp roles (448 threads): 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = operand splitter,
 // 6..13 = accumulator drain + fused epilogue (two warps per TMEM lane quarter, 64 columns each).  The kernel is
 // persistent: the TMA / split / MMA pipeline runs into the next tile while the drain warps finish the current one.
-#include "gemm_common.cuh"
+#include "gemm_x3_parts.cuh"
 
 namespace grl {
 using namespace sm100;
-
-struct X3Cfg {
-    static constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 32, UMMA_K = 8;
-    static constexpr int TILE_BYTES = 128 * 128;                    // every operand tile is 16 KB
-    static constexpr int STAGE_BYTES = 4 * TILE_BYTES;              // A | B(_hi) | B_lo | A_lo
-    static constexpr int STAGES = 3;
-    static constexpr int DRAIN_WARPS = 8;                           // two per TMEM lane quarter: 64 columns each
-    static constexpr int DRAIN_COLS = BLOCK_N / (DRAIN_WARPS / 4);
-    static constexpr int EPI_COLS = 16;                             // columns transposed per pass
-    static constexpr int EPI_PITCH = EPI_COLS + 4;                  // floats (conflict-free STS.128 rows)
-    static constexpr int EPI_BYTES = DRAIN_WARPS * 32 * EPI_PITCH * 4;   // one 32 x 16 transposition buffer per drain warp
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
-    static constexpr int TMEM_COLS = 512;                           // main0 | main1 | small | (unused)
-    static constexpr int THREADS = 64 + 128 + 32 * DRAIN_WARPS;
-};
 
 #define GRL_X3_RAW_HI (1u << 8)   // experiment: trust the tensor core to ignore the 13 low bits (no in-place hi write)
 
@@ -61,43 +46,6 @@ __device__ __forceinline__ void split_tile(uint8_t* raw, uint8_t* lo_tile, int t
         lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
         if (!raw_hi) a[idx] = hi;
         alo[idx] = lo;
-    }
-}
-
-// Epilogue of one drain warp over ITS 32 accumulator rows x DRAIN_COLS columns held in registers (one row per lane):
-// 16-column chunks are transposed through a private 32 x 20 fp32 buffer so that every global store instruction writes
-// eight 64-byte row segments.  Private buffer + registers only: the operand stages keep streaming the NEXT tile.
-__device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const float (&acc)[X3Cfg::DRAIN_COLS], float* buf,
-                                                   int row0, int n0, int lane) {
-    constexpr int PITCH = X3Cfg::EPI_PITCH, CH = X3Cfg::EPI_COLS;
-    const bool vec_ok = epilogue_vec_ok(p);
-    const int rsub = lane >> 2, c4 = (lane & 3) * 4;
-    const int rows = min(32, p.M - row0);
-#pragma unroll
-    for (int c0 = 0; c0 < X3Cfg::DRAIN_COLS; c0 += CH) {
-        if (n0 + c0 >= p.N) break;                                  // warp-uniform
-        __syncwarp();                                               // readers of the previous chunk are done
-#pragma unroll
-        for (int j = 0; j < CH; j += 4)
-            *reinterpret_cast<float4*>(buf + lane * PITCH + j) = make_float4(acc[c0 + j], acc[c0 + j + 1], acc[c0 + j + 2], acc[c0 + j + 3]);
-        __syncwarp();
-        const int col = n0 + c0 + c4;
-        if (col < p.N) {
-            float b4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-            if (p.flags & GRL_EPI_BIAS) {
-#pragma unroll
-                for (int t = 0; t < 4; ++t)
-                    if (col + t < p.N) b4[t] = __ldg(p.bias + col + t);
-            }
-#pragma unroll
-            for (int rr = rsub; rr < 32; rr += 8) {
-                if (rr < rows) {
-                    const float4 t4 = *reinterpret_cast<const float4*>(buf + rr * PITCH + c4);
-                    float v[4] = {t4.x + b4[0], t4.y + b4[1], t4.z + b4[2], t4.w + b4[3]};
-                    epilogue_store4(p, row0 + rr, col, v, vec_ok);
-                }
-            }
-        }
     }
 }
 
@@ -382,10 +330,11 @@ extern "C" int grl_gemm_x3_set_promo(int promo) {
     return 0;
 }
 
+namespace grl {
 // Split-K plan of the TN kernel: all tiles * splits CTAs run in waves of kNumSMs, a CTA costs its K-blocks plus a fixed
 // prologue + drain + epilogue (~12 K-blocks of time).  One wave with fewer CTAs than SMs can lose to two fuller waves
 // (gcn3 dW: 56 tiles -> 2 splits = 112 CTAs = 2000 K-blocks each, against 5 splits = 280 CTAs = 2 waves of 800).
-static int tn_plan_splits(int tiles, int kblocks) {
+int tn_plan_splits(int tiles, int kblocks) {
     constexpr int kOverheadKb = 12, kMaxSplits = 16;
     int cap = kNumSMs / tiles;
     if (cap < kMaxSplits) cap = kMaxSplits;
@@ -403,6 +352,15 @@ static int tn_plan_splits(int tiles, int kblocks) {
     }
     return best;
 }
+
+int launch_reduce_splits(const float* ws, float* out, int64_t n, int splits, cudaStream_t st) {
+    int blocks = static_cast<int>((n + 255) / 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    reduce_splits_kernel<<<blocks, 256, 0, st>>>(ws, out, n, splits);
+    GRL_LAUNCH_CHECK("reduce_splits_kernel");
+    return 0;
+}
+}  // namespace grl
 
 extern "C" size_t grl_gemm_tn_workspace_bytes(int Ma, int Nb) {
     // one [Ma, Nb] fp32 slab per split; splits <= max(16, kNumSMs / tiles)
@@ -440,10 +398,5 @@ extern "C" int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t 
     gemm_x3_kernel<true><<<dim3(tiles, splits), Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_x3_promo, kb_per_split, tiles, tA,
                                                                                     tB, tB, tA, tB, tB);
     GRL_LAUNCH_CHECK("gemm_x3_kernel<TN>");
-    const int64_t n = static_cast<int64_t>(Ma) * Nb;
-    int blocks = static_cast<int>((n + 255) / 256);
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    reduce_splits_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(workspace), C, n, splits);
-    GRL_LAUNCH_CHECK("reduce_splits_kernel");
-    return 0;
+    return launch_reduce_splits(static_cast<const float*>(workspace), C, static_cast<int64_t>(Ma) * Nb, splits, st);
 }

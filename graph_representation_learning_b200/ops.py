@@ -109,16 +109,25 @@ def colsum(X: torch.Tensor) -> torch.Tensor:
 # dense contractions
 # ----------------------------------------------------------------------------------------------
 class GemmConfig:
-    """fp32_mode: how fp32 operands go through the tensor cores -- "tf32x3" (error-compensated, fp32-grade,
-    the parity mode and default) or "tf32" (single pass, ~1e-3).  bf16 operands always use kind::f16."""
+    """How fp32 operands go through the tensor cores: "tf32x3" (error-compensated, three tf32 products, 4-5e-7
+    norm-wise), "tf32bc" (tf32 main product + the two correction products as one bf16 product, activation operand
+    through TMEM: 6-7e-7, 1.2-1.6x faster) or "tf32" (single pass, ~1e-3).  bf16 operands always use kind::f16.
+
+    ``fp32_mode`` serves the FORWARD products, whose outputs meet ReLU thresholds: a pre-activation within the GEMM's
+    error of zero flips its derivative and moves whole gradient tensors by 1e-4 .. 1e-3 (tests/test_gpu_parity.py,
+    scripts/mode_noise.py), so the forward keeps the most accurate mode.  ``fp32_mode_bwd`` serves dX = dZ W and
+    dW = X^T dZ: the backward pass is linear in dZ, its GEMM error stays a 7e-7 relative perturbation of the gradient,
+    so it takes the faster mode."""
     fp32_mode = "tf32x3"
+    fp32_mode_bwd = "tf32bc"
+    _modes = {"tf32x3": 2, "tf32bc": 3, "tf32": 1}
 
 
-def _mode_for(dtype: torch.dtype) -> int:
+def _mode_for(dtype: torch.dtype, fp32_mode: Optional[str] = None) -> int:
     if dtype == torch.bfloat16:
         return _lib.GEMM_BF16
     if dtype == torch.float32:
-        return _lib.GEMM_TF32X3 if GemmConfig.fp32_mode == "tf32x3" else _lib.GEMM_TF32
+        return GemmConfig._modes[fp32_mode or GemmConfig.fp32_mode]
     raise _lib.GrlError(f"GEMM operands must be fp32 or bf16, got {dtype}")
 
 
@@ -143,6 +152,14 @@ def _prep_weight(b_view: torch.Tensor, dtype: torch.dtype, mode: int):
     N, K = b_view.shape
     m = _ld_multiple(dtype)
     Kp = (K + m - 1) // m * m
+    if mode == _lib.GEMM_TF32_BF16C:
+        src = b_view.float().contiguous()
+        hi = torch.empty(N, Kp, dtype=torch.float32, device=b_view.device)
+        packed = torch.empty(N, 2 * Kp, dtype=torch.bfloat16, device=b_view.device)
+        _lib.check(_lib.load().grl_split_tf32_mix(src.data_ptr(), K, hi.data_ptr(), Kp, packed.data_ptr(), 2 * Kp, N, K,
+                                                  _lib.stream_ptr(src.device)), "grl_split_tf32_mix")
+        _lib.count_launch(1)
+        return hi[:, :K], packed
     if mode != _lib.GEMM_TF32X3:
         if Kp == K:
             return b_view.to(dtype).contiguous(), None
@@ -160,13 +177,14 @@ def _prep_weight(b_view: torch.Tensor, dtype: torch.dtype, mode: int):
 
 def gemm_nt(a_list: Sequence[torch.Tensor], b_list: Sequence[torch.Tensor], out_dtype: Optional[torch.dtype] = None,
             bias: Optional[torch.Tensor] = None, relu: bool = False, p: float = 0.0, mask: Optional[torch.Tensor] = None,
-            seed: int = 0, stream_id: int = 0) -> torch.Tensor:
-    """C[M, N] = epilogue(sum_k a_k[M, K_k] @ b_k[N, K_k]^T) on the tcgen05 kernel (csrc/gemm_tcgen05.cu).
-    ``a_k`` are activations (row-major views), ``b_k`` are [N, K_k] views of weights in any layout."""
+            seed: int = 0, stream_id: int = 0, fp32_mode: Optional[str] = None) -> torch.Tensor:
+    """C[M, N] = epilogue(sum_k a_k[M, K_k] @ b_k[N, K_k]^T) on the tcgen05 kernels (csrc/gemm_tcgen05.cu,
+    gemm_x3_tcgen05.cu, gemm_bc_tcgen05.cu).  ``a_k`` are activations (row-major views), ``b_k`` are [N, K_k] views
+    of weights in any layout.  ``fp32_mode`` overrides ``GemmConfig.fp32_mode`` for this product."""
     if not 1 <= len(a_list) <= 2 or len(a_list) != len(b_list):
         raise _lib.GrlError("gemm_nt takes one or two K segments")
     cdt = a_list[0].dtype
-    mode = _mode_for(cdt)
+    mode = _mode_for(cdt, fp32_mode)
     M, N = a_list[0].shape[0], b_list[0].shape[0]
     out_dtype = out_dtype or cdt
     C = torch.empty(M, N, dtype=out_dtype, device=a_list[0].device)
@@ -196,17 +214,18 @@ def gemm_nt(a_list: Sequence[torch.Tensor], b_list: Sequence[torch.Tensor], out_
 _tn_workspace = {}
 
 
-def gemm_tn(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+def gemm_tn(a: torch.Tensor, b: torch.Tensor, fp32_mode: Optional[str] = None) -> torch.Tensor:
     """dW[Ma, Nb] = a[R, Ma]^T @ b[R, Nb], fp32 output: the weight-gradient contraction over the node dimension.
 
-    fp32 operands: MN-major TF32X3 tcgen05 kernel with split-K (csrc/gemm_x3_tcgen05.cu, grl_gemm_tn).
+    fp32 operands, split-K over R with a deterministic reduce: "tf32bc" (default, ``GemmConfig.fp32_mode_bwd``) = the
+    TMEM-operand kernel (csrc/gemm_bc_tcgen05.cu, grl_split_act_mn + grl_gemm_tn_bc); "tf32x3" = the MN-major
+    three-product kernel (csrc/gemm_x3_tcgen05.cu, grl_gemm_tn).
     bf16 operands: TRANSITIONAL (DESIGN.md "GEMM status") cuBLAS via torch.mm until the bf16 MN-major kernel lands."""
     if a.dtype != torch.float32:
         return torch.mm(a.t(), b, out_dtype=torch.float32)
     a, b = _tma_ready(a), _tma_ready(b)
     R, Ma = a.shape
     Nb = b.shape[1]
-    C = torch.empty(Ma, Nb, dtype=torch.float32, device=a.device)
     lib = _lib.load()
     ws_bytes = lib.grl_gemm_tn_workspace_bytes(Ma, Nb)
     key = (a.device, torch.cuda.current_stream(a.device).cuda_stream)
@@ -214,6 +233,23 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     if ws is None or ws.numel() < ws_bytes:          # one reusable split-K workspace per (device, stream)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=a.device)
         _tn_workspace[key] = ws
+    C = torch.empty(Ma, Nb, dtype=torch.float32, device=a.device)
+    if (fp32_mode or GemmConfig.fp32_mode_bwd) == "tf32bc":
+        # the WIDE operand goes through TMEM, the narrow one is split once in HBM; the product is stored transposed
+        # when the caller's first operand is the narrow one
+        swap = Nb > Ma
+        wide, narrow = (b, a) if swap else (a, b)
+        Wn, Nn = wide.shape[1], narrow.shape[1]
+        ldp = (Nn + 7) // 8 * 8
+        hi = torch.empty(R, ldp, dtype=torch.float32, device=a.device)
+        packed = torch.empty((R + 31) // 32 * 64, ldp, dtype=torch.bfloat16, device=a.device)
+        _lib.check(lib.grl_split_act_mn(narrow.data_ptr(), narrow.stride(0), hi.data_ptr(), ldp, packed.data_ptr(), ldp,
+                                        R, Nn, _lib.stream_ptr(a.device)), "grl_split_act_mn")
+        _lib.check(lib.grl_gemm_tn_bc(wide.data_ptr(), wide.stride(0), Wn, hi.data_ptr(), ldp, packed.data_ptr(), ldp, Nn,
+                                      R, C.data_ptr(), 1 if swap else 0, ws.data_ptr(), ws.numel(),
+                                      _lib.stream_ptr(a.device)), "grl_gemm_tn_bc")
+        _lib.count_launch(3)
+        return C
     _lib.check(lib.grl_gemm_tn(a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), C.data_ptr(), Nb, Ma, Nb, R,
                                ws.data_ptr(), ws.numel(), _lib.stream_ptr(a.device)), "grl_gemm_tn")
     _lib.count_launch(2)
@@ -290,7 +326,8 @@ class _LinearAct(torch.autograd.Function):
         d_weight = d_bias = None
         if ctx.needs_input_grad[0]:
             # fp32 master gradient whatever the compute dtype; [K, N] for h_weights, [N, K] for nn.Linear
-            parts = [gemm_tn(x, dZ) if weight_is_kn else gemm_tn(dZ, x) for x in xs]
+            bwd = GemmConfig.fp32_mode_bwd
+            parts = [gemm_tn(x, dZ, bwd) if weight_is_kn else gemm_tn(dZ, x, bwd) for x in xs]
             d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
         if has_bias and ctx.needs_input_grad[1]:
             d_bias = colsum(dZ)
@@ -301,7 +338,7 @@ class _LinearAct(torch.autograd.Function):
             if ctx.needs_input_grad[8 + k]:
                 # dX_k[M, K_k] = dZ[M, N] @ W_k with W_k presented as the NT "B" operand [K_k, N]
                 wk = weight[off:off + K, :] if weight_is_kn else weight[:, off:off + K].t()
-                dxs.append(gemm_nt([dZ], [wk]))
+                dxs.append(gemm_nt([dZ], [wk], fp32_mode=GemmConfig.fp32_mode_bwd))
             else:
                 dxs.append(None)
             off += K

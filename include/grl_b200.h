@@ -171,13 +171,18 @@ int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void* Y, int64_
  * segments), F.relu and nn.Dropout(p=0.5) after them, and the dX = dZ * W products of their autograd.
  * mode: GRL_GEMM_BF16 (bf16 operands), GRL_GEMM_TF32 (fp32 operands, single tf32 pass, ~1e-3),
  *       GRL_GEMM_TF32X3 (fp32 operands, error-compensated 3-pass, fp32-grade ~1e-6; needs B0_lo / B1_lo =
- *       the low parts of B from grl_split_tf32, B0/B1 being the high parts).
+ *       the low parts of B from grl_split_tf32, B0/B1 being the high parts),
+ *       GRL_GEMM_TF32_BF16C (fp32 operands; main product A_hi*B_hi in tf32, the two correction products as ONE
+ *       bf16 product over a doubled K: 8 instead of 12 MMA steps per K-block, ~1e-6 norm-wise.  B0/B1 = the
+ *       round-to-nearest tf32 high parts and B0_lo/B1_lo = the packed bf16 operands of grl_split_tf32_mix, whose
+ *       row pitch must be 2*ldb bf16 elements).
  * Alignment (TMA): base pointers 16-byte aligned, lda/ldb multiples of 16 bytes.  C: fp32 or bf16, any ldc >= N.
  * Epilogue flags / dropout bits exactly as grl_bias_act_dropout_fwd (same Philox indexing m*N + n).
  * ------------------------------------------------------------------------------------------ */
 #define GRL_GEMM_BF16   0
 #define GRL_GEMM_TF32   1
 #define GRL_GEMM_TF32X3 2
+#define GRL_GEMM_TF32_BF16C 3
 int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo, int64_t ldb0, int K0,
                 const void* A1, int64_t lda1, const void* B1, const void* B1_lo, int64_t ldb1, int K1,
                 void* C, int64_t ldc, int out_dtype, int M, int N, int mode,
@@ -186,6 +191,7 @@ int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo,
 /* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
  * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2. */
 int grl_gemm_x3_set_promo(int promo);
+int grl_gemm_bc_set_promo(int promo);   /* the same knob of the GRL_GEMM_TF32_BF16C kernels; default 4 */
 /* Weight-gradient GEMM ("TN", reduction over the node dimension R, both operands MN-major fp32 activations):
  *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]        fp32-grade TF32X3 on tcgen05, split-K over R, deterministic reduce.
  * Replaces autograd's dW = new_V^T * dOut / dOut^T * X of gnn/models/networks/robust_gcn.py:50 and of every
@@ -193,6 +199,20 @@ int grl_gemm_x3_set_promo(int promo);
 size_t grl_gemm_tn_workspace_bytes(int Ma, int Nb);
 int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                 int Ma, int Nb, int64_t R, void* workspace, size_t workspace_bytes, void* stream);
+/* The same contraction in GRL_GEMM_TF32_BF16C arithmetic, activation operand A through TMEM:
+ *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]   (transpose_out = 0)      or   C[Nb, Ma] = its transpose (transpose_out = 1)
+ * A = the WIDE operand (raw fp32, lda % 4 == 0); B = the narrow one, split once by grl_split_act_mn into B_hi
+ * (fp32 [R, Nb], pitch ldb_hi) and B_packed (bf16 [ceil(R/32)*64, ldb_packed]).  C dense.  Workspace as grl_gemm_tn. */
+int grl_split_act_mn(const float* src, int64_t ld_src, float* hi, int64_t ld_hi, void* packed, int64_t ld_packed,
+                     int64_t R, int cols, void* stream);
+int grl_gemm_tn_bc(const float* A, int64_t lda, int Ma, const float* B_hi, int64_t ldb_hi, const void* B_packed,
+                   int64_t ldb_packed, int Nb, int64_t R, float* C, int transpose_out,
+                   void* workspace, size_t workspace_bytes, void* stream);
+/* Weight operand of GRL_GEMM_TF32_BF16C: hi[rows, cols] (pitch ld_hi) = src rounded to nearest tf32; packed = bf16
+ * [rows, 2*ceil4(cols)] (pitch ld_packed bf16 elements, multiple of 8): 16-byte chunk c of a row holds
+ * {hi[4c..4c+3], lo[4c..4c+3]} with lo = src - hi; entries past cols are zero. */
+int grl_split_tf32_mix(const float* src, int64_t ld_src, float* hi, int64_t ld_hi, void* packed, int64_t ld_packed,
+                       int64_t rows, int cols, void* stream);
 /* hi = src with the 13 low mantissa bits cleared (exactly representable in tf32), lo = src - hi. */
 int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst,
                    int64_t rows, int cols, void* stream);

@@ -1,6 +1,7 @@
 """tcgen05 GEMM (csrc/gemm_tcgen05.cu) against an fp64 torch matmul of the same operands.
 
-Tolerances: TF32X3 (the fp32 parity mode) 2e-6 norm-wise; single-pass TF32 2e-3; BF16 operands are quantised
+Tolerances: the fp32 parity modes TF32X3 (three tf32 products) and TF32_BF16C (tf32 + bf16 correction product, activation
+operand through TMEM; the default) 2e-6 norm-wise; single-pass TF32 2e-3; BF16 operands are quantised
 first, so only the fp32 accumulation differs from the fp64 product: 1e-5 (2e-2 once the OUTPUT is bf16)."""
 import pytest
 import torch
@@ -22,7 +23,7 @@ def _mk(M, N, K, gen, dev, dtype):
 
 
 @pytest.mark.parametrize("M,N,K", SHAPES)
-@pytest.mark.parametrize("mode", ["tf32x3", "tf32", "bf16"])
+@pytest.mark.parametrize("mode", ["tf32bc", "tf32x3", "tf32", "bf16"])
 def test_gemm_nt_plain(M, N, K, mode):
     from graph_representation_learning_b200 import ops
     dev = torch.device("cuda:0")
@@ -30,17 +31,18 @@ def test_gemm_nt_plain(M, N, K, mode):
     dtype = torch.bfloat16 if mode == "bf16" else torch.float32
     a, b = _mk(M, N, K, gen, dev, dtype)
     ref = a.double() @ b.double().t()
-    ops.GemmConfig.fp32_mode = mode if mode != "bf16" else "tf32x3"
+    prev = ops.GemmConfig.fp32_mode
+    ops.GemmConfig.fp32_mode = mode if mode != "bf16" else prev
     try:
         out = ops.gemm_nt([a.to(dev, dtype)], [b.to(dev, dtype)], out_dtype=torch.float32)
     finally:
-        ops.GemmConfig.fp32_mode = "tf32x3"
-    tol = {"tf32x3": 2e-6, "tf32": 2e-3, "bf16": 1e-5}[mode]
+        ops.GemmConfig.fp32_mode = prev
+    tol = {"tf32bc": 2e-6, "tf32x3": 2e-6, "tf32": 2e-3, "bf16": 1e-5}[mode]
     assert out.shape == (M, N)
     assert rel_err(out.cpu(), ref) < tol
 
 
-@pytest.mark.parametrize("mode", ["tf32x3", "bf16"])
+@pytest.mark.parametrize("mode", ["tf32bc", "tf32x3", "bf16"])
 def test_gemm_nt_two_segments_strided_views_and_epilogue(mode):
     """virtual concat [x1 | x2] @ W^T with W an [N, K1+K2] nn.Linear weight, x1/x2 column slices of wider buffers,
     bias + ReLU + injected dropout mask fused."""
@@ -57,10 +59,15 @@ def test_gemm_nt_two_segments_strided_views_and_epilogue(mode):
     x1, x2 = big1[:, 64:], big2[:, :K2]
     ref = torch.relu(torch.cat([x1, x2], 1).double() @ W.double().t() + bias.double()) * keep / 0.5
     d1, d2, dW = big1.to(dev), big2.to(dev), W.to(dev)
-    out = ops.gemm_nt([d1[:, 64:], d2[:, :K2]], [dW[:, :K1], dW[:, K1:]], bias=bias.to(dev), relu=True, p=0.5,
-                      mask=keep.to(dev, torch.uint8).contiguous())
+    prev = ops.GemmConfig.fp32_mode
+    ops.GemmConfig.fp32_mode = mode if mode != "bf16" else prev
+    try:
+        out = ops.gemm_nt([d1[:, 64:], d2[:, :K2]], [dW[:, :K1], dW[:, K1:]], bias=bias.to(dev), relu=True, p=0.5,
+                          mask=keep.to(dev, torch.uint8).contiguous())
+    finally:
+        ops.GemmConfig.fp32_mode = prev
     assert out.dtype == dtype
-    assert rel_err(out.cpu(), ref) < (2e-6 if mode == "tf32x3" else 2e-2)
+    assert rel_err(out.cpu(), ref) < (2e-6 if mode != "bf16" else 2e-2)
 
 
 def test_gemm_nt_kn_weight_and_philox_matches_unfused_epilogue():
@@ -99,20 +106,37 @@ def test_gemm_large_k_tail_and_m_tail_fp32_grade():
 
 
 @pytest.mark.parametrize("R,Ma,Nb", [(1000, 256, 128), (128, 128, 128), (33, 40, 24), (5000, 1792, 256), (777, 53, 1280),
-                                     (20000, 300, 256)])
-def test_gemm_tn_weight_gradient(R, Ma, Nb):
-    """dW = A^T B over the node dimension (MN-major operands, split-K, deterministic reduce), fp32-grade."""
+                                     (20000, 300, 256), (4100, 16, 128), (1000, 129, 7)])
+@pytest.mark.parametrize("mode", ["tf32bc", "tf32x3"])
+def test_gemm_tn_weight_gradient(R, Ma, Nb, mode):
+    """dW = A^T B over the node dimension (split-K, deterministic reduce), fp32-grade, both parity modes; covers the
+    wide-operand swap + transposed store of the TMEM kernel (Nb > Ma), reduction tails (R % 32 != 0) and narrow operands
+    whose width is not a multiple of 8."""
     from graph_representation_learning_b200 import ops
     dev = torch.device("cuda:0")
     gen = torch.Generator().manual_seed(R + Ma + Nb)
     a = torch.randn(R, Ma, generator=gen)
     b = torch.randn(R, Nb, generator=gen)
     ref = a.double().t() @ b.double()
-    out = ops.gemm_tn(a.to(dev), b.to(dev))
+    out = ops.gemm_tn(a.to(dev), b.to(dev), fp32_mode=mode)
+    again = ops.gemm_tn(a.to(dev), b.to(dev), fp32_mode=mode)
     assert out.shape == (Ma, Nb) and out.dtype == torch.float32
     assert rel_err(out.cpu(), ref) < 2e-6
-    again = ops.gemm_tn(a.to(dev), b.to(dev))
     assert torch.equal(out, again)          # split-K partials are reduced in a fixed order
+
+
+def test_gemm_bc_small_magnitudes_keep_fp32_grade():
+    """gradient-sized operands (1e-6): the bf16 correction terms share fp32's exponent range, nothing underflows"""
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(5)
+    a = torch.randn(2000, 256, generator=gen) * 1e-6
+    b = torch.randn(384, 256, generator=gen) * 1e-3
+    out = ops.gemm_nt([a.to(dev)], [b.to(dev)], fp32_mode="tf32bc")
+    assert rel_err(out.cpu(), a.double() @ b.double().t()) < 2e-6
+    dz = torch.randn(2000, 128, generator=gen) * 1e-7
+    dw = ops.gemm_tn(a.to(dev), dz.to(dev), fp32_mode="tf32bc")
+    assert rel_err(dw.cpu(), a.double().t() @ dz.double()) < 2e-6
 
 
 def test_gemm_tn_strided_operands_emb1_like():

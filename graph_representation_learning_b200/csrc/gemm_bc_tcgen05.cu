@@ -47,12 +47,15 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float first, float second) {   /
     return *reinterpret_cast<const uint32_t*>(&v);
 }
 
-template <bool kTN>
+// kX3 (NT only): the three-tf32-product arithmetic of gemm_x3_tcgen05.cu (a_hi = a truncated to tf32, corrections
+// a_lo*b_hi + a_hi*b_lo in tf32 against the fp32 low parts of grl_split_tf32) on this kernel's TMEM operand path.
+template <bool kTN, bool kX3>
 __global__ void __launch_bounds__(BcCfg::THREADS, 1)
 gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, const int n_tiles, const int transpose_out,
                const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmB0,
                const __grid_constant__ CUtensorMap tmBp0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ CUtensorMap tmBp1) {
+    static_assert(!(kTN && kX3), "the three-product arithmetic on the TMEM path exists for NT only");
     using Cfg = BcCfg;
     constexpr int STAGES = Cfg::STAGES, TA = Cfg::TA_STAGES, DRAIN_WARPS = X3Cfg::DRAIN_WARPS;
     extern __shared__ uint8_t smem_raw[];
@@ -137,7 +140,7 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                         const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
                         tma_load_2d(tile(s, T_A), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
                         tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
-                        tma_load_2d(tile(s, T_BP), seg1 ? &tmBp1 : &tmBp0, &full_bar[s], 2 * k_elem, n0);
+                        tma_load_2d(tile(s, T_BP), seg1 ? &tmBp1 : &tmBp0, &full_bar[s], kX3 ? k_elem : 2 * k_elem, n0);
                     }
                 }
             }
@@ -179,7 +182,12 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                             const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
                             const uint64_t koff_c = static_cast<uint64_t>(kTN ? k * 128 : k * 2);
                             umma_ts<true>(d_main, ta_hi + 8 * k, b_desc + koff, idesc, (i | k) != 0);
-                            umma_ts<false>(d_small, ta_pk + 8 * k, bp_desc + koff_c, idesc_c, (kk | k) != 0);
+                            if constexpr (kX3) {
+                                umma_ts<true>(d_small, ta_pk + 8 * k, b_desc + koff, idesc, (kk | k) != 0);    // a_lo * b_hi
+                                umma_ts<true>(d_small, ta_hi + 8 * k, bp_desc + koff, idesc, 1u);              // a_hi * b_lo
+                            } else {
+                                umma_ts<false>(d_small, ta_pk + 8 * k, bp_desc + koff_c, idesc_c, (kk | k) != 0);
+                            }
                         }
                         umma_commit(&empty_bar[s]);
                         umma_commit(&ta_empty[j]);
@@ -225,8 +233,13 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                         float lo[4];
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
-                            hi[4 * c + e] = tf32_rn_bits(w[e]);
+                            hi[4 * c + e] = kX3 ? (w[e] & 0xFFFFE000u) : tf32_rn_bits(w[e]);
                             lo[e] = __uint_as_float(w[e]) - __uint_as_float(hi[4 * c + e]);
+                        }
+                        if constexpr (kX3) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) pk[4 * c + e] = __float_as_uint(lo[e]);
+                            continue;
                         }
                         // packed chunk c = {lo[4c..4c+3], hi[4c..4c+3]} against B' chunk c = {b_hi[4c..], b_lo[4c..]}
                         pk[4 * c + 0] = pack_bf16x2(lo[0], lo[1]);
@@ -318,11 +331,11 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
 // pipe (0.59 ms for [128000x1792]x[1792x256]) and promo = 4 does not (0.50 ms) at 7.4e-7 instead of 6.9e-7.
 static int g_bc_promo = 4;
 
-template <bool kTN>
+template <bool kTN, bool kX3>
 static int ensure_bc_smem_attr() {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_bc_kernel<kTN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(gemm_bc_kernel<kTN, kX3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              BcCfg::SMEM_BYTES);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
         attr_set = true;
@@ -330,28 +343,37 @@ static int ensure_bc_smem_attr() {
     return 0;
 }
 
-// B*lo of GemmArgs = the packed bf16 weight operands [N, 2 * ceil4(K)] of grl_split_tf32_mix, row pitch 2 * ldb.
-int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st) {
+// x3 = false: B*lo of GemmArgs = the packed bf16 weight operands [N, 2 * ceil4(K)] of grl_split_tf32_mix, row pitch
+// 2 * ldb.  x3 = true: B*lo = the fp32 low parts of grl_split_tf32 (pitch ldb), three-product arithmetic.
+int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo_x3) {
     using Cfg = BcCfg;
     CUtensorMap tA0, tB0, tBp0, tA1, tB1, tBp1;
     int rc;
+    auto lo_map = [&](CUtensorMap* out, const void* ptr, int K, int64_t ldb) {
+        return x3 ? make_tmap_sw128(out, ptr, 4, p.N, K, ldb, Cfg::BLOCK_N)
+                  : make_tmap_sw128(out, ptr, 2, p.N, 2 * ((K + 3) / 4 * 4), 2 * ldb, Cfg::BLOCK_N);
+    };
     if ((rc = make_tmap_sw128(&tA0, a.A0, 4, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;
     if ((rc = make_tmap_sw128(&tB0, a.B0, 4, p.N, a.K0, a.ldb0, Cfg::BLOCK_N))) return rc;
-    if ((rc = make_tmap_sw128(&tBp0, a.B0lo, 2, p.N, 2 * ((a.K0 + 3) / 4 * 4), 2 * a.ldb0, Cfg::BLOCK_N))) return rc;
+    if ((rc = lo_map(&tBp0, a.B0lo, a.K0, a.ldb0))) return rc;
     tA1 = tA0; tB1 = tB0; tBp1 = tBp0;
     if (a.K1 > 0) {
         if ((rc = make_tmap_sw128(&tA1, a.A1, 4, p.M, a.K1, a.lda1, Cfg::BLOCK_M))) return rc;
         if ((rc = make_tmap_sw128(&tB1, a.B1, 4, p.N, a.K1, a.ldb1, Cfg::BLOCK_N))) return rc;
-        if ((rc = make_tmap_sw128(&tBp1, a.B1lo, 2, p.N, 2 * ((a.K1 + 3) / 4 * 4), 2 * a.ldb1, Cfg::BLOCK_N))) return rc;
+        if ((rc = lo_map(&tBp1, a.B1lo, a.K1, a.ldb1))) return rc;
     }
     p.kblocks0 = (a.K0 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K;
     p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
-    if ((rc = ensure_bc_smem_attr<false>())) return rc;
+    if ((rc = x3 ? ensure_bc_smem_attr<false, true>() : ensure_bc_smem_attr<false, false>())) return rc;
     const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
     const int n_tiles = tiles_m * tiles_n;
     const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;
-    gemm_bc_kernel<false><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_bc_promo, 0, n_tiles, 0, tA0, tB0, tBp0,
-                                                                      tA1, tB1, tBp1);
+    if (x3)
+        gemm_bc_kernel<false, true><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, promo_x3, 0, n_tiles, 0, tA0, tB0, tBp0,
+                                                                                tA1, tB1, tBp1);
+    else
+        gemm_bc_kernel<false, false><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_bc_promo, 0, n_tiles, 0, tA0, tB0, tBp0,
+                                                                                 tA1, tB1, tBp1);
     GRL_LAUNCH_CHECK("gemm_bc_kernel<NT>");
     return 0;
 }
@@ -481,8 +503,8 @@ extern "C" int grl_gemm_tn_bc(const float* A, int64_t lda, int Ma, const float* 
     splits = (p.kblocks0 + kb_per_split - 1) / kb_per_split;
     const size_t need = sizeof(float) * static_cast<size_t>(Ma) * Nb * splits;
     GRL_CHECK_ARG(workspace_bytes >= need, GRL_E_WORKSPACE, "grl_gemm_tn_bc: workspace %zu < %zu", workspace_bytes, need);
-    if ((rc = ensure_bc_smem_attr<true>())) return rc;
-    gemm_bc_kernel<true><<<dim3(tiles, splits), Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_bc_promo, kb_per_split, tiles,
+    if ((rc = ensure_bc_smem_attr<true, false>())) return rc;
+    gemm_bc_kernel<true, false><<<dim3(tiles, splits), Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, g_bc_promo, kb_per_split, tiles,
                                                                                     transpose_out, tA, tB, tBp, tA, tB, tBp);
     GRL_LAUNCH_CHECK("gemm_bc_kernel<TN>");
     return launch_reduce_splits(static_cast<const float*>(workspace), C, static_cast<int64_t>(Ma) * Nb, splits, st);

@@ -187,6 +187,6 @@ struct GemmArgs {
 };
 
 int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_x3_tcgen05.cu
-int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_bc_tcgen05.cu
+int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo_x3);   // gemm_bc_tcgen05.cu
 
 }  // namespace grl

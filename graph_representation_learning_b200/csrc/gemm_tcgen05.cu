@@ -234,7 +234,7 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
     switch (mode) {
         case kBF16: return wide ? launch_gemm<kBF16, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kBF16, 128>(ga, gp, st) : launch_gemm<kBF16, 64>(ga, gp, st));
         case kTF32: return wide ? launch_gemm<kTF32, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kTF32, 128>(ga, gp, st) : launch_gemm<kTF32, 64>(ga, gp, st));
-        case kTF32BC: return launch_gemm_bc(ga, gp, st);
+        case kTF32BC: return launch_gemm_bc(ga, gp, st, false, 0);
         default:    return launch_gemm_x3(ga, gp, st);
     }
 }

@@ -263,6 +263,8 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
 
 static int g_x3_promo = 2;
 static int g_x3_persistent = 1;   // 0: one CTA per tile (A/B experiments via grl_gemm_x3_set_promo(-1 / -2))
+static int g_x3_tmem_operand = 0; // 1: NT products run on the TMEM-operand kernel of gemm_bc_tcgen05.cu (-3); 0: here (-4, default:
+                                  // measured equal, scripts/gemm_x3_ab.py -- twelve tf32 MMAs per K-block dominate either way)
 
 template <bool kTN>
 static int ensure_smem_attr() {
@@ -278,6 +280,7 @@ static int ensure_smem_attr() {
 
 int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     using Cfg = X3Cfg;
+    if (g_x3_tmem_operand) return launch_gemm_bc(a, p, st, true, g_x3_promo);
     CUtensorMap tA0, tB0, tBlo0, tA1, tB1, tBlo1;
     int rc;
     if ((rc = make_tmap_sw128(&tA0, a.A0, 4, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;
@@ -320,6 +323,10 @@ using namespace grl;
 extern "C" int grl_gemm_x3_set_promo(int promo) {
     if (promo == -1 || promo == -2) {             // experiment switch: -1 = one CTA per tile, -2 = persistent (default)
         g_x3_persistent = promo == -2;
+        return 0;
+    }
+    if (promo == -3 || promo == -4) {             // -3 = activation operand through TMEM, -4 = shared memory (default)
+        g_x3_tmem_operand = promo == -3;
         return 0;
     }
     if (promo < 1 || promo > 1 << 20) {

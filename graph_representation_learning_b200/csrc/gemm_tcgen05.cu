@@ -169,6 +169,124 @@ static int launch_gemm(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     return 0;
 }
 
+// bf16 weight gradients: C[Ma, Nb] (fp32) = A[R, Ma]^T * B[R, Nb], both operands MN-major bf16 activations read in place
+// by TMA (two boxes of {64 columns, 64 reduction rows} per operand and K-block, SWIZZLE_128B = the tensor core's MN-major
+// 16-bit layout: 64-column atoms 8192 B apart, 8 reduction rows per 1024-byte swizzle pattern).  Split-K over R
+// (blockIdx.y) into a workspace, deterministic reduction by launch_reduce_splits.  Same warp roles as gemm_nt_kernel.
+struct TnBf16Cfg {
+    static constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 64, UMMA_K = 16;
+    static constexpr int TILE_BYTES = 128 * 128;
+    static constexpr int STAGE_BYTES = 2 * TILE_BYTES;
+    static constexpr int STAGES = 6;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static constexpr int TMEM_COLS = 128;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tn_bf16_kernel(const GemmParams p, const int kb_per_split, const __grid_constant__ CUtensorMap tmA,
+                    const __grid_constant__ CUtensorMap tmB) {
+    using Cfg = TnBf16Cfg;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + STAGES;
+    uint64_t* accum_bar = bars + 2 * STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int m0 = (blockIdx.x / tiles_n) * Cfg::BLOCK_M;
+    const int n0 = (blockIdx.x % tiles_n) * Cfg::BLOCK_N;
+    const int kb_begin = static_cast<int>(blockIdx.y) * kb_per_split;
+    const int total_kb = max(min(p.kblocks0, kb_begin + kb_per_split) - kb_begin, 0);
+
+    auto stage_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
+    auto stage_b = [&](int s) { return tiles + s * Cfg::STAGE_BYTES + Cfg::TILE_BYTES; };
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(accum_bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kk = 0; kk < total_kb; ++kk) {
+                const int s = kk % STAGES;
+                mbar_wait(&empty_bar[s], ((kk / STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+                const int r0 = (kb_begin + kk) * Cfg::BLOCK_K;
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    tma_load_2d(stage_a(s) + a * 8192, &tmA, &full_bar[s], m0 + a * 64, r0);
+                    tma_load_2d(stage_b(s) + a * 8192, &tmB, &full_bar[s], n0 + a * 64, r0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(1, Cfg::BLOCK_M, Cfg::BLOCK_N, 1, 1);
+            for (int kk = 0; kk < total_kb; ++kk) {
+                const int s = kk % STAGES;
+                mbar_wait(&full_bar[s], (kk / STAGES) & 1);
+                tc_fence_after_sync();
+                const uint64_t a_desc = umma_desc_mnmajor_sw128(smem_u32(stage_a(s)), 8192, 1024, 2);
+                const uint64_t b_desc = umma_desc_mnmajor_sw128(smem_u32(stage_b(s)), 8192, 1024, 2);
+#pragma unroll
+                for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                    const uint64_t koff = static_cast<uint64_t>(k * 128);       // 16 reduction rows = 2048 B, >> 4
+                    umma<false>(tmem_base, a_desc + koff, b_desc + koff, idesc, (kk | k) != 0);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(accum_bar);
+        }
+    } else {
+        mbar_wait(accum_bar, 0);
+        tc_fence_after_sync();
+        const int quarter = warp & 3;
+        float* stage = reinterpret_cast<float*>(tiles);
+        constexpr int PITCH = Cfg::BLOCK_N + 4;
+        float* my_row = stage + (quarter * 32 + lane) * PITCH;
+        const bool any = total_kb > 0;
+#pragma unroll 1
+        for (int c0 = 0; c0 < Cfg::BLOCK_N; c0 += 32) {
+            if (n0 + c0 >= p.N) break;
+            uint32_t r[32];
+            if (any) {
+                tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + c0, r);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) r[j] = 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<uint4*>(my_row + c0 + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+        }
+        __syncwarp();
+        GemmParams q = p;
+        q.C = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.ldc;
+        epilogue_warp_rows<Cfg::BLOCK_N>(q, stage, quarter * 32, m0, n0, lane);
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
 __global__ void split_tf32_kernel(const float* __restrict__ src, int64_t ld_src, float* __restrict__ hi,
                                   float* __restrict__ lo, int64_t ld_dst, int64_t rows, int cols) {
     const int64_t total = rows * cols;
@@ -237,4 +355,42 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
         case kTF32BC: return launch_gemm_bc(ga, gp, st, false, 0);
         default:    return launch_gemm_x3(ga, gp, st);
     }
+}
+
+namespace grl {
+int tn_plan_splits(int tiles, int kblocks);                                                        // gemm_x3_tcgen05.cu
+int launch_reduce_splits(const float* ws, float* out, int64_t n, int splits, cudaStream_t st);
+}
+
+extern "C" int grl_gemm_tn_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int64_t ldc, int Ma,
+                                int Nb, int64_t R, void* workspace, size_t workspace_bytes, void* stream) {
+    using Cfg = TnBf16Cfg;
+    GRL_CHECK_ARG(A && B && C && workspace, GRL_E_BADARG, "grl_gemm_tn_bf16: null pointer");
+    GRL_CHECK_ARG(Ma > 0 && Nb > 0 && R > 0 && R < (1LL << 31), GRL_E_BADARG, "grl_gemm_tn_bf16: bad shape");
+    GRL_CHECK_ARG(lda >= Ma && ldb >= Nb && ldc == Nb, GRL_E_BADARG, "grl_gemm_tn_bf16: bad leading dimension (C must be dense)");
+    GRL_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && aligned_to(A, 16) && aligned_to(B, 16), GRL_E_ALIGN,
+                  "grl_gemm_tn_bf16: operands need 16-byte aligned base pointers and row pitches");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CUtensorMap tA, tB;
+    int rc;
+    if ((rc = make_tmap_sw128(&tA, A, 2, R, Ma, lda, Cfg::BLOCK_K))) return rc;      // box {64 columns, 64 rows}
+    if ((rc = make_tmap_sw128(&tB, B, 2, R, Nb, ldb, Cfg::BLOCK_K))) return rc;
+    GemmParams p{};
+    p.M = Ma; p.N = Nb; p.ldc = Nb; p.C = workspace;
+    p.kblocks0 = static_cast<int>((R + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K);
+    const int tiles = ((Ma + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M) * ((Nb + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N);
+    int splits = tn_plan_splits(tiles, p.kblocks0);
+    const int kb_per_split = (p.kblocks0 + splits - 1) / splits;
+    splits = (p.kblocks0 + kb_per_split - 1) / kb_per_split;
+    const size_t need = sizeof(float) * static_cast<size_t>(Ma) * Nb * splits;
+    GRL_CHECK_ARG(workspace_bytes >= need, GRL_E_WORKSPACE, "grl_gemm_tn_bf16: workspace %zu < %zu", workspace_bytes, need);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tn_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+        attr_set = true;
+    }
+    gemm_tn_bf16_kernel<<<dim3(tiles, splits), kGemmThreads, Cfg::SMEM_BYTES, st>>>(p, kb_per_split, tA, tB);
+    GRL_LAUNCH_CHECK("gemm_tn_bf16_kernel");
+    return launch_reduce_splits(static_cast<const float*>(workspace), C, static_cast<int64_t>(Ma) * Nb, splits, st);
 }

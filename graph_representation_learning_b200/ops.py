@@ -220,9 +220,9 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, fp32_mode: Optional[str] = None) -
     fp32 operands, split-K over R with a deterministic reduce: "tf32bc" (default, ``GemmConfig.fp32_mode_bwd``) = the
     TMEM-operand kernel (csrc/gemm_bc_tcgen05.cu, grl_split_act_mn + grl_gemm_tn_bc); "tf32x3" = the MN-major
     three-product kernel (csrc/gemm_x3_tcgen05.cu, grl_gemm_tn).
-    bf16 operands: TRANSITIONAL (DESIGN.md "GEMM status") cuBLAS via torch.mm until the bf16 MN-major kernel lands."""
-    if a.dtype != torch.float32:
-        return torch.mm(a.t(), b, out_dtype=torch.float32)
+    bf16 operands: MN-major kind::f16 kernel, fp32 accumulation and output (csrc/gemm_tcgen05.cu, grl_gemm_tn_bf16)."""
+    if a.dtype not in (torch.float32, torch.bfloat16) or b.dtype != a.dtype:
+        raise _lib.GrlError(f"gemm_tn operands must both be fp32 or both bf16, got {a.dtype} / {b.dtype}")
     a, b = _tma_ready(a), _tma_ready(b)
     R, Ma = a.shape
     Nb = b.shape[1]
@@ -234,6 +234,11 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, fp32_mode: Optional[str] = None) -
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=a.device)
         _tn_workspace[key] = ws
     C = torch.empty(Ma, Nb, dtype=torch.float32, device=a.device)
+    if a.dtype == torch.bfloat16:
+        _lib.check(lib.grl_gemm_tn_bf16(a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), C.data_ptr(), Nb, Ma, Nb, R,
+                                        ws.data_ptr(), ws.numel(), _lib.stream_ptr(a.device)), "grl_gemm_tn_bf16")
+        _lib.count_launch(2)
+        return C
     if (fp32_mode or GemmConfig.fp32_mode_bwd) == "tf32bc":
         # the WIDE operand goes through TMEM, the narrow one is split once in HBM; the product is stored transposed
         # when the caller's first operand is the narrow one

@@ -199,6 +199,9 @@ int grl_gemm_bc_set_promo(int promo);   /* the same knob of the GRL_GEMM_TF32_BF
 size_t grl_gemm_tn_workspace_bytes(int Ma, int Nb);
 int grl_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                 int Ma, int Nb, int64_t R, void* workspace, size_t workspace_bytes, void* stream);
+/* The same contraction for bf16 operands (kind::f16, fp32 accumulation and output; lda/ldb multiples of 8). */
+int grl_gemm_tn_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, float* C, int64_t ldc,
+                     int Ma, int Nb, int64_t R, void* workspace, size_t workspace_bytes, void* stream);
 /* The same contraction in GRL_GEMM_TF32_BF16C arithmetic, activation operand A through TMEM:
  *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]   (transpose_out = 0)      or   C[Nb, Ma] = its transpose (transpose_out = 1)
  * A = the WIDE operand (raw fp32, lda % 4 == 0); B = the narrow one, split once by grl_split_act_mn into B_hi

@@ -149,3 +149,19 @@ def test_gemm_tn_strided_operands_emb1_like():
     ref = dz.double().t() @ buf[:, :K].double()
     out = ops.gemm_tn(dz.to(dev), buf.to(dev)[:, :K])          # nn.Linear layout [out, in]
     assert rel_err(out.cpu(), ref) < 2e-6
+
+
+@pytest.mark.parametrize("R,Ma,Nb", [(1000, 256, 128), (4096, 512, 512), (130, 72, 40), (20000, 1792, 512), (777, 56, 1280)])
+def test_gemm_tn_bf16_weight_gradient(R, Ma, Nb):
+    """bf16 activations, MN-major kind::f16 kernel, fp32 accumulation/output: only the accumulation order differs from
+    the fp64 product of the same bf16 values (1e-5); deterministic."""
+    from graph_representation_learning_b200 import ops
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(R + Ma + Nb)
+    a = torch.randn(R, Ma, generator=gen).bfloat16()
+    b = torch.randn(R, Nb, generator=gen).bfloat16()
+    ref = a.double().t() @ b.double()
+    out = ops.gemm_tn(a.to(dev), b.to(dev))
+    assert out.shape == (Ma, Nb) and out.dtype == torch.float32
+    assert rel_err(out.cpu(), ref) < 1e-5
+    assert torch.equal(out, ops.gemm_tn(a.to(dev), b.to(dev)))

@@ -38,6 +38,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-bow", action="store_true", help="skip the bag-of-words feature variant (sparse emb1 path)")
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket ONE extra train step (after the timed region) with cudaProfilerStart/Stop for "
                          "`ncu --profile-from-start off`; numbers printed by such a run are not bench values")
@@ -259,6 +260,35 @@ def run_b200(args):
                                           "(NumpyPadding + default_collate format)"}}
         del host_dense, host_edges, Vp_h
 
+    # (2b) the second named feature variant: bag-of-words text-line encodings (7 ones in the 4365 binary
+    # columns + 4 spatial floats per node, what TextlineEncoding emits) through the sparse-feature path -- same model,
+    # same graph, same step; emb1 runs as a gather-sum + a 4-column GEMM (features.py), the host ships CSR + edge triples
+    bow = None
+    if not args.no_bow and wl.dtype == torch.float32:
+        from graph_representation_learning_b200 import SparseNodeFeatures
+        from graph_representation_learning_b200.trainer import DevicePrefetcher
+        Vb, _, _ = synthetic.make_batch(wl, 1234 + rank, dev, B=B, features="bow")
+        sf = SparseNodeFeatures.from_dense(Vb)
+        del Vb
+
+        def fresh():   # a new batch object every step: the CSC of the features is rebuilt inside the step, like A's
+            return SparseNodeFeatures(sf.shape, sf.rowptr, sf.col, sf.val, sf.heavy_cols, sf.heavy)
+        ms_bow, _, _ = timed(lambda: step.run_train_step({"textline_encoding": fresh(), "adjacency_matrix": A,
+                                                          "node_label": y}), max(5, args.steps // 2), 3)
+        bow = {"value": world * B / (ms_bow * 1e-3), "unit": UNIT, "ms_per_step": ms_bow,
+               "features": "bow: 7 ones in 4365 binary columns + 4 floats per node, shipped as CSR (%d entries) + a "
+                           "[Nt, %d] heavy-column block" % (sf.nnz, int(sf.heavy_cols.numel()))}
+        if not args.no_e2e:
+            host_bow = {"textline_encoding": sf.to("cpu").pin_memory(), "node_label": pin(y),
+                        "edges": pin(A.nonzero().to(torch.int32)), "edge_weights": None,
+                        "graph_shape": (B, wl.N, wl.num_edges)}
+            ms_bow_e2e = e2e_run(host_bow, e_steps, 2)
+            bow["e2e"] = {"value": world * B / (ms_bow_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_bow_e2e,
+                          "h2d_bytes_per_step": host_bow["textline_encoding"].nbytes() + nbytes(host_bow, ["node_label", "edges"]),
+                          "d2h_bytes_per_step": 4}
+            del host_bow
+        del sf
+
     # (3) roofline of the aggregation kernel (gcn1 SpMM, DropEdge weights applied), timed alone with CUDA events
     pk = peaks()
     g = PackedGraphBatch.from_dense(A)
@@ -306,6 +336,7 @@ def run_b200(args):
                        "l2": "inputs (V %.2f GB) larger than L2" % (V.numel() * V.element_size() / 1e9),
                        "features": "dense U[0,1)"},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "bow_features": bow,
         }))
     if world > 1:
         dist.destroy_process_group()

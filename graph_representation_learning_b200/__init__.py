@@ -6,6 +6,7 @@ Public surface (mirrors the reference's ``gnn.models`` / ``gnn.cl_warper`` names
 """
 from ._lib import GrlError, LIB_PATH  # noqa: F401
 from .graph import PackedGraphBatch  # noqa: F401
+from .features import SparseNodeFeatures  # noqa: F401
 from .networks import (BaseNetwork, GraphCNNDropEdge, GraphConv, NodeSelfAtten, RanPACLayer,  # noqa: F401
                        make_linear_relu)
 

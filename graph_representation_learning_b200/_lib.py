@@ -40,6 +40,8 @@ SIGNATURES = {
     "grl_csr_transpose_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "grl_csr_transpose": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),
+    "grl_csr_transpose_general": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p,
+                                          c_void_p, c_size_t, c_void_p]),
     "grl_dropedge_weights": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_uint64, c_uint64, c_void_p, c_void_p]),
     "grl_dropedge_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_uint64,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -22,6 +22,7 @@ import numpy as np
 import torch
 from torch.utils.data._utils.collate import default_collate
 
+from .features import SparseNodeFeatures
 from .graph import PackedGraphBatch
 
 
@@ -188,7 +189,12 @@ class EdgeListCollate(BaseCollate):
         """H2D (async from pinned memory) + CSR/CSC pack on the device; the result feeds ``model.forward([V, A])``."""
         B, N, L = batch["graph_shape"]
         D = batch["textline_encoding"].shape[-1]
-        V = batch["features_padded"].to(device, non_blocking=True)[:, :, :D]     # the pitch survives the copy
+        if isinstance(batch["textline_encoding"], SparseNodeFeatures):            # bag-of-words features (features.py)
+            V = batch["textline_encoding"].to(device, non_blocking=True)
+            V.build_transpose()
+            V.identity_perm()
+        else:
+            V = batch["features_padded"].to(device, non_blocking=True)[:, :, :D]     # the pitch survives the copy
         y = batch["node_label"].to(device, non_blocking=True)
         edges = batch["edges"].to(device, non_blocking=True)
         wts = batch["edge_weights"]

@@ -333,33 +333,50 @@ extern "C" size_t grl_csr_transpose_workspace_bytes(int64_t n_nodes, int64_t nnz
     return sizeof(int32_t) * static_cast<size_t>(n_nodes + 2 * nnz) + 256 + grl_scan_workspace_bytes(n_nodes);
 }
 
-extern "C" int grl_csr_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, int L, int64_t nnz,
-                                 int32_t* colptr, int32_t* rowidx, int32_t* perm, void* workspace,
-                                 size_t workspace_bytes, void* stream) {
-    GRL_CHECK_ARG(rowptr && col && colptr && rowidx && perm && workspace, GRL_E_BADARG, "grl_csr_transpose: null pointer");
-    const int64_t n_nodes = static_cast<int64_t>(B) * N, R = n_nodes * (L + 1);
-    GRL_CHECK_ARG(workspace_bytes >= grl_csr_transpose_workspace_bytes(n_nodes, nnz), GRL_E_WORKSPACE,
-                  "grl_csr_transpose: workspace too small");
+// shared body: CSC of an [R x n_cols] CSR matrix whose stored column index is local to a block of rows_per_block rows
+// (column of entry e in row r = (r / rows_per_block) * cols_per_block + col[e]); one block = the whole matrix otherwise
+static int csr_transpose_impl(const int32_t* rowptr, const int32_t* col, int64_t R, int64_t rows_per_block,
+                              int cols_per_block, int64_t n_cols, int64_t nnz, int32_t* colptr, int32_t* rowidx,
+                              int32_t* perm, void* workspace, size_t workspace_bytes, void* stream, const char* who) {
+    GRL_CHECK_ARG(rowptr && col && colptr && rowidx && perm && workspace, GRL_E_BADARG, "%s: null pointer", who);
+    GRL_CHECK_ARG(workspace_bytes >= grl_csr_transpose_workspace_bytes(n_cols, nnz), GRL_E_WORKSPACE,
+                  "%s: workspace too small", who);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int32_t* cursor = static_cast<int32_t*>(workspace);
-    int32_t* tmp_e = cursor + n_nodes;
+    int32_t* tmp_e = cursor + n_cols;
     int32_t* tmp_r = tmp_e + nnz;
     uintptr_t scan_ws = reinterpret_cast<uintptr_t>(tmp_r + nnz);
     scan_ws = (scan_ws + 255) & ~static_cast<uintptr_t>(255);
-    const size_t scan_bytes = grl_scan_workspace_bytes(n_nodes) - 256;
+    const size_t scan_bytes = grl_scan_workspace_bytes(n_cols) - 256;
 
-    cudaError_t e = cudaMemsetAsync(colptr, 0, sizeof(int32_t) * (n_nodes + 1), st);
+    cudaError_t e = cudaMemsetAsync(colptr, 0, sizeof(int32_t) * (n_cols + 1), st);
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(colptr)");
-    e = cudaMemsetAsync(cursor, 0, sizeof(int32_t) * n_nodes, st);
+    e = cudaMemsetAsync(cursor, 0, sizeof(int32_t) * n_cols, st);
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(cursor)");
-    const int rows_per_graph = N * (L + 1);
-    csc_count_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, col, R, rows_per_graph, N, colptr);
+    const int rpb = static_cast<int>(rows_per_block);
+    csc_count_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, col, R, rpb, cols_per_block, colptr);
     GRL_LAUNCH_CHECK("csc_count_kernel");
-    int rc = grl_scan_inclusive_i32(colptr + 1, n_nodes, reinterpret_cast<void*>(scan_ws), scan_bytes, stream);
+    int rc = grl_scan_inclusive_i32(colptr + 1, n_cols, reinterpret_cast<void*>(scan_ws), scan_bytes, stream);
     if (rc) return rc;
-    csc_scatter_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, col, R, rows_per_graph, N, colptr, cursor, tmp_e, tmp_r);
+    csc_scatter_kernel<<<grid_for(R, 256), 256, 0, st>>>(rowptr, col, R, rpb, cols_per_block, colptr, cursor, tmp_e, tmp_r);
     GRL_LAUNCH_CHECK("csc_scatter_kernel");
-    csc_rank_kernel<<<grid_for(n_nodes * 32, 256), 256, 0, st>>>(colptr, n_nodes, tmp_e, tmp_r, rowidx, perm);
+    csc_rank_kernel<<<grid_for(n_cols * 32, 256), 256, 0, st>>>(colptr, n_cols, tmp_e, tmp_r, rowidx, perm);
     GRL_LAUNCH_CHECK("csc_rank_kernel");
     return 0;
+}
+
+extern "C" int grl_csr_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, int L, int64_t nnz,
+                                 int32_t* colptr, int32_t* rowidx, int32_t* perm, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+    const int64_t n_nodes = static_cast<int64_t>(B) * N, R = n_nodes * (L + 1);
+    return csr_transpose_impl(rowptr, col, R, static_cast<int64_t>(N) * (L + 1), N, n_nodes, nnz, colptr, rowidx, perm,
+                              workspace, workspace_bytes, stream, "grl_csr_transpose");
+}
+
+extern "C" int grl_csr_transpose_general(const int32_t* rowptr, const int32_t* col, int64_t R, int n_cols, int64_t nnz,
+                                         int32_t* colptr, int32_t* rowidx, int32_t* perm, void* workspace,
+                                         size_t workspace_bytes, void* stream) {
+    GRL_CHECK_ARG(R > 0 && R < (1LL << 31) && n_cols > 0, GRL_E_BADARG, "grl_csr_transpose_general: bad shape");
+    return csr_transpose_impl(rowptr, col, R, R, n_cols, n_cols, nnz, colptr, rowidx, perm, workspace, workspace_bytes,
+                              stream, "grl_csr_transpose_general");
 }

@@ -23,6 +23,7 @@ import torch
 from torch import nn
 
 from . import _lib, ops
+from .features import SparseNodeFeatures
 from .graph import PackedGraphBatch
 
 RP_FACTOR = 10  # drop_robust_gcn.py:10
@@ -200,14 +201,15 @@ class GraphCNNDropEdge(BaseNetwork):
     # ------------------------------------------------------------------ forward
     def forward(self, inputs: Sequence[Any], efficient_mode: bool = True, *,
                 masks: Optional[Dict[str, Any]] = None) -> torch.Tensor:
-        """inputs = (V, A): V ``B x N x input_dim``; A the collate's dense ``B x N x L x N`` adjacency
+        """inputs = (V, A): V ``B x N x input_dim`` (or the same batch as ``SparseNodeFeatures``); A the collate's dense ``B x N x L x N`` adjacency
         ([b, start, type, end], fp16/fp32) or a ``PackedGraphBatch``.  Returns fp32 logits ``B x N x output_dim``.
 
         ``efficient_mode`` is accepted for signature compatibility (the adjacency is always packed once).
         ``masks`` (tests only) injects keep-bits: {"edge": [3 x uint8[nnz]], "feat": [5 x uint8[B*N, C]]}.
         """
         V, A = inputs
-        _lib.require_cuda(V, "V")
+        sparse_v = isinstance(V, SparseNodeFeatures)
+        _lib.require_cuda(V.val if sparse_v else V, "V")
         B, N = V.shape[0], V.shape[1]
         g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A)
         if g.B != B or g.N != N or g.L != self.num_edges:
@@ -220,11 +222,15 @@ class GraphCNNDropEdge(BaseNetwork):
         em = masks["edge"] if masks else [None] * 3
         fm = masks["feat"] if masks else [None] * 5
 
-        x = _flat(V)
-        if x.dtype != self.compute_dtype:
-            x = x.to(self.compute_dtype)
         lin = self.emb1[0]
-        emb = ops.linear_act([x], lin.weight, lin.bias, relu=True, p=p_feat, mask=fm[0], seed=seed, stream_id=sid + 0)
+        if sparse_v:     # bag-of-words features as CSR + heavy-column block (features.py): gather-sum instead of the GEMM
+            emb = ops.sparse_linear_act(V, lin.weight, lin.bias, relu=True, p=p_feat, mask=fm[0], seed=seed,
+                                        stream_id=sid + 0, compute_dtype=self.compute_dtype)
+        else:
+            x = _flat(V)
+            if x.dtype != self.compute_dtype:
+                x = x.to(self.compute_dtype)
+            emb = ops.linear_act([x], lin.weight, lin.bias, relu=True, p=p_feat, mask=fm[0], seed=seed, stream_id=sid + 0)
 
         w1 = g.edge_weights(p_edge, seed, sid + 1, em[0])
         g1 = ops.graph_conv([emb], g, w1, self.gcn1.h_weights, self.gcn1.bias, relu=True, p=p_feat, mask=fm[1],

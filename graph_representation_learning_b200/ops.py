@@ -356,6 +356,74 @@ def linear_act(xs: Sequence[torch.Tensor], weight: torch.Tensor, bias: Optional[
     return _LinearAct.apply(weight, bias, relu, float(p), mask, seed, stream_id, weight_is_kn, *xs)
 
 
+class _SparseLinearAct(torch.autograd.Function):
+    """y = dropout(relu(V @ W^T + b)) for V given as ``SparseNodeFeatures`` (features.py): heavy columns through a
+    K = n_heavy tensor-core GEMM, light columns as a gather-sum over the rows of W^T (csrc/spmm.cu: fp32 FMA in CSR
+    order); weight gradient = the same two pieces transposed.  No gradient flows to the features."""
+
+    @staticmethod
+    def forward(ctx, feats, weight, bias, relu, p, mask, seed, stream_id, cdt):
+        lib = _lib.load()
+        Nt, S, D = feats.num_nodes, weight.shape[0], weight.shape[1]
+        if D != feats.shape[2]:
+            raise _lib.GrlError(f"sparse features have {feats.shape[2]} columns, the layer expects {D}")
+        Dh = int(feats.heavy_cols.numel())
+        Wt = weight.detach().t().to(cdt).contiguous()                      # [D, S]: one row per feature column
+        if Dh:
+            hv = feats.heavy[:, :Dh] if cdt == torch.float32 else feats.heavy.to(cdt)[:, :Dh]
+            z = gemm_nt([hv], [weight.detach()[:, feats.heavy_cols]], out_dtype=cdt)
+        else:
+            z = torch.empty(Nt, S, dtype=cdt, device=weight.device)
+        if feats.nnz or not Dh:
+            _lib.check(lib.grl_spmm_bwd(feats.rowptr.data_ptr(), feats.col.data_ptr(), feats.identity_perm().data_ptr(),
+                                        feats.val.data_ptr(), Wt.data_ptr(), S, z.data_ptr(), S, _lib.dtype_code(z), 1, Nt, 1,
+                                        S, 1 if Dh else 0, _lib.stream_ptr(z.device)), "grl_spmm_bwd(features)")
+            _lib.count_launch(1)
+        if bias is not None and (bias.dtype != torch.float32 or not bias.is_contiguous()):
+            bias = bias.float().contiguous()
+        epilogue_fwd_(z, bias, z, relu, p, mask, seed, stream_id)
+        ctx.feats = feats
+        ctx.save_for_backward(weight, z if relu else None)
+        ctx.cfg = (relu, p, bias is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dY):
+        weight, y = ctx.saved_tensors
+        relu, p, has_bias = ctx.cfg
+        feats = ctx.feats
+        lib = _lib.load()
+        dY = dY.contiguous()
+        if relu or p > 0.0:
+            dZ = torch.empty_like(dY)
+            epilogue_bwd_(dY, y, dZ, relu, p)
+        else:
+            dZ = dY
+        d_weight = d_bias = None
+        if ctx.needs_input_grad[1]:
+            S, D = weight.shape
+            dZ32 = dZ if dZ.dtype == torch.float32 else dZ.float()          # fp32 master gradient
+            feats.build_transpose()
+            dWt = torch.empty(D, S, dtype=torch.float32, device=dZ.device)
+            _lib.check(lib.grl_spmm_bwd(feats.colptr.data_ptr(), feats.rowidx.data_ptr(), feats.perm.data_ptr(),
+                                        feats.val.data_ptr(), dZ32.data_ptr(), S, dWt.data_ptr(), S, _lib.dtype_code(dWt), 1, D, 1, S, 0,
+                                        _lib.stream_ptr(dZ.device)), "grl_spmm_bwd(features^T)")
+            _lib.count_launch(1)
+            Dh = int(feats.heavy_cols.numel())
+            if Dh:
+                dWt[feats.heavy_cols] = gemm_tn(feats.heavy[:, :Dh], dZ32, GemmConfig.fp32_mode_bwd)     # [Dh, S]
+            d_weight = dWt.t()
+        if has_bias and ctx.needs_input_grad[2]:
+            d_bias = colsum(dZ)
+        return (None, d_weight, d_bias, None, None, None, None, None, None)
+
+
+def sparse_linear_act(feats, weight: torch.Tensor, bias: Optional[torch.Tensor], relu: bool = False, p: float = 0.0,
+                      mask: Optional[torch.Tensor] = None, seed: int = 0, stream_id: int = 0,
+                      compute_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    return _SparseLinearAct.apply(feats, weight, bias, relu, float(p), mask, seed, stream_id, compute_dtype)
+
+
 def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Tensor, h_weights: torch.Tensor,
                bias: Optional[torch.Tensor], relu: bool = False, p: float = 0.0, mask: Optional[torch.Tensor] = None,
                seed: int = 0, stream_id: int = 0) -> torch.Tensor:

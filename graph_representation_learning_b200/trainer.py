@@ -19,6 +19,8 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
+from .features import SparseNodeFeatures
+
 
 _ws_cache: Dict[Any, torch.Tensor] = {}
 
@@ -250,7 +252,7 @@ class KVTrainStep:
             from .collate import EdgeListCollate
             batch_sample = EdgeListCollate.to_device(batch_sample, self.device)
         V = batch_sample["textline_encoding"]
-        if not V.is_floating_point():
+        if not isinstance(V, SparseNodeFeatures) and not V.is_floating_point():
             V = V.float()                               # kv_procedure.py:117 (.float() of whatever the dataset gave)
         V = V.to(self.device, non_blocking=True)
         A = batch_sample["adjacency_matrix"]
@@ -421,7 +423,11 @@ class DevicePrefetcher:
             else:
                 out = {}
                 for k, v in batch.items():
-                    if isinstance(v, torch.Tensor):
+                    if isinstance(v, SparseNodeFeatures):
+                        out[k] = v.to(self.device, non_blocking=True)
+                        out[k].build_transpose()           # CSC for the emb1 weight gradient, on the copy stream
+                        out[k].identity_perm()
+                    elif isinstance(v, torch.Tensor):
                         if k == "textline_encoding":
                             if not v.is_floating_point():
                                 v = v.float()
@@ -451,6 +457,9 @@ class DevicePrefetcher:
             for v in cur.values():                        # allocated on the side stream, consumed on the main one
                 if isinstance(v, torch.Tensor):
                     v.record_stream(main)
+                elif isinstance(v, SparseNodeFeatures):
+                    for t in v.tensors():
+                        t.record_stream(main)
                 elif hasattr(v, "rowptr"):
                     for t in (v.rowptr, v.col, v.val, v.colptr, v.rowidx, v.perm):
                         if t is not None:

@@ -95,6 +95,13 @@ int grl_csr_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, i
                       int32_t* colptr, int32_t* rowidx, int32_t* perm,
                       void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same transposition for a plain [R x n_cols] CSR matrix (global column indices): the sparse node-feature matrix
+ * of bag-of-words text-line encodings (gnn/data_generator/data_process/textline_encoding.py:23-42), whose CSC drives the
+ * emb1 weight gradient.  Workspace: grl_csr_transpose_workspace_bytes(n_cols, nnz). */
+int grl_csr_transpose_general(const int32_t* rowptr, const int32_t* col, int64_t R, int n_cols, int64_t nnz,
+                              int32_t* colptr, int32_t* rowidx, int32_t* perm,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * DropEdge: materialise the per-entry weight of one layer,
  *   w[e] = val[e] * keep[e] / (1 - p),   keep[e] = mask[e] (injected, uint8) if mask != NULL

@@ -250,3 +250,82 @@ class GraphCNNDropEdge(BaseNetwork):
                                seed=seed, stream_id=sid + 7)
         logits = ops.linear_act([new_v], self.classifier.weight, self.classifier.bias)
         return logits.float().view(B, N, self.output_dim)
+
+
+class _FeatureDropout(torch.autograd.Function):
+    """nn.Dropout(p) without an activation in front (RobustGCN drops the attention output, robust_gcn.py:222): the keep
+    factors come from the same Philox / injected-mask epilogue kernel as everywhere else, applied to ones."""
+
+    @staticmethod
+    def forward(ctx, x, p, mask, seed, stream_id):
+        k = torch.empty_like(x)
+        ops.epilogue_fwd_(torch.ones_like(x), None, k, False, p, mask, seed, stream_id)
+        ctx.save_for_backward(k)
+        return x * k
+
+    @staticmethod
+    def backward(ctx, dy):
+        (k,) = ctx.saved_tensors
+        return dy * k, None, None, None, None
+
+
+@register_model
+class RobustGCN(BaseNetwork):
+    """gnn/models/networks/robust_gcn.py:173-231 -- the sibling of GraphCNNDropEdge without DropEdge and random
+    projection, with two more GraphConv layers behind the attention.  Same kernels: one packed graph per forward, virtual
+    concats ([g2, g1], [g3, g1] in the reference's order), fused bias / ReLU / dropout epilogues."""
+
+    def __init__(self, input_dim: int, output_dim: int, num_edges: int, net_size: int = 256, use_attention: bool = True):
+        super().__init__()
+        self.output_dim, self.net_size, self.num_edges = output_dim, net_size, num_edges
+        self.emb1 = make_linear_relu(input_dim, net_size)
+        self.dropout = nn.Dropout(p=0.5)
+        self.gcn1 = GraphConv(net_size, net_size, num_edges)
+        self.gcn2 = GraphConv(net_size, net_size, num_edges)
+        self.gcn3 = GraphConv(net_size * 2, net_size, num_edges)
+        half = net_size // 2
+        self.emb2 = make_linear_relu(net_size * 2, half)
+        self.use_attention = use_attention
+        if use_attention:
+            self.self_atten = NodeSelfAtten(half)
+        self.gcn4 = GraphConv(half, half, num_edges)
+        self.gcn5 = GraphConv(half, half, num_edges)
+        self.classifier = nn.Linear(half, output_dim)
+        self.compute_dtype = torch.float32
+        self.rng_seed: Optional[int] = None
+        self._rng_calls = 0
+
+    def forward(self, inputs: Sequence[Any], efficient_mode: bool = True, *,
+                masks: Optional[Dict[str, Any]] = None) -> torch.Tensor:
+        V, A = inputs
+        _lib.require_cuda(V, "V")
+        B, N = V.shape[0], V.shape[1]
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A)
+        if g.B != B or g.N != N or g.L != self.num_edges:
+            raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
+                                f"num_edges={self.num_edges}")
+        p = self.dropout.p if self.training else 0.0
+        seed = torch.initial_seed() if self.rng_seed is None else self.rng_seed
+        sid = self._rng_calls * 16
+        self._rng_calls += 1
+        fm = masks["feat"] if masks else [None] * 6
+        w = g.edge_weights(0.0)                                  # no DropEdge in this model
+        lin = self.emb1[0]
+        emb = ops.linear_act([_flat(V).float()], lin.weight, lin.bias, relu=True, p=p, mask=fm[0], seed=seed, stream_id=sid)
+        g1 = ops.graph_conv([emb], g, w, self.gcn1.h_weights, self.gcn1.bias, relu=True, p=p, mask=fm[1], seed=seed,
+                            stream_id=sid + 1)
+        g2 = ops.graph_conv([g1], g, w, self.gcn2.h_weights, self.gcn2.bias, relu=True, p=p, mask=fm[2], seed=seed,
+                            stream_id=sid + 2)
+        g3 = ops.graph_conv([g2, g1], g, w, self.gcn3.h_weights, self.gcn3.bias, relu=True, p=p, mask=fm[3], seed=seed,
+                            stream_id=sid + 3)
+        lin = self.emb2[0]
+        new_v = ops.linear_act([g3, g1], lin.weight, lin.bias, relu=True)
+        if self.use_attention:
+            new_v = _flat(self.self_atten(new_v.view(B, N, -1)))
+        if p > 0.0:
+            new_v = _FeatureDropout.apply(new_v.contiguous(), p, fm[4], seed, sid + 4)
+        g4 = ops.graph_conv([new_v], g, w, self.gcn4.h_weights, self.gcn4.bias, relu=True, p=p, mask=fm[5], seed=seed,
+                            stream_id=sid + 5)
+        g5 = ops.graph_conv([g4], g, w, self.gcn5.h_weights, self.gcn5.bias, relu=True)
+        logits = ops.linear_act([g5], self.classifier.weight, self.classifier.bias)
+        return logits.float().view(B, N, self.output_dim)

@@ -177,9 +177,47 @@ def collate_case(NumpyPadding):
     print("collate:", {k: tuple(v.shape) for k, v in batch.items()}, {k: v.dtype for k, v in batch.items()})
 
 
+def robust_gcn_case(name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0):
+    """Sibling model that reuses GraphConv / NodeSelfAtten: gnn/models/networks/robust_gcn.py:173-231.
+    No DropEdge; six feature dropouts in call order emb(0) g1(1) g2(2) g3(3) attention-out(4) g4(5)."""
+    from gnn.models.networks.robust_gcn import RobustGCN
+    gen = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    model = RobustGCN(in_dim, out_dim, L, net_size=S)
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    V = torch.rand(B, N, in_dim, generator=gen)
+    A = synth_graph(gen, B, N, L, deg)
+    y = torch.randint(0, out_dim, (B, N), generator=gen)
+    H = S // 2
+    feat_masks = [torch.bernoulli(torch.full((B, N, w), 0.5), generator=gen).to(torch.uint8) for w in (S, S, S, S, H, H)]
+    model.eval()
+    with torch.no_grad():
+        logits_eval = model([V, A.float()])
+    model.train()
+    model.dropout = InjectedDropout(0.5, feat_masks)
+    logits_train = model.forward([V, A.float()])
+    loss = torch.nn.CrossEntropyLoss()(logits_train.transpose(1, 2), y)
+    loss.backward()
+    out = {"V": V.numpy(), "A": A.numpy(), "y": y.numpy(), "logits_eval": logits_eval.numpy(),
+           "logits_train": logits_train.detach().numpy(), "loss": loss.detach().numpy(),
+           "meta": np.array(json.dumps(dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed)))}
+    for i, m in enumerate(feat_masks):
+        out[f"feat_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for k, v in sd0.items():
+        out["sd0/" + k] = v.numpy()
+    for k, p in model.named_parameters():
+        if p.grad is not None:
+            out["grad/" + k] = p.grad.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(f"{name}: loss {float(loss):.6f}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     GraphCNNDropEdge, NumpyPadding = import_reference()
+    if len(sys.argv) > 1 and sys.argv[1] == "robust_gcn":       # add the sibling-model vectors without touching the rest
+        robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
+        return
     small_model_case(GraphCNNDropEdge, "model_small", seed=11, B=3, N=10, in_dim=24, S=32, out_dim=7)
     small_model_case(GraphCNNDropEdge, "model_weighted_pad", seed=12, B=2, N=12, in_dim=20, S=32, out_dim=5,
                      weighted=True, empty_types=(4, 5), pad=2)
@@ -188,6 +226,7 @@ def main():
     preprocess_case(GraphCNNDropEdge)
     init_case(GraphCNNDropEdge)
     collate_case(NumpyPadding)
+    robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
 
 
 if __name__ == "__main__":

@@ -414,3 +414,39 @@ def test_model_eval_on_edge_list_equals_dense_path(dev):
     model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size).to(dev).eval()
     with torch.no_grad():
         assert torch.equal(model([V, g_d]), model([V, g_e]))
+
+
+# ---------------------------------------------------------------------------------------- sibling model
+def test_robust_gcn_matches_reference_vectors(dev):
+    """RobustGCN (gnn/models/networks/robust_gcn.py:173-231) on the same kernels: eval logits, and train-mode logits /
+    loss / every gradient with the six injected feature-dropout masks, against vectors of the unmodified reference."""
+    import json
+    import os
+
+    import numpy as np
+    from _golden import GOLDEN
+    from graph_representation_learning_b200 import RobustGCN
+    z = np.load(os.path.join(GOLDEN, "robustgcn_small.npz"))
+    m = json.loads(str(z["meta"]))
+    B, N, S = m["B"], m["N"], m["S"]
+    model = RobustGCN(m["in_dim"], m["out_dim"], m["L"], net_size=S)
+    sd0 = {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd0/")}
+    res = model.load_state_dict(sd0, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    model = model.to(dev)
+    V, A, y = (torch.from_numpy(z[k]).to(dev) for k in ("V", "A", "y"))
+    model.eval()
+    with torch.no_grad():
+        out = model([V, A])
+    assert rel_err(out.cpu(), torch.from_numpy(z["logits_eval"])) < TOL_OUT
+    widths = [S, S, S, S, S // 2, S // 2]
+    fm = [torch.from_numpy(np.unpackbits(z[f"feat_mask{i}"])[: B * N * w].reshape(B * N, w).copy()).to(dev).contiguous()
+          for i, w in enumerate(widths)]
+    model.train()
+    logits = model([V, A], masks={"feat": fm})
+    loss = torch.nn.functional.cross_entropy(logits.transpose(1, 2), y)
+    loss.backward()
+    assert rel_err(logits.detach().cpu(), torch.from_numpy(z["logits_train"])) < TOL_OUT
+    assert abs(float(loss) - float(z["loss"])) < 1e-5 * max(1.0, float(z["loss"]))
+    for k, p in model.named_parameters():
+        assert rel_err(p.grad.cpu(), torch.from_numpy(z["grad/" + k])) < TOL_GRAD, k

@@ -214,13 +214,16 @@ def gemm_nt(a_list: Sequence[torch.Tensor], b_list: Sequence[torch.Tensor], out_
 _tn_workspace = {}
 
 
-def gemm_tn(a: torch.Tensor, b: torch.Tensor, fp32_mode: Optional[str] = None) -> torch.Tensor:
+def gemm_tn(a: torch.Tensor, b: torch.Tensor, fp32_mode: Optional[str] = None,
+            split_cache: Optional[dict] = None) -> torch.Tensor:
     """dW[Ma, Nb] = a[R, Ma]^T @ b[R, Nb], fp32 output: the weight-gradient contraction over the node dimension.
 
     fp32 operands, split-K over R with a deterministic reduce: "tf32bc" (default, ``GemmConfig.fp32_mode_bwd``) = the
     TMEM-operand kernel (csrc/gemm_bc_tcgen05.cu, grl_split_act_mn + grl_gemm_tn_bc); "tf32x3" = the MN-major
     three-product kernel (csrc/gemm_x3_tcgen05.cu, grl_gemm_tn).
-    bf16 operands: MN-major kind::f16 kernel, fp32 accumulation and output (csrc/gemm_tcgen05.cu, grl_gemm_tn_bf16)."""
+    bf16 operands: MN-major kind::f16 kernel, fp32 accumulation and output (csrc/gemm_tcgen05.cu, grl_gemm_tn_bf16).
+    ``split_cache``: a dict shared by the calls of one backward step so that the same narrow operand (dZ against the
+    segments of a virtual concat) is split once."""
     if a.dtype not in (torch.float32, torch.bfloat16) or b.dtype != a.dtype:
         raise _lib.GrlError(f"gemm_tn operands must both be fp32 or both bf16, got {a.dtype} / {b.dtype}")
     a, b = _tma_ready(a), _tma_ready(b)
@@ -246,14 +249,22 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, fp32_mode: Optional[str] = None) -
         wide, narrow = (b, a) if swap else (a, b)
         Wn, Nn = wide.shape[1], narrow.shape[1]
         ldp = (Nn + 7) // 8 * 8
-        hi = torch.empty(R, ldp, dtype=torch.float32, device=a.device)
-        packed = torch.empty((R + 31) // 32 * 64, ldp, dtype=torch.bfloat16, device=a.device)
-        _lib.check(lib.grl_split_act_mn(narrow.data_ptr(), narrow.stride(0), hi.data_ptr(), ldp, packed.data_ptr(), ldp,
-                                        R, Nn, _lib.stream_ptr(a.device)), "grl_split_act_mn")
+        key = (narrow.data_ptr(), narrow.stride(0), R, Nn)
+        cached = split_cache.get(key) if split_cache is not None else None
+        if cached is None:
+            hi = torch.empty(R, ldp, dtype=torch.float32, device=a.device)
+            packed = torch.empty((R + 31) // 32 * 64, ldp, dtype=torch.bfloat16, device=a.device)
+            _lib.check(lib.grl_split_act_mn(narrow.data_ptr(), narrow.stride(0), hi.data_ptr(), ldp, packed.data_ptr(),
+                                            ldp, R, Nn, _lib.stream_ptr(a.device)), "grl_split_act_mn")
+            _lib.count_launch(1)
+            if split_cache is not None:
+                split_cache[key] = (hi, packed, narrow)        # keeps `narrow` alive: the key is its address
+        else:
+            hi, packed, _ = cached
         _lib.check(lib.grl_gemm_tn_bc(wide.data_ptr(), wide.stride(0), Wn, hi.data_ptr(), ldp, packed.data_ptr(), ldp, Nn,
                                       R, C.data_ptr(), 1 if swap else 0, ws.data_ptr(), ws.numel(),
                                       _lib.stream_ptr(a.device)), "grl_gemm_tn_bc")
-        _lib.count_launch(3)
+        _lib.count_launch(2)
         return C
     _lib.check(lib.grl_gemm_tn(a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), C.data_ptr(), Nb, Ma, Nb, R,
                                ws.data_ptr(), ws.numel(), _lib.stream_ptr(a.device)), "grl_gemm_tn")
@@ -331,8 +342,8 @@ class _LinearAct(torch.autograd.Function):
         d_weight = d_bias = None
         if ctx.needs_input_grad[0]:
             # fp32 master gradient whatever the compute dtype; [K, N] for h_weights, [N, K] for nn.Linear
-            bwd = GemmConfig.fp32_mode_bwd
-            parts = [gemm_tn(x, dZ, bwd) if weight_is_kn else gemm_tn(dZ, x, bwd) for x in xs]
+            bwd, cache = GemmConfig.fp32_mode_bwd, {}
+            parts = [gemm_tn(x, dZ, bwd, cache) if weight_is_kn else gemm_tn(dZ, x, bwd, cache) for x in xs]
             d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
         if has_bias and ctx.needs_input_grad[1]:
             d_bias = colsum(dZ)

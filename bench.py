@@ -146,6 +146,10 @@ def run_b200(args):
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
     dev = torch.device("cuda", local_rank)
+    numa_cpus = None
+    if world > 1:       # host buffers and copy threads next to this rank's GPU (before any pinned allocation)
+        from graph_representation_learning_b200.trainer import bind_process_to_gpu_numa
+        numa_cpus = bind_process_to_gpu_numa(local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -334,7 +338,8 @@ def run_b200(args):
             "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam (forward includes the CSR/CSC pack of dense A)",
                        "graphs_per_gpu": B, "global_batch": world * B, "parallelism": f"dp{world}",
                        "l2": "inputs (V %.2f GB) larger than L2" % (V.numel() * V.element_size() / 1e9),
-                       "features": "dense U[0,1)"},
+                       "features": "dense U[0,1)",
+                       "host_cpus_rank0": (f"{len(numa_cpus)} GPU-local cores" if numa_cpus else "unbound")},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "bow_features": bow,
         }))
@@ -344,10 +349,27 @@ def run_b200(args):
 
 def main():
     args = parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_b200(args)
+    # stdout carries exactly ONE JSON line: anything native libraries print there (NCCL's version banner under
+    # NCCL_DEBUG=VERSION, ...) is sent to stderr by pointing fd 1 at fd 2 while the run lasts
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        import contextlib
+        import io
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            if args.impl == "reference":
+                run_reference(args)
+            else:
+                run_b200(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    lines = [ln for ln in buf.getvalue().splitlines() if ln.startswith("{")]
+    if lines:
+        print(lines[-1], flush=True)
 
 
 if __name__ == "__main__":

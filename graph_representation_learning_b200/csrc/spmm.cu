@@ -214,6 +214,7 @@ int g_spmm_mode = 0;
 int try_launch_spmm_tile(const int32_t* rowptr, const int32_t* col, const float* w, const void* X, int64_t ldx, void* Y,
                          int64_t ldy, int dtype, int B, int N, int L, int F, cudaStream_t st);   // spmm_tile.cu
 extern int g_slab2_gl;    // spmm_slab2.cu
+extern int g_slab2_vw;    // spmm_slab2.cu
 
 template <typename T, bool kTransposed>
 static int launch_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* widx, const float* w, const void* Xv,
@@ -320,13 +321,14 @@ extern "C" int grl_dropedge_weights(const float* val, const uint8_t* mask, int64
 
 extern "C" int grl_spmm_set_tile_mode(int mode) {
     if (mode != 0 && mode != -1 && mode != -2 && mode != 8 && mode != 16 && mode != 32 && mode != 108 && mode != 116 &&
-        mode != 132) {
+        mode != 132 && mode != 208 && mode != 216) {
         set_error("grl_spmm_set_tile_mode: mode %d not in {0 auto, -1 gather, -2 legacy rows, 8/16/32 slab v1, "
                   "108/116/132 slab v2}", mode);
         return GRL_E_BADARG;
     }
-    g_spmm_mode = mode > 100 ? 0 : mode;             // 108/116/132 only steer grl_spmm_fwd_stream
-    g_slab2_gl = mode > 100 ? mode - 100 : 0;
+    g_spmm_mode = mode > 100 ? 0 : mode;             // 1xx / 2xx only steer grl_spmm_fwd_stream
+    g_slab2_gl = mode > 200 ? mode - 200 : (mode > 100 ? mode - 100 : 0);
+    g_slab2_vw = mode > 200 ? 2 : (mode > 100 ? 1 : 0);    // 208 / 216: two 16-byte words per lane
     return 0;
 }
 

@@ -170,17 +170,22 @@ dropedge_stream_kernel(const int32_t* __restrict__ rowptr, const int32_t* __rest
 
 // Typed rows (t_from, t_to) of a node that kept no entry: written as zeros.  Out of line: rare on dense synthetic
 // graphs, common on real documents (padding nodes carry only the self loop).
-__device__ __noinline__ void slab2_zero_rows(uint8_t* yfirst, uint32_t ldy, uint32_t n_rows) {
+__device__ __noinline__ void slab2_zero_rows(uint8_t* yfirst, uint32_t ldy, uint32_t n_rows, uint32_t word_pitch, int words) {
     for (uint32_t tt = 0; tt < n_rows; ++tt)
-        __stcs(reinterpret_cast<uint4*>(yfirst + static_cast<size_t>(tt) * ldy), make_uint4(0, 0, 0, 0));
+        for (int v = 0; v < words; ++v)
+            __stcs(reinterpret_cast<uint4*>(yfirst + static_cast<size_t>(tt) * ldy + v * word_pitch), make_uint4(0, 0, 0, 0));
 }
 
-template <typename T, int GL>
-__global__ void __launch_bounds__(1024, 1)
+// VW = 16-byte words per lane (1 or 2): word v of lane gl sits at byte gl*16 + v*GL*16 of the slab / output row, so every
+// LDS.128 / st.global of a group stays one contiguous GL*16-byte segment.  VW = 2 halves the bookkeeping instructions per
+// byte (entry decode, compare, address) at 512 threads per CTA (the second accumulator pair needs the registers).
+template <typename T, int GL, int VW>
+__global__ void __launch_bounds__(VW == 2 ? 512 : 1024, 1)
 spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) {
     using Cfg = Slab2Cfg<GL>;
     constexpr int G = Cfg::G, J = Cfg::J, CAP = Cfg::CAP;
-    constexpr uint32_t ROW_BYTES = GL * 16;            // one slab row = the chunk's FC columns
+    constexpr uint32_t WORD_PITCH = GL * 16;           // distance between the words of one lane
+    constexpr uint32_t ROW_BYTES = GL * 16 * VW;       // one slab row = the chunk's FC columns
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t bar[2];
 
@@ -255,8 +260,9 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
             // the open row; yrow = output row of the open typed row (one row before the node's first while none is)
             uint32_t thr = 0, S = slab_lane;
             uint8_t* yrow = ynode - ldy;
-            SlabAcc<T> acc;
-            acc.zero();
+            SlabAcc<T> acc[VW];
+#pragma unroll
+            for (int v = 0; v < VW; ++v) acc[v].zero();
 
             // One entry (x = t << 24 | slab byte offset).  The first entry of a typed row stores the previous row,
             // zero-fills skipped rows, re-bases the state and starts the accumulator with a multiply
@@ -264,17 +270,22 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
             auto walk_step = [&](uint32_t x, uint32_t wbits) {
                 if (x >= thr) {
                     const uint32_t d = x - thr;                   // (typed rows skipped) << 24 | column offset
-                    if (thr != 0u) acc.store_streaming(yrow);
-                    if (d >= 0x01000000u) slab2_zero_rows(yrow + ldy, ldy, d >> 24);
+                    if (thr != 0u) {
+#pragma unroll
+                        for (int v = 0; v < VW; ++v) acc[v].store_streaming(yrow + v * WORD_PITCH);
+                    }
+                    if (d >= 0x01000000u) slab2_zero_rows(yrow + ldy, ldy, d >> 24, WORD_PITCH, VW);
                     uint64_t yn;
                     asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(yn) : "r"((d >> 24) + 1u), "r"(ldy), "l"(reinterpret_cast<uint64_t>(yrow)));
                     yrow = reinterpret_cast<uint8_t*>(yn);
                     const uint32_t tb = x & 0xFF000000u;
                     thr = tb + 0x01000000u;
                     S = slab_lane - tb;
-                    acc.mul(SlabAcc<T>::gather(S + x), wbits);
+#pragma unroll
+                    for (int v = 0; v < VW; ++v) acc[v].mul(SlabAcc<T>::gather(S + x + v * WORD_PITCH), wbits);
                 } else {
-                    acc.fma(SlabAcc<T>::gather(S + x), wbits);
+#pragma unroll
+                    for (int v = 0; v < VW; ++v) acc[v].fma(SlabAcc<T>::gather(S + x + v * WORD_PITCH), wbits);
                 }
             };
 
@@ -333,9 +344,9 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
     }
 }
 
-template <typename T, int GL>
+template <typename T, int GL, int VW>
 static int launch_slab2(const Slab2Params& p, const CUtensorMap& tm, int grid, size_t smem, int threads, cudaStream_t st) {
-    auto kern = spmm_slab2_kernel<T, GL>;
+    auto kern = spmm_slab2_kernel<T, GL, VW>;
     static size_t attr_smem = 0;
     if (smem > attr_smem) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -348,6 +359,8 @@ static int launch_slab2(const Slab2Params& p, const CUtensorMap& tm, int grid, s
 }
 
 int g_slab2_gl = 0;   // 0 = choose the group width, 8 / 16 / 32 = force it (grl_spmm_set_tile_mode 108 / 116 / 132)
+constexpr bool kSlab2PreferTwoWords = false;   // flipped once the A/B (scripts/spmm_bench.py --modes=116,208) says so
+int g_slab2_vw = 0;   // 0 = choose, 1 / 2 = force the 16-byte words per lane (grl_spmm_set_tile_mode 2xx = two words)
 
 // returns 0 = launched, 1 = the slab of one graph does not fit / layout not TMA-able, other = error
 static int try_launch_spmm_slab2(const int2* nodeinfo, const uint2* ew, const void* X, int64_t ldx, void* Y, int64_t ldy,
@@ -360,18 +373,18 @@ static int try_launch_spmm_slab2(const int2* nodeinfo, const uint2* ew, const vo
     const int rows = n_boxes * box_rows;
     constexpr size_t kMaxSmem = 227 * 1024 - 1024;
 
-    struct Plan { int gl, threads, n_buf; size_t smem; uint32_t slab_bytes; };
-    auto plan_for = [&](int gl, Plan* out) -> bool {
-        if (F % (gl * 16 / es) != 0) return false;
+    struct Plan { int gl, vw, threads, n_buf; size_t smem; uint32_t slab_bytes; };
+    auto plan_for = [&](int gl, int vw, Plan* out) -> bool {
+        if (F % (gl * vw * 16 / es) != 0) return false;
         const int G = 32 / gl;
-        int threads = 1024;
+        int threads = vw == 2 ? 512 : 1024;
         while (threads > 32 && (threads / 32) * G > N) threads >>= 1;              // tiny graphs: no idle warps
         const size_t stage = static_cast<size_t>(threads / 32) * G * (64 + 8) * 8;  // Slab2Cfg::STAGE_SLOTS
-        const size_t slab = static_cast<size_t>(rows + 1) * gl * 16;                // + the zero row
+        const size_t slab = static_cast<size_t>(rows + 1) * gl * vw * 16;           // + the zero row
         if (slab >= (1u << 24)) return false;
         const size_t one = slab + stage + 128, two = 2 * slab + stage + 128;
         if (one > kMaxSmem) return false;
-        out->gl = gl; out->threads = threads; out->slab_bytes = static_cast<uint32_t>(slab);
+        out->gl = gl; out->vw = vw; out->threads = threads; out->slab_bytes = static_cast<uint32_t>(slab);
         out->n_buf = two <= kMaxSmem ? 2 : 1;
         out->smem = out->n_buf == 2 ? two : one;
         return true;
@@ -379,13 +392,17 @@ static int try_launch_spmm_slab2(const int2* nodeinfo, const uint2* ew, const vo
     Plan pl{};
     bool have = false;
     if (g_slab2_gl) {
-        have = plan_for(g_slab2_gl, &pl);
+        have = plan_for(g_slab2_gl, g_slab2_vw ? g_slab2_vw : 1, &pl);
     } else {
         for (int gl : {32, 16, 8})                       // the widest group that fits (fewest column chunks per graph)
-            if (plan_for(gl, &pl)) { have = true; break; }
+            if (plan_for(gl, 1, &pl)) { have = true; break; }
+        if (have && kSlab2PreferTwoWords && pl.gl >= 16) {   // same row width with half the lanes and two words per lane
+            Plan p2{};
+            if (plan_for(pl.gl / 2, 2, &p2)) pl = p2;
+        }
     }
     if (!have) return 1;
-    const int n_chunks = F / (pl.gl * 16 / es);
+    const int n_chunks = F / (pl.gl * pl.vw * 16 / es);
     const int n_items = B * n_chunks;
     int per_sm = static_cast<int>((228 * 1024) / (pl.smem + 1024));
     if (per_sm > 2048 / pl.threads) per_sm = 2048 / pl.threads;
@@ -393,12 +410,13 @@ static int try_launch_spmm_slab2(const int2* nodeinfo, const uint2* ew, const vo
     const int grid = n_items < kNumSMs * per_sm ? n_items : kNumSMs * per_sm;
 
     CUtensorMap tm;
-    int rc = make_tmap_plain(&tm, X, es, static_cast<int64_t>(B) * N, F, ldx, pl.gl * 16 / es, box_rows);
+    int rc = make_tmap_plain(&tm, X, es, static_cast<int64_t>(B) * N, F, ldx, pl.gl * pl.vw * 16 / es, box_rows);
     if (rc) return rc;
     Slab2Params p{nodeinfo, ew, static_cast<uint8_t*>(Y), ldy * es, N, L + 1, n_chunks, box_rows, n_boxes, n_items,
                   pl.n_buf, pl.slab_bytes};
 #define GRL_SLAB2_CASE(TT, V) \
-    if (pl.gl == V) return launch_slab2<TT, V>(p, tm, grid, pl.smem, pl.threads, st)
+    if (pl.gl == V && pl.vw == 1) return launch_slab2<TT, V, 1>(p, tm, grid, pl.smem, pl.threads, st); \
+    if (pl.gl == V && pl.vw == 2) return launch_slab2<TT, V, 2>(p, tm, grid, pl.smem, pl.threads, st)
     if (dtype == GRL_F32) {
         GRL_SLAB2_CASE(float, 8); GRL_SLAB2_CASE(float, 16); GRL_SLAB2_CASE(float, 32);
     } else {

@@ -25,6 +25,30 @@ from .features import SparseNodeFeatures
 _ws_cache: Dict[Any, torch.Tensor] = {}
 
 
+def bind_process_to_gpu_numa(device_index: int) -> Optional[list]:
+    """Pin this process to the CPU cores NVML reports as local to GPU ``device_index`` (its NUMA node), so that the
+    pinned host buffers allocated afterwards (first touch) and the H2D copies of the data loader stay on the socket
+    the GPU hangs off.  One process per GPU on an 8-GPU box otherwise shares one node's memory controllers and PCIe
+    root: measured 98 ms per 2.34 GB batch at 8 ranks against 40 ms at 1.  Call before allocating pinned memory.
+    Returns the CPU list, or None when NVML / the cpuset does not allow it (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+        handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        n_cpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, (n_cpu + 63) // 64)
+        local = {c for c in range(n_cpu) if (int(mask[c // 64]) >> (c % 64)) & 1}
+        cpus = sorted(local & os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
 def _reduce_workspace(device: torch.device) -> torch.Tensor:
     """scratch for the block partial sums of the loss / norm reductions (one per device and stream)"""
     from . import _lib

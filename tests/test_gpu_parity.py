@@ -134,7 +134,7 @@ def test_spmm_forward_kernels_agree_bit_for_bit(dev, dtype, B, N, F, density):
         assert getattr(w, "_grl_stream", None) is not None
         outs = {}
         try:
-            for mode in (-2, -1, 8, 16, 32, 0, 108, 116, 132, 100):
+            for mode in (-2, -1, 8, 16, 32, 0, 108, 116, 132, 208, 216, 100):
                 stream_kernel = mode >= 100              # node-stream slab kernel (100 = its own choice of group width)
                 ops._spmm_stream_enabled[0] = stream_kernel
                 _lib.check(lib.grl_spmm_set_tile_mode(0 if mode == 100 else mode), "grl_spmm_set_tile_mode")

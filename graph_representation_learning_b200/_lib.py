@@ -38,6 +38,10 @@ SIGNATURES = {
     "grl_coo_fill": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                              c_void_p, c_void_p]),
     "grl_csr_transpose_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "grl_csr_bitmap_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "grl_csr_count_bitmap": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "grl_csr_fill_bitmap": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p]),
     "grl_csr_transpose": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),
     "grl_csr_transpose_general": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p,

@@ -115,6 +115,98 @@ __global__ void __launch_bounds__(256) csr_fill_kernel(const T* __restrict__ adj
     }
 }
 
+// ---------------------------------------------------------------- dense -> CSR through a bitmap (one read of A)
+// The count pass already sees every element: it also leaves one bit per element (row-major, ceil(N/32) words per
+// adjacency row, 1/16 of an fp16 A), so the fill pass never re-reads the dense tensor -- it walks the bitmap and fetches
+// only the stored values.  Loads of a row are issued four deep (the plain kernels keep one 8/16-byte load per lane in
+// flight: 0.24 + 0.36 ms for the 768 MB fp16 adjacency of cfg2, against 0.12 ms per pass at HBM speed).
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) csr_count_bitmap_kernel(const T* __restrict__ adj, int64_t n_adj_rows, int N, int L,
+                                                               int self_loop, int32_t* __restrict__ rowptr,
+                                                               uint32_t* __restrict__ bitmap, int words) {
+    constexpr int LPW = 32 / VEC;                        // lanes that share one 32-bit bitmap word
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    if (warp == 0 && lane == 0) rowptr[0] = 0;
+    for (int64_t ar = warp; ar < n_adj_rows; ar += n_warps) {
+        const T* row = adj + ar * N;
+        uint32_t* brow = bitmap + ar * words;
+        int cnt = 0;
+        for (int jb = 0; jb < N; jb += 4 * 32 * VEC) {
+            unsigned b[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j0 = jb + u * 32 * VEC + lane * VEC;
+                b[u] = j0 < N ? load_nz_bits<T, VEC>(row, j0, N) : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                cnt += __popc(b[u]);
+                unsigned v = b[u] << (VEC * (lane % LPW));
+#pragma unroll
+                for (int o = 1; o < LPW; o <<= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
+                const int w = (jb + u * 32 * VEC + lane * VEC) >> 5;
+                if (lane % LPW == 0 && w < words) brow[w] = v;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) {
+            const int64_t node = ar / L;
+            const int l = static_cast<int>(ar - node * L);
+            const int64_t r = node * (L + self_loop) + l + self_loop;
+            rowptr[r + 1] = cnt;
+            if (self_loop && l == 0) rowptr[r] = 1;
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) csr_fill_bitmap_kernel(const T* __restrict__ adj, const uint32_t* __restrict__ bitmap,
+                                                              int words, int64_t n_adj_rows, int N, int L, int self_loop,
+                                                              const int32_t* __restrict__ rowptr, int32_t* __restrict__ col,
+                                                              float* __restrict__ val) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t ar = warp; ar < n_adj_rows; ar += n_warps) {
+        const int64_t node = ar / L;
+        const int l = static_cast<int>(ar - node * L);
+        const int64_t r = node * (L + self_loop) + l + self_loop;
+        if (self_loop && l == 0 && lane == 0) {
+            const int32_t e = rowptr[r - 1];
+            col[e] = static_cast<int32_t>(node % N);
+            val[e] = 1.0f;
+        }
+        int32_t out = rowptr[r];
+        const int32_t end = rowptr[r + 1];
+        if (out == end) continue;
+        const T* row = adj + ar * N;
+        const uint32_t* brow = bitmap + ar * words;
+        for (int wb = 0; wb < words && out < end; wb += 32) {
+            unsigned bits = (wb + lane < words) ? __ldg(brow + wb + lane) : 0u;
+            const int mine = __popc(bits);
+            int incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            int pos = out + incl - mine;
+            const int j_base = (wb + lane) << 5;
+            while (bits) {
+                const int k = __ffs(bits) - 1;
+                bits &= bits - 1;
+                col[pos] = j_base + k;
+                val[pos] = to_float(row[j_base + k]);
+                ++pos;
+            }
+            out += __shfl_sync(0xffffffffu, incl, 31);
+        }
+    }
+}
+
 // ---------------------------------------------------------------- COO (edge list) -> CSR
 __global__ void coo_count_kernel(const int32_t* __restrict__ edges, int64_t E, int N, int L,
                                  int32_t* __restrict__ rowptr, int64_t n_nodes) {
@@ -256,9 +348,68 @@ static int launch_fill(const T* adj, int B, int N, int L, int self_loop, const i
     return 0;
 }
 
+template <typename T>
+static int launch_count_bitmap(const T* adj, int B, int N, int L, int self_loop, int32_t* rowptr, uint32_t* bitmap,
+                               cudaStream_t st) {
+    const int64_t rows = static_cast<int64_t>(B) * N * L;
+    const int grid = grid_for(rows * 32, 256);
+    const int words = (N + 31) / 32;
+    constexpr int V16 = 16 / sizeof(T), V8 = 8 / sizeof(T);
+    if (N % V16 == 0 && aligned_to(adj, 16))
+        csr_count_bitmap_kernel<T, V16><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words);
+    else if (N % V8 == 0 && aligned_to(adj, 8))
+        csr_count_bitmap_kernel<T, V8><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words);
+    else
+        csr_count_bitmap_kernel<T, 1><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words);
+    GRL_LAUNCH_CHECK("csr_count_bitmap_kernel");
+    return 0;
+}
+
 }  // namespace grl
 
 using namespace grl;
+
+extern "C" size_t grl_csr_bitmap_bytes(int B, int N, int L) {
+    return sizeof(uint32_t) * static_cast<size_t>(B) * N * L * ((N + 31) / 32);
+}
+
+extern "C" int grl_csr_count_bitmap(const void* adj, int adj_dtype, int B, int N, int L, int self_loop, int32_t* rowptr,
+                                    void* bitmap, void* stream) {
+    GRL_CHECK_ARG(adj && rowptr && bitmap, GRL_E_BADARG, "grl_csr_count_bitmap: null pointer");
+    GRL_CHECK_ARG(B > 0 && N > 0 && L > 0, GRL_E_BADARG, "grl_csr_count_bitmap: B=%d N=%d L=%d must be positive", B, N, L);
+    self_loop = self_loop ? 1 : 0;
+    GRL_CHECK_ARG(static_cast<int64_t>(B) * N * (L + 1) < INT32_MAX, GRL_E_UNSUP, "grl_csr_count_bitmap: too many rows for int32");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint32_t* bm = static_cast<uint32_t*>(bitmap);
+    if (adj_dtype == GRL_F32) return launch_count_bitmap(static_cast<const float*>(adj), B, N, L, self_loop, rowptr, bm, st);
+    if (adj_dtype == GRL_F16) return launch_count_bitmap(static_cast<const __half*>(adj), B, N, L, self_loop, rowptr, bm, st);
+    set_error("grl_csr_count_bitmap: adjacency dtype %d unsupported (f32 or f16)", adj_dtype);
+    return GRL_E_UNSUP;
+}
+
+extern "C" int grl_csr_fill_bitmap(const void* adj, int adj_dtype, const void* bitmap, int B, int N, int L, int self_loop,
+                                   const int32_t* rowptr, int32_t* col, float* val, void* stream) {
+    GRL_CHECK_ARG(adj && bitmap && rowptr && col && val, GRL_E_BADARG, "grl_csr_fill_bitmap: null pointer");
+    GRL_CHECK_ARG(B > 0 && N > 0 && L > 0, GRL_E_BADARG, "grl_csr_fill_bitmap: B=%d N=%d L=%d must be positive", B, N, L);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    self_loop = self_loop ? 1 : 0;
+    const int64_t rows = static_cast<int64_t>(B) * N * L;
+    const int grid = grid_for(rows * 32, 256);
+    const int words = (N + 31) / 32;
+    const uint32_t* bm = static_cast<const uint32_t*>(bitmap);
+    if (adj_dtype == GRL_F32)
+        csr_fill_bitmap_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(adj), bm, words, rows, N, L, self_loop,
+                                                            rowptr, col, val);
+    else if (adj_dtype == GRL_F16)
+        csr_fill_bitmap_kernel<__half><<<grid, 256, 0, st>>>(static_cast<const __half*>(adj), bm, words, rows, N, L, self_loop,
+                                                             rowptr, col, val);
+    else {
+        set_error("grl_csr_fill_bitmap: adjacency dtype %d unsupported (f32 or f16)", adj_dtype);
+        return GRL_E_UNSUP;
+    }
+    GRL_LAUNCH_CHECK("csr_fill_bitmap_kernel");
+    return 0;
+}
 
 extern "C" int grl_csr_count(const void* adj, int adj_dtype, int B, int N, int L, int self_loop, int32_t* rowptr,
                              void* stream) {

@@ -72,7 +72,10 @@ class PackedGraphBatch:
         R = B * N * (L + 1)
         rowptr = torch.empty(R + 1, dtype=torch.int32, device=dev)
         code = _lib.dtype_code(adj)
-        _lib.check(lib.grl_csr_count(adj.data_ptr(), code, B, N, T, sl, rowptr.data_ptr(), st), "grl_csr_count")
+        # one read of the dense tensor: the count pass leaves a bitmap (1/16 of an fp16 A) that the fill pass walks
+        bitmap = torch.empty(lib.grl_csr_bitmap_bytes(B, N, T), dtype=torch.uint8, device=dev)
+        _lib.check(lib.grl_csr_count_bitmap(adj.data_ptr(), code, B, N, T, sl, rowptr.data_ptr(), bitmap.data_ptr(), st),
+                   "grl_csr_count_bitmap")
         ws_bytes = lib.grl_scan_workspace_bytes(R)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         _lib.check(lib.grl_scan_inclusive_i32(rowptr.data_ptr() + 4, R, ws.data_ptr(), ws_bytes, st),
@@ -82,8 +85,8 @@ class PackedGraphBatch:
         col = torch.empty(nnz, dtype=torch.int32, device=dev)
         val = torch.zeros(nnz, dtype=torch.float32, device=dev) if nnz_capacity is not None else \
             torch.empty(nnz, dtype=torch.float32, device=dev)
-        _lib.check(lib.grl_csr_fill(adj.data_ptr(), code, B, N, T, sl, rowptr.data_ptr(), col.data_ptr(),
-                                    val.data_ptr(), st), "grl_csr_fill")
+        _lib.check(lib.grl_csr_fill_bitmap(adj.data_ptr(), code, bitmap.data_ptr(), B, N, T, sl, rowptr.data_ptr(),
+                                           col.data_ptr(), val.data_ptr(), st), "grl_csr_fill_bitmap")
         _lib.count_launch(1)
         g = PackedGraphBatch(B, N, L, nnz, rowptr, col, val)
         if with_transpose:

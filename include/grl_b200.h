@@ -74,6 +74,15 @@ int grl_scan_inclusive_i32(int32_t* data, int64_t n, void* workspace, size_t wor
 int grl_csr_fill(const void* adj, int adj_dtype, int B, int N, int L, int self_loop,
                  const int32_t* rowptr, int32_t* col, float* val, void* stream);
 
+/* The same pack with ONE read of the dense tensor: the count pass also writes one bit per element (row-major,
+ * ceil(N/32) uint32 words per (b, i, l) row; grl_csr_bitmap_bytes), the fill pass walks the bitmap and fetches only the
+ * stored values.  Same rowptr / col / val, bit for bit. */
+size_t grl_csr_bitmap_bytes(int B, int N, int L);
+int grl_csr_count_bitmap(const void* adj, int adj_dtype, int B, int N, int L, int self_loop,
+                         int32_t* rowptr, void* bitmap, void* stream);
+int grl_csr_fill_bitmap(const void* adj, int adj_dtype, const void* bitmap, int B, int N, int L, int self_loop,
+                        const int32_t* rowptr, int32_t* col, float* val, void* stream);
+
 /* CSR pack from an edge list (COO).  Replaces the dense N x L x N intermediate written by
  * Graph -> adj[start, label, end] = 1 (gnn/data_generator/data_process/utils/graph_utils.py:821-829)
  * followed by NumpyPadding (gnn/data_generator/data_collate/numpy_padding.py:63-103).

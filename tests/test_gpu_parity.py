@@ -450,3 +450,44 @@ def test_robust_gcn_matches_reference_vectors(dev):
     assert abs(float(loss) - float(z["loss"])) < 1e-5 * max(1.0, float(z["loss"]))
     for k, p in model.named_parameters():
         assert rel_err(p.grad.cpu(), torch.from_numpy(z["grad/" + k])) < TOL_GRAD, k
+
+
+@pytest.mark.parametrize("B,N,L,dtype,density,weighted", [
+    (3, 500, 6, torch.float16, 0.016, False), (2, 13, 6, torch.float32, 0.3, True), (1, 1030, 2, torch.float16, 0.05, True),
+    (2, 64, 6, torch.float16, 0.2, False), (2, 96, 3, torch.float32, 0.0, False), (1, 37, 6, torch.float16, 1.0, False)])
+def test_csr_pack_single_read_bitmap_equals_two_pass_pack(dev, B, N, L, dtype, density, weighted):
+    """grl_csr_count_bitmap / grl_csr_fill_bitmap (one read of the dense adjacency) against grl_csr_count / grl_csr_fill:
+    rowptr, col, val bit-exact -- 16-byte, 8-byte and scalar load paths, rows longer than 32 bitmap words, empty and full
+    rows, fp16 similarity weights, -0.0 treated as zero."""
+    from graph_representation_learning_b200 import _lib
+    lib = _lib.load()
+    gen = torch.Generator().manual_seed(B * 100 + N)
+    A = (torch.rand(B, N, L, N, generator=gen) < density).float()
+    if weighted:
+        A = A * (0.25 + torch.rand(B, N, L, N, generator=gen))
+    A[0, 0, 0, N - 1] = -0.0
+    A = A.to(dtype).to(dev).contiguous()
+    R = B * N * (L + 1)
+    st, code = _lib.stream_ptr(dev), _lib.dtype_code(A)
+    outs = []
+    for use_bitmap in (False, True):
+        rowptr = torch.empty(R + 1, dtype=torch.int32, device=dev)
+        bitmap = torch.empty(lib.grl_csr_bitmap_bytes(B, N, L), dtype=torch.uint8, device=dev)
+        if use_bitmap:
+            _lib.check(lib.grl_csr_count_bitmap(A.data_ptr(), code, B, N, L, 1, rowptr.data_ptr(), bitmap.data_ptr(), st), "count")
+        else:
+            _lib.check(lib.grl_csr_count(A.data_ptr(), code, B, N, L, 1, rowptr.data_ptr(), st), "count")
+        ws = torch.empty(lib.grl_scan_workspace_bytes(R), dtype=torch.uint8, device=dev)
+        _lib.check(lib.grl_scan_inclusive_i32(rowptr.data_ptr() + 4, R, ws.data_ptr(), ws.numel(), st), "scan")
+        nnz = int(rowptr[-1])
+        col = torch.full((nnz,), -1, dtype=torch.int32, device=dev)
+        val = torch.full((nnz,), float("nan"), device=dev)
+        if use_bitmap:
+            _lib.check(lib.grl_csr_fill_bitmap(A.data_ptr(), code, bitmap.data_ptr(), B, N, L, 1, rowptr.data_ptr(),
+                                               col.data_ptr(), val.data_ptr(), st), "fill")
+        else:
+            _lib.check(lib.grl_csr_fill(A.data_ptr(), code, B, N, L, 1, rowptr.data_ptr(), col.data_ptr(), val.data_ptr(), st), "fill")
+        outs.append((rowptr, col, val))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    assert int(outs[1][0][-1]) == int((A.float() != 0).sum()) + B * N

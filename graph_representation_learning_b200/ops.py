@@ -334,18 +334,41 @@ class _LinearAct(torch.autograd.Function):
         weight, y, *xs = ctx.saved_tensors
         relu, p, weight_is_kn, has_bias = ctx.cfg
         dY = dY.contiguous()
-        if relu or p > 0.0:
+        d_weight = d_bias = None
+        bwd, cache = GemmConfig.fp32_mode_bwd, {}
+        want_w = ctx.needs_input_grad[0]
+        want_b = has_bias and ctx.needs_input_grad[1]
+        M, C = dY.shape
+        fused = (relu and dY.dtype == torch.float32 and bwd == "tf32bc" and C % 8 == 0 and C <= 2048 and
+                 256 % (C // 8) == 0 and M > 0 and y.stride(0) % 4 == 0)
+        if fused:
+            # one pass: dZ, its split for the weight-gradient kernel (when dZ is the narrow operand) and the bias gradient
+            lib = _lib.load()
+            dZ = torch.empty_like(dY)
+            # gemm_tn takes dZ as the narrow (pre-split) operand when it is narrower than x (ties: its second argument)
+            split = want_w and all((x.shape[1] >= C) if weight_is_kn else (x.shape[1] > C) for x in xs)
+            hi = torch.empty(M, C, dtype=torch.float32, device=dY.device) if split else None
+            packed = torch.empty((M + 31) // 32 * 64, C, dtype=torch.bfloat16, device=dY.device) if split else None
+            d_bias = torch.empty(C, dtype=torch.float32, device=dY.device) if want_b else None
+            ws = torch.empty(lib.grl_dz_split_workspace_bytes(M, C) if want_b else 0, dtype=torch.uint8, device=dY.device)
+            flags = _lib.EPI_RELU | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+            _lib.check(lib.grl_dz_split(dY.data_ptr(), dY.stride(0), y.data_ptr(), y.stride(0), dZ.data_ptr(), dZ.stride(0),
+                                        _lib.ptr(hi), _lib.ptr(packed), C, M, C, flags, float(p), _lib.ptr(d_bias),
+                                        _lib.ptr(ws) if want_b else 0, ws.numel(), _lib.stream_ptr(dY.device)),
+                       "grl_dz_split")
+            _lib.count_launch(2 if want_b else 1)
+            if split:
+                cache[(dZ.data_ptr(), dZ.stride(0), M, C)] = (hi, packed, dZ)
+        elif relu or p > 0.0:
             dZ = torch.empty_like(dY)
             epilogue_bwd_(dY, y, dZ, relu, p)
         else:
             dZ = dY
-        d_weight = d_bias = None
-        if ctx.needs_input_grad[0]:
+        if want_w:
             # fp32 master gradient whatever the compute dtype; [K, N] for h_weights, [N, K] for nn.Linear
-            bwd, cache = GemmConfig.fp32_mode_bwd, {}
             parts = [gemm_tn(x, dZ, bwd, cache) if weight_is_kn else gemm_tn(dZ, x, bwd, cache) for x in xs]
             d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
-        if has_bias and ctx.needs_input_grad[1]:
+        if want_b and d_bias is None:
             d_bias = colsum(dZ)
         dxs = []
         off = 0

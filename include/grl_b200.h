@@ -227,6 +227,14 @@ int grl_split_act_mn(const float* src, int64_t ld_src, float* hi, int64_t ld_hi,
 int grl_gemm_tn_bc(const float* A, int64_t lda, int Ma, const float* B_hi, int64_t ldb_hi, const void* B_packed,
                    int64_t ldb_packed, int Nb, int64_t R, float* C, int transpose_out,
                    void* workspace, size_t workspace_bytes, void* stream);
+/* One pass over dY / Y that produces every backward operand of a layer (fp32): dZ = dY * (Y > 0 ? 1/(1-p) : 0) (flags as
+ * grl_bias_act_dropout_bwd), optionally the grl_split_act_mn split of dZ (hi, packed: both or neither, pitch ld_split)
+ * and optionally the bias gradient colsum_out[C] = column sums of dZ, reduced in a fixed order (workspace:
+ * grl_dz_split_workspace_bytes).  Needs C % 8 == 0 and 256 % (C/8) == 0 (GRL_E_UNSUP otherwise: use the separate calls). */
+size_t grl_dz_split_workspace_bytes(int64_t M, int C);
+int grl_dz_split(const float* dY, int64_t lddy, const float* Y, int64_t ldy, float* dZ, int64_t lddz, float* hi,
+                 void* packed, int64_t ld_split, int64_t M, int C, uint32_t flags, float p, float* colsum_out,
+                 void* workspace, size_t workspace_bytes, void* stream);
 /* Weight operand of GRL_GEMM_TF32_BF16C: hi[rows, cols] (pitch ld_hi) = src rounded to nearest tf32; packed = bf16
  * [rows, 2*ceil4(cols)] (pitch ld_packed bf16 elements, multiple of 8): 16-byte chunk c of a row holds
  * {hi[4c..4c+3], lo[4c..4c+3]} with lo = src - hi; entries past cols are zero. */

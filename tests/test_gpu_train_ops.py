@@ -125,3 +125,39 @@ def test_train_step_with_own_loss_clip_adam_equals_library_sequence(dev):
         n_all += d.numel()
         n_far += int((d > 1e-6).sum())
     assert n_far <= 0.002 * n_all, (n_far, n_all)
+
+
+@pytest.mark.parametrize("M,C,p", [(1000, 256, 0.5), (130, 16, 0.0), (4097, 128, 0.5), (33, 512, 0.5)])
+def test_dz_split_matches_separate_kernels(M, C, p):
+    """grl_dz_split (one pass: dZ, tf32 / bf16 split of dZ, bias gradient) against grl_bias_act_dropout_bwd +
+    grl_split_act_mn (bit-exact) and an fp64 column sum (fixed-order fp32 reduction: 1e-6)."""
+    from graph_representation_learning_b200 import _lib, ops
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(M + C)
+    dY = torch.randn(M, C, generator=gen).to(dev)
+    Y = (torch.randn(M, C, generator=gen).clamp_min(0) * (torch.rand(M, C, generator=gen) < 0.5)).to(dev)
+    st = _lib.stream_ptr(dev)
+    flags = _lib.EPI_RELU | (_lib.EPI_DROPOUT if p > 0 else 0)
+    dZ_ref = torch.empty_like(dY)
+    ops.epilogue_bwd_(dY, Y, dZ_ref, True, p)
+    rows_p = (M + 31) // 32 * 64
+    hi_ref = torch.empty(M, C, device=dev)
+    pk_ref = torch.empty(rows_p, C, dtype=torch.bfloat16, device=dev)
+    _lib.check(lib.grl_split_act_mn(dZ_ref.data_ptr(), C, hi_ref.data_ptr(), C, pk_ref.data_ptr(), C, M, C, st), "split")
+    dZ = torch.full_like(dY, float("nan"))
+    hi = torch.full((M, C), float("nan"), device=dev)
+    pk = torch.full((rows_p, C), float("nan"), dtype=torch.bfloat16, device=dev)
+    db = torch.full((C,), float("nan"), device=dev)
+    ws = torch.empty(lib.grl_dz_split_workspace_bytes(M, C), dtype=torch.uint8, device=dev)
+    _lib.check(lib.grl_dz_split(dY.data_ptr(), C, Y.data_ptr(), C, dZ.data_ptr(), C, hi.data_ptr(), pk.data_ptr(), C, M, C,
+                                flags, p, db.data_ptr(), ws.data_ptr(), ws.numel(), st), "grl_dz_split")
+    assert torch.equal(dZ, dZ_ref) and torch.equal(hi, hi_ref)
+    assert torch.equal(pk.view(torch.int16), pk_ref.view(torch.int16))
+    ref = dZ_ref.double().sum(0)
+    assert float((db.double() - ref).norm() / ref.norm().clamp_min(1e-30)) < 1e-6
+    db2 = torch.empty_like(db)
+    _lib.check(lib.grl_dz_split(dY.data_ptr(), C, Y.data_ptr(), C, dZ.data_ptr(), C, 0, 0, C, M, C, flags, p,
+                                db2.data_ptr(), ws.data_ptr(), ws.numel(), st), "grl_dz_split")
+    assert torch.equal(db, db2)                      # fixed summation order
+    assert lib.grl_dz_split(dY.data_ptr(), 53, Y.data_ptr(), 53, dZ.data_ptr(), 53, 0, 0, 56, M, 53, flags, p, 0, 0, 0, st) != 0

@@ -120,3 +120,24 @@ def test_kv_inference_batched_equals_per_document_on_the_cuda_model(tmp_path):
         for x, y in zip(a, b):
             assert x["formal_key"] == y["formal_key"] and x["key_type"] == y["key_type"]
             assert abs(x["confidence"] - y["confidence"]) < 1e-5
+
+
+def test_graphed_eval_forward_matches_eager():
+    """CUDA-graph replay of pack + eval forward == the eager path, bit for bit, on fresh batches after capture"""
+    from graph_representation_learning_b200 import GraphCNNDropEdge
+    from graph_representation_learning_b200.procedures import GraphedEvalForward
+    dev = torch.device("cuda:0")
+    torch.manual_seed(2)
+    B, N, L, D, S, C = 4, 50, 6, 96, 64, 7
+    model = GraphCNNDropEdge(D, C, L, net_size=S).to(dev).eval()
+    gf = GraphedEvalForward(model, B, N, D, L)
+    gen = torch.Generator().manual_seed(1)
+    for density in (0.1, 0.3, 0.0):
+        V = torch.rand(B, N, D, generator=gen)
+        A = (torch.rand(B, N, L, N, generator=gen) < density).half()
+        out = gf(V, A).clone()
+        with torch.no_grad():
+            ref = model([V.to(dev), A.to(dev)])
+        assert torch.equal(out, ref)
+    full = (torch.ones(B, N, L, N)).half()                 # the dense worst case fits the buffers
+    assert torch.equal(gf(V, full), model([V.to(dev), full.to(dev)]).detach())

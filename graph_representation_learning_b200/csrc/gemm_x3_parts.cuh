@@ -18,7 +18,7 @@ struct X3Cfg {
     static constexpr int EPI_PITCH = EPI_COLS + 4;                  // floats (conflict-free STS.128 rows)
     static constexpr int EPI_BYTES = DRAIN_WARPS * 32 * EPI_PITCH * 4;   // one 32 x 16 transposition buffer per drain warp
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
-    static constexpr int TMEM_COLS = 512;                           // main0 | main1 | small | (unused)
+    static constexpr int TMEM_COLS = 512;                           // main0 | main1 | small0 | small1
     static constexpr int THREADS = 64 + 128 + 32 * DRAIN_WARPS;
 };
 

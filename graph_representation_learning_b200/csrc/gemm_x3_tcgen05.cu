@@ -69,8 +69,8 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
     uint64_t* split_bar = bars + 2 * STAGES;       // [STAGES] hi / lo tiles written by the splitter warps
     uint64_t* acc_full = bars + 3 * STAGES;        // [2] chunk accumulator complete
     uint64_t* acc_empty = bars + 3 * STAGES + 2;   // [2] chunk accumulator drained
-    uint64_t* small_empty = bars + 3 * STAGES + 4; // correction accumulator of the previous tile read out
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 5);
+    uint64_t* small_empty = bars + 3 * STAGES + 4; // [2] correction accumulator (one per tile parity) read out
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 6);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
@@ -102,7 +102,8 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], 32 * Cfg::DRAIN_WARPS);
         }
-        mbar_init(small_empty, 32 * Cfg::DRAIN_WARPS);
+        mbar_init(&small_empty[0], 32 * Cfg::DRAIN_WARPS);
+        mbar_init(&small_empty[1], 32 * Cfg::DRAIN_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -146,10 +147,12 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         // ===================================================================== MMA issuer (one lane)
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc(2, Cfg::BLOCK_M, Cfg::BLOCK_N, kTN ? 1 : 0, kTN ? 1 : 0);
-            const uint32_t d_small = tmem_base + 256;
+            // two correction accumulators (TMEM columns 256.. and 384..), alternating per tile: the MMAs of tile i+1 start
+            // while the drain warps still read tile i's corrections (short-K products spent a third of every tile there)
             int it = 0, cg = 0, tl = 0;                            // K-blocks, chunks, tiles issued by this CTA
             for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
-                mbar_wait(small_empty, (tl & 1) ^ 1);              // previous tile's correction sums were read out
+                const uint32_t d_small = tmem_base + 256 + (tl & 1) * 128;
+                mbar_wait(&small_empty[tl & 1], ((tl >> 1) & 1) ^ 1);   // this accumulator's previous tile was read out
                 tc_fence_after_sync();
                 int kk = 0;
                 for (int c = 0; c < n_chunks; ++c, ++cg) {
@@ -214,9 +217,10 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         const int colbase = half * Cfg::DRAIN_COLS;
         const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + colbase;
         float* my_buf = epi_buf + (warp - 6) * 32 * Cfg::EPI_PITCH;
-        int cg = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        int cg = 0, tl = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
             const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+            const uint32_t small_col = 256 + (tl & 1) * 128;
             float acc[Cfg::DRAIN_COLS];
 #pragma unroll
             for (int j = 0; j < Cfg::DRAIN_COLS; ++j) acc[j] = 0.0f;
@@ -238,17 +242,17 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
             if (n_chunks > 0) {
                 // correction terms (complete: the last acc_full commit covers every earlier MMA of the tile)
                 uint32_t r0[32], r1[32];
-                tmem_ld_32x32(lane_base + 256, r0);
-                tmem_ld_32x32(lane_base + 256 + 32, r1);
+                tmem_ld_32x32(lane_base + small_col, r0);
+                tmem_ld_32x32(lane_base + small_col + 32, r1);
                 tmem_ld_wait();
                 tc_fence_before_sync();
-                mbar_arrive(small_empty);                    // the MMA warp may start the next tile's corrections
+                mbar_arrive(&small_empty[tl & 1]);           // this correction accumulator may be reused two tiles on
 #pragma unroll
                 for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
 #pragma unroll
                 for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
             } else {
-                mbar_arrive(small_empty);
+                mbar_arrive(&small_empty[tl & 1]);
             }
             GemmParams q = p;
             if constexpr (kTN)   // partial tile of split blockIdx.y -> its slab of the workspace

@@ -23,9 +23,9 @@ for seed in range(21, 21 + int(sys.argv[1]) if len(sys.argv) > 1 else 29):
     row = {"seed": seed, "cpu_fp32": {k: rel_err(f32_logits if k == "logits" else f32_grads[k], ref_logits if k == "logits" else ref_grads[k]) for k in keys}}
     model = model.to(dev).eval()
     from graph_representation_learning_b200 import _lib
-    for mode, promo in (("tf32x3", 2), ("tf32bc", 4), ("tf32bc", 2), ("tf32bc", 1)):
-        ops.GemmConfig.fp32_mode = ops.GemmConfig.fp32_mode_bwd = mode
-        _lib.load().grl_gemm_bc_set_promo(promo)
+    for mode, mode_b in (("tf32x3", "tf32x3"), ("tf32bc", "tf32bc"), ("tf32x3", "tf32bc"), ("tf32bc", "tf32x3")):
+        ops.GemmConfig.fp32_mode, ops.GemmConfig.fp32_mode_bwd = mode, mode_b
+        promo = mode_b[4:]
         model.zero_grad(set_to_none=True)
         logits = model([V.to(dev), A.to(dev)])
         torch.nn.functional.cross_entropy(logits.transpose(1, 2), y.to(dev)).backward()

@@ -27,6 +27,23 @@ def timed(fn, steps, warmup):
     return e0.elapsed_time(e1) / steps
 
 
+def latencies(fn, steps, warmup):
+    """per-call device latency (one event pair per call, a synchronize between calls as a serving loop would see)"""
+    for _ in range(warmup):
+        fn()
+    out = []
+    for _ in range(steps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out.append(e0.elapsed_time(e1))
+    out.sort()
+    return out
+
+
 def run_train(wl, dev, steps, warmup, edges_mode):
     torch.manual_seed(0)
     model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention).to(dev)
@@ -66,10 +83,12 @@ def run_infer_sweep(dev, sizes, B):
                 g = PackedGraphBatch.from_edges(edges, B, N, wl.num_edges, with_transpose=False)
                 return model([V, g])
         ms = timed(fwd, 5 if N >= 5000 else 10, 2)
+        lat = latencies(fwd, 20 if N >= 5000 else 50, 2)
         logits = fwd()
         assert torch.isfinite(logits).all()
         out.append({"config": f"cfg5: eval forward, batch {B} x {N} nodes (edge-list pack + model)", "N": N,
-                    "latency_ms": round(ms, 3), "graphs_per_s": round(B / ms * 1e3, 1),
+                    "latency_ms": round(ms, 3), "latency_p50_ms": round(lat[len(lat) // 2], 3),
+                    "latency_p99_ms": round(lat[min(len(lat) - 1, int(0.99 * len(lat)))], 3), "graphs_per_s": round(B / ms * 1e3, 1),
                     "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 1e9, 2)})
         print(json.dumps(out[-1]), flush=True)
         del V, edges, logits

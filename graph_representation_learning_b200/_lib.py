@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgrl_b200.so")
 
 GRL_F32, GRL_BF16, GRL_F16 = 0, 1, 2
-EPI_BIAS, EPI_RELU, EPI_DROPOUT = 1, 2, 4
+EPI_BIAS, EPI_RELU, EPI_DROPOUT, EPI_LEAKY = 1, 2, 4, 8
 GRL_E_BADARG, GRL_E_ALIGN, GRL_E_UNSUP, GRL_E_WORKSPACE = -1, -2, -3, -4
 
 _DTYPES = {torch.float32: GRL_F32, torch.bfloat16: GRL_BF16, torch.float16: GRL_F16}

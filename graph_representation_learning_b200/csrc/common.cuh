@@ -137,5 +137,6 @@ template <> __device__ inline float from_float<float>(float x) { return x; }
 template <> __device__ inline __nv_bfloat16 from_float<__nv_bfloat16>(float x) { return __float2bfloat16_rn(x); }
 
 constexpr int kNumSMs = 148;  // B200
+constexpr float kLeakySlope = 0.01f;  // F.leaky_relu's default negative slope (GRL_EPI_LEAKY)
 
 }  // namespace grl

@@ -68,6 +68,9 @@ bias_act_dropout_fwd_kernel(const T* X, int64_t ldx, const float* __restrict__ b
         if (flags & GRL_EPI_RELU) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) v[k] = fmaxf(v[k], 0.0f);
+        } else if (flags & GRL_EPI_LEAKY) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = v[k] > 0.0f ? v[k] : kLeakySlope * v[k];
         }
         if (flags & GRL_EPI_DROPOUT) {
             const int64_t e0 = m * C + c;  // logical element index, independent of ld
@@ -89,7 +92,8 @@ bias_act_dropout_fwd_kernel(const T* X, int64_t ldx, const float* __restrict__ b
 template <typename T>
 __global__ void __launch_bounds__(256)
 bias_act_dropout_bwd_kernel(const T* dY, int64_t lddy, const T* Y, int64_t ldy,
-                            T* dX, int64_t lddx, int64_t M, int C, bool relu, float scale, bool vec) {
+                            T* dX, int64_t lddx, int64_t M, int C, bool relu, float scale, float neg, float zero,
+                            bool vec) {
     const int c4 = C >> 2;
     const int64_t total = M * c4;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -100,7 +104,10 @@ bias_act_dropout_bwd_kernel(const T* dY, int64_t lddy, const T* Y, int64_t ldy,
         load4<T>(dY + m * lddy + c, vec, g);
         if (relu) load4<T>(Y + m * ldy + c, vec, y);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) g[k] = y[k] > 0.0f ? g[k] * scale : 0.0f;
+        for (int k = 0; k < 4; ++k) {
+            const float f = y[k] > 0.0f ? scale : (y[k] < 0.0f ? neg : zero);
+            g[k] = f != 0.0f ? g[k] * f : 0.0f;          // +0 (not -0) where the derivative is zero
+        }
         store4<T>(dX + m * lddx + c, vec, g);
     }
 }
@@ -120,6 +127,7 @@ bias_act_dropout_fwd_scalar_kernel(const T* X, int64_t ldx, const float* __restr
         float v = to_float(X[m * ldx + c]);
         if (flags & GRL_EPI_BIAS) v += bias[c];
         if (flags & GRL_EPI_RELU) v = fmaxf(v, 0.0f);
+        else if (flags & GRL_EPI_LEAKY) v = v > 0.0f ? v : kLeakySlope * v;
         if (flags & GRL_EPI_DROPOUT) {
             const bool keep = mask ? (mask[t] != 0) : (Philox::word(seed, stream_id, static_cast<uint64_t>(t)) >= thresh);
             v = keep ? v * scale : 0.0f;
@@ -131,14 +139,15 @@ bias_act_dropout_fwd_scalar_kernel(const T* X, int64_t ldx, const float* __restr
 template <typename T>
 __global__ void __launch_bounds__(256)
 bias_act_dropout_bwd_scalar_kernel(const T* dY, int64_t lddy, const T* Y, int64_t ldy, T* dX, int64_t lddx, int64_t M,
-                                   int C, bool relu, float scale) {
+                                   int C, bool relu, float scale, float neg, float zero) {
     const int64_t total = M * C;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
         const int64_t m = t / C;
         const int c = static_cast<int>(t - m * C);
         const float y = relu ? to_float(Y[m * ldy + c]) : 1.0f;
-        dX[m * lddx + c] = from_float<T>(y > 0.0f ? to_float(dY[m * lddy + c]) * scale : 0.0f);
+        const float f = y > 0.0f ? scale : (y < 0.0f ? neg : zero);
+        dX[m * lddx + c] = from_float<T>(f != 0.0f ? to_float(dY[m * lddy + c]) * f : 0.0f);
     }
 }
 
@@ -227,23 +236,29 @@ extern "C" int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void
                                         int dtype, int64_t M, int C, uint32_t flags, float p, void* stream) {
     GRL_CHECK_ARG(dY && dX, GRL_E_BADARG, "grl_bias_act_dropout_bwd: null pointer");
     GRL_CHECK_ARG(M >= 0 && C > 0, GRL_E_BADARG, "grl_bias_act_dropout_bwd: bad shape M=%lld C=%d", (long long)M, C);
-    const bool relu = (flags & GRL_EPI_RELU) != 0;
+    // "relu" below = the derivative is read off the sign of the forward output Y (ReLU or leaky ReLU)
+    const bool leaky = (flags & GRL_EPI_LEAKY) != 0 && !(flags & GRL_EPI_RELU);
+    const bool relu = (flags & GRL_EPI_RELU) != 0 || leaky;
     GRL_CHECK_ARG(relu || !(flags & GRL_EPI_DROPOUT) || p == 0.0f, GRL_E_UNSUP,
-                  "grl_bias_act_dropout_bwd: dropout without ReLU is not supported");
-    GRL_CHECK_ARG(!relu || Y, GRL_E_BADARG, "grl_bias_act_dropout_bwd: RELU needs the forward output Y");
+                  "grl_bias_act_dropout_bwd: dropout without an activation is not supported");
+    GRL_CHECK_ARG(!relu || Y, GRL_E_BADARG, "grl_bias_act_dropout_bwd: RELU / LEAKY needs the forward output Y");
     if (M == 0) return 0;
-    const float scale = (flags & GRL_EPI_DROPOUT) ? 1.0f / (1.0f - p) : 1.0f;
+    const bool drop = (flags & GRL_EPI_DROPOUT) && p > 0.0f;
+    const float scale = drop ? 1.0f / (1.0f - p) : 1.0f;
+    // y < 0: leaky slope; y == 0: a dropped element (0) or, without dropout, leaky ReLU at z == 0 (slope, as torch)
+    const float neg = leaky ? kLeakySlope * scale : 0.0f;
+    const float zero = (leaky && !drop) ? kLeakySlope : 0.0f;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (C % 4 != 0) {
         const int sgrid = ew_grid(M * C);
         if (dtype == GRL_F32)
             bias_act_dropout_bwd_scalar_kernel<float><<<sgrid, 256, 0, st>>>(
                 static_cast<const float*>(dY), lddy, static_cast<const float*>(Y), ldy, static_cast<float*>(dX), lddx, M, C,
-                relu, scale);
+                relu, scale, neg, zero);
         else if (dtype == GRL_BF16)
             bias_act_dropout_bwd_scalar_kernel<__nv_bfloat16><<<sgrid, 256, 0, st>>>(
                 static_cast<const __nv_bfloat16*>(dY), lddy, static_cast<const __nv_bfloat16*>(Y), ldy,
-                static_cast<__nv_bfloat16*>(dX), lddx, M, C, relu, scale);
+                static_cast<__nv_bfloat16*>(dX), lddx, M, C, relu, scale, neg, zero);
         else {
             set_error("grl_bias_act_dropout_bwd: dtype %d unsupported", dtype);
             return GRL_E_UNSUP;
@@ -258,11 +273,12 @@ extern "C" int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void
     if (dtype == GRL_F32)
         bias_act_dropout_bwd_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(dY), lddy,
                                                                 static_cast<const float*>(Y), ldy,
-                                                                static_cast<float*>(dX), lddx, M, C, relu, scale, vec);
+                                                                static_cast<float*>(dX), lddx, M, C, relu, scale, neg, zero,
+                                                                vec);
     else if (dtype == GRL_BF16)
         bias_act_dropout_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
             static_cast<const __nv_bfloat16*>(dY), lddy, static_cast<const __nv_bfloat16*>(Y), ldy,
-            static_cast<__nv_bfloat16*>(dX), lddx, M, C, relu, scale, vec);
+            static_cast<__nv_bfloat16*>(dX), lddx, M, C, relu, scale, neg, zero, vec);
     else {
         set_error("grl_bias_act_dropout_bwd: dtype %d unsupported", dtype);
         return GRL_E_UNSUP;

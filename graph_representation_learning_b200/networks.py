@@ -146,12 +146,15 @@ class NodeSelfAtten(nn.Module):
 class RanPACLayer(nn.Module):
     """Frozen random projection (weights ~ N(0,1), requires_grad=False, still part of the state dict)."""
 
-    def __init__(self, input_dim: int, output_dim: int):
+    def __init__(self, input_dim: int, output_dim: int, lambda_value: Optional[float] = None):
         super().__init__()
         self.projection = nn.Linear(input_dim, output_dim, bias=False)
         for param in self.projection.parameters():
             param.requires_grad = False
         nn.init.normal_(self.projection.weight, mean=0, std=1.0)
+        if lambda_value is not None:        # rp_robust_gcn.py:13-24: N(0,1) scaled by sqrt(output_dim) * lambda
+            with torch.no_grad():
+                self.projection.weight *= float(output_dim) ** 0.5 * lambda_value
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return ops.linear_act([_flat(x)], self.projection.weight, None).view(*x.shape[:-1], -1)
@@ -328,4 +331,77 @@ class RobustGCN(BaseNetwork):
                             stream_id=sid + 5)
         g5 = ops.graph_conv([g4], g, w, self.gcn5.h_weights, self.gcn5.bias, relu=True)
         logits = ops.linear_act([g5], self.classifier.weight, self.classifier.bias)
+        return logits.float().view(B, N, self.output_dim)
+
+
+@register_model
+class RPGraphCNNDropEdge(BaseNetwork):
+    """gnn/models/networks/rp_robust_gcn.py:29-115 -- GraphCNNDropEdge with the random projection in FRONT of the
+    attention: emb2 -> frozen ``rp_emb`` (H -> rp_size, leaky ReLU) -> attention over rp_size -> frozen ``rp_final``
+    (rp_size -> rp_size, leaky ReLU, dropout) -> classifier.  Same kernels as GraphCNNDropEdge; leaky ReLU (slope 0.01)
+    is the ``GRL_EPI_LEAKY`` epilogue of the GEMMs."""
+
+    def __init__(self, input_dim: int, output_dim: int, num_edges: int, net_size: int = 256, use_attention: bool = True,
+                 rp_size: int = 10000, lambda_value: float = 0.05):
+        super().__init__()
+        self.output_dim, self.net_size, self.num_edges = output_dim, net_size, num_edges
+        self.rp_size, self.lambda_value, self.use_attention = rp_size, lambda_value, use_attention
+        self.emb1 = make_linear_relu(input_dim, net_size)
+        self.dropout = nn.Dropout(p=0.5)
+        self.edge_dropout = nn.Dropout(p=0.3)
+        self.gcn1 = GraphConv(net_size, net_size, num_edges)
+        self.gcn2 = GraphConv(net_size, net_size, num_edges)
+        self.gcn3 = GraphConv(net_size * 2, net_size, num_edges)
+        self.half_net_size = net_size // 2
+        self.emb2 = make_linear_relu(net_size * 2, self.half_net_size)
+        self.rp_emb = RanPACLayer(self.half_net_size, rp_size, lambda_value)
+        if use_attention:
+            self.self_atten = NodeSelfAtten(rp_size)
+        self.rp_final = RanPACLayer(rp_size, rp_size, lambda_value)
+        self.classifier = nn.Linear(rp_size, output_dim)
+        self.rng_seed: Optional[int] = None
+        self._rng_calls = 0
+
+    def forward(self, inputs: Sequence[Any], efficient_mode: bool = True, *,
+                masks: Optional[Dict[str, Any]] = None) -> torch.Tensor:
+        """Same inputs as GraphCNNDropEdge.forward; ``masks`` = {"edge": 3 x uint8[nnz], "feat": 5 x uint8[B*N, C]}
+        in call order (emb1, g1, g2, g3, rp_final)."""
+        V, A = inputs
+        sparse_v = isinstance(V, SparseNodeFeatures)
+        _lib.require_cuda(V.val if sparse_v else V, "V")
+        B, N = V.shape[0], V.shape[1]
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A)
+        if g.B != B or g.N != N or g.L != self.num_edges:
+            raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
+                                f"num_edges={self.num_edges}")
+        p_feat = self.dropout.p if self.training else 0.0
+        p_edge = self.edge_dropout.p if self.training else 0.0
+        seed = torch.initial_seed() if self.rng_seed is None else self.rng_seed
+        sid = self._rng_calls * 16
+        self._rng_calls += 1
+        em = masks["edge"] if masks else [None] * 3
+        fm = masks["feat"] if masks else [None] * 5
+        lin = self.emb1[0]
+        if sparse_v:
+            emb = ops.sparse_linear_act(V, lin.weight, lin.bias, relu=True, p=p_feat, mask=fm[0], seed=seed, stream_id=sid)
+        else:
+            emb = ops.linear_act([_flat(V).float()], lin.weight, lin.bias, relu=True, p=p_feat, mask=fm[0], seed=seed,
+                                 stream_id=sid)
+        w1 = g.edge_weights(p_edge, seed, sid + 1, em[0])
+        g1 = ops.graph_conv([emb], g, w1, self.gcn1.h_weights, self.gcn1.bias, relu=True, p=p_feat, mask=fm[1],
+                            seed=seed, stream_id=sid + 2)
+        w2 = g.edge_weights(p_edge, seed, sid + 3, em[1])
+        g2 = ops.graph_conv([g1], g, w2, self.gcn2.h_weights, self.gcn2.bias, relu=True, p=p_feat, mask=fm[2],
+                            seed=seed, stream_id=sid + 4)
+        w3 = g.edge_weights(p_edge, seed, sid + 5, em[2])
+        g3 = ops.graph_conv([g1, g2], g, w3, self.gcn3.h_weights, self.gcn3.bias, relu=True, p=p_feat, mask=fm[3],
+                            seed=seed, stream_id=sid + 6)
+        lin = self.emb2[0]
+        new_v = ops.linear_act([g1, g3], lin.weight, lin.bias, relu=True)
+        new_v = ops.linear_act([new_v], self.rp_emb.projection.weight, None, relu="leaky")
+        if self.use_attention:
+            new_v = _flat(self.self_atten(new_v.view(B, N, -1)))
+        new_v = ops.linear_act([new_v], self.rp_final.projection.weight, None, relu="leaky", p=p_feat, mask=fm[4],
+                               seed=seed, stream_id=sid + 7)
+        logits = ops.linear_act([new_v], self.classifier.weight, self.classifier.bias)
         return logits.float().view(B, N, self.output_dim)

@@ -70,9 +70,16 @@ def spmm_bwd_(g: PackedGraphBatch, w: torch.Tensor, dY: torch.Tensor, dX: torch.
     _lib.count_launch(1)
 
 
+def _act_flag(relu) -> int:
+    """``relu`` arguments take True (ReLU), False (none) or "leaky" (leaky ReLU, slope 0.01)"""
+    if relu == "leaky":
+        return _lib.EPI_LEAKY
+    return _lib.EPI_RELU if relu else 0
+
+
 def epilogue_fwd_(X: torch.Tensor, bias: Optional[torch.Tensor], Y: torch.Tensor, relu: bool, p: float,
                   mask: Optional[torch.Tensor], seed: int, stream_id: int) -> None:
-    flags = (_lib.EPI_BIAS if bias is not None else 0) | (_lib.EPI_RELU if relu else 0) | \
+    flags = (_lib.EPI_BIAS if bias is not None else 0) | _act_flag(relu) | \
             (_lib.EPI_DROPOUT if p > 0.0 else 0)
     M, C = X.shape
     if mask is not None:
@@ -88,7 +95,7 @@ def epilogue_fwd_(X: torch.Tensor, bias: Optional[torch.Tensor], Y: torch.Tensor
 
 
 def epilogue_bwd_(dY: torch.Tensor, Y: Optional[torch.Tensor], dX: torch.Tensor, relu: bool, p: float) -> None:
-    flags = (_lib.EPI_RELU if relu else 0) | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+    flags = _act_flag(relu) | (_lib.EPI_DROPOUT if p > 0.0 else 0)
     M, C = dY.shape
     _lib.check(_lib.load().grl_bias_act_dropout_bwd(dY.data_ptr(), _row_major_2d(dY, "dY"), _lib.ptr(Y),
                                                     _row_major_2d(Y, "Y") if Y is not None else C, dX.data_ptr(),
@@ -196,7 +203,7 @@ def gemm_nt(a_list: Sequence[torch.Tensor], b_list: Sequence[torch.Tensor], out_
         bias = bias.float().contiguous()
     if mask is not None and (mask.dtype != torch.uint8 or mask.numel() != M * N or not mask.is_contiguous()):
         raise _lib.GrlError("dropout mask must be contiguous uint8 [M, N]")
-    flags = (_lib.EPI_BIAS if bias is not None else 0) | (_lib.EPI_RELU if relu else 0) | \
+    flags = (_lib.EPI_BIAS if bias is not None else 0) | _act_flag(relu) | \
             (_lib.EPI_DROPOUT if p > 0.0 else 0)
     two = len(a_list) == 2
     a1, (b1, b1lo) = (a_ops[1], b_ops[1]) if two else (None, (None, None))
@@ -339,7 +346,7 @@ class _LinearAct(torch.autograd.Function):
         want_w = ctx.needs_input_grad[0]
         want_b = has_bias and ctx.needs_input_grad[1]
         M, C = dY.shape
-        fused = (relu and dY.dtype == torch.float32 and bwd == "tf32bc" and C % 8 == 0 and C <= 2048 and
+        fused = (relu is True and dY.dtype == torch.float32 and bwd == "tf32bc" and C % 8 == 0 and C <= 2048 and
                  256 % (C // 8) == 0 and M > 0 and y.stride(0) % 4 == 0)
         if fused:
             # one pass: dZ, its split for the weight-gradient kernel (when dZ is the narrow operand) and the bias gradient

@@ -47,6 +47,7 @@ extern "C" {
 #define GRL_EPI_BIAS    1u
 #define GRL_EPI_RELU    2u
 #define GRL_EPI_DROPOUT 4u
+#define GRL_EPI_LEAKY   8u  /* leaky ReLU, slope 0.01 (F.leaky_relu default; rp_robust_gcn.py:100,109); ignored with RELU */
 
 int grl_abi_version(void);
 const char* grl_last_error(void);

@@ -212,11 +212,53 @@ def robust_gcn_case(name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0):
     print(f"{name}: loss {float(loss):.6f}")
 
 
+def rp_dropedge_case(name, seed, B, N, in_dim, S, out_dim, rp_size, L=6, deg=2.0):
+    """Sibling model: gnn/models/networks/rp_robust_gcn.py:29-115 -- random projection in front of the
+    attention, leaky ReLU.  Dropout call order: emb(0) g1(1) g2(2) g3(3) rp_final(4); three DropEdge masks."""
+    from gnn.models.networks.rp_robust_gcn import RPGraphCNNDropEdge
+    gen = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    model = RPGraphCNNDropEdge(in_dim, out_dim, L, net_size=S, rp_size=rp_size)
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    V = torch.rand(B, N, in_dim, generator=gen)
+    A = synth_graph(gen, B, N, L, deg)
+    y = torch.randint(0, out_dim, (B, N), generator=gen)
+    edge_masks = [torch.bernoulli(torch.full((B, (L + 1) * N, N), 0.7), generator=gen).to(torch.uint8) for _ in range(3)]
+    feat_masks = [torch.bernoulli(torch.full((B, N, w), 0.5), generator=gen).to(torch.uint8) for w in (S, S, S, S, rp_size)]
+    model.eval()
+    with torch.no_grad():
+        logits_eval = model([V, A.float()])
+    model.train()
+    model.dropout = InjectedDropout(0.5, feat_masks)
+    model.edge_dropout = InjectedDropout(0.3, edge_masks)
+    logits_train = model.forward([V, A.float()])
+    loss = torch.nn.CrossEntropyLoss()(logits_train.transpose(1, 2), y)
+    loss.backward()
+    out = {"V": V.numpy(), "A": A.numpy(), "y": y.numpy(), "logits_eval": logits_eval.numpy(),
+           "logits_train": logits_train.detach().numpy(), "loss": loss.detach().numpy(),
+           "meta": np.array(json.dumps(dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed,
+                                            rp_size=rp_size)))}
+    for i, m in enumerate(edge_masks):
+        out[f"edge_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for i, m in enumerate(feat_masks):
+        out[f"feat_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for k, v in sd0.items():
+        out["sd0/" + k] = v.numpy()
+    for k, p in model.named_parameters():
+        if p.grad is not None:
+            out["grad/" + k] = p.grad.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(f"{name}: loss {float(loss):.6f}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     GraphCNNDropEdge, NumpyPadding = import_reference()
     if len(sys.argv) > 1 and sys.argv[1] == "robust_gcn":       # add the sibling-model vectors without touching the rest
         robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "rp_dropedge":
+        rp_dropedge_case("rpdropedge_small", seed=22, B=3, N=10, in_dim=24, S=32, out_dim=7, rp_size=48)
         return
     small_model_case(GraphCNNDropEdge, "model_small", seed=11, B=3, N=10, in_dim=24, S=32, out_dim=7)
     small_model_case(GraphCNNDropEdge, "model_weighted_pad", seed=12, B=2, N=12, in_dim=20, S=32, out_dim=5,
@@ -227,6 +269,7 @@ def main():
     init_case(GraphCNNDropEdge)
     collate_case(NumpyPadding)
     robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
+    rp_dropedge_case("rpdropedge_small", seed=22, B=3, N=10, in_dim=24, S=32, out_dim=7, rp_size=48)
 
 
 if __name__ == "__main__":

@@ -452,6 +452,49 @@ def test_robust_gcn_matches_reference_vectors(dev):
         assert rel_err(p.grad.cpu(), torch.from_numpy(z["grad/" + k])) < TOL_GRAD, k
 
 
+def test_rp_graphcnn_dropedge_matches_reference_vectors(dev):
+    """RPGraphCNNDropEdge (gnn/models/networks/rp_robust_gcn.py:29-115): random projection in front of the attention,
+    leaky-ReLU epilogues (GRL_EPI_LEAKY), attention over rp_size (generic-width kernels).  Eval logits and train-mode
+    logits / loss / every gradient with injected DropEdge + dropout masks, against vectors of the unmodified reference."""
+    import json
+    import os
+
+    import numpy as np
+    from _golden import GOLDEN
+    from graph_representation_learning_b200 import PackedGraphBatch, RPGraphCNNDropEdge
+    z = np.load(os.path.join(GOLDEN, "rpdropedge_small.npz"))
+    m = json.loads(str(z["meta"]))
+    B, N, S, L, rp = m["B"], m["N"], m["S"], m["L"], m["rp_size"]
+    model = RPGraphCNNDropEdge(m["in_dim"], m["out_dim"], L, net_size=S, rp_size=rp)
+    sd0 = {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd0/")}
+    res = model.load_state_dict(sd0, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert not model.rp_emb.projection.weight.requires_grad and not model.rp_final.projection.weight.requires_grad
+    model = model.to(dev)
+    V, A, y = (torch.from_numpy(z[k]).to(dev) for k in ("V", "A", "y"))
+    model.eval()
+    with torch.no_grad():
+        out = model([V, A])
+    assert rel_err(out.cpu(), torch.from_numpy(z["logits_eval"])) < TOL_OUT
+    g = PackedGraphBatch.from_dense(A)
+    em = [g.gather_dense_mask(torch.from_numpy(np.unpackbits(z[f"edge_mask{i}"])[: B * (L + 1) * N * N]
+                                               .reshape(B, (L + 1) * N, N).copy()).to(dev)) for i in range(3)]
+    fm = [torch.from_numpy(np.unpackbits(z[f"feat_mask{i}"])[: B * N * w].reshape(B * N, w).copy()).to(dev).contiguous()
+          for i, w in enumerate([S, S, S, S, rp])]
+    model.train()
+    logits = model([V, g], masks={"edge": em, "feat": fm})
+    loss = torch.nn.functional.cross_entropy(logits.transpose(1, 2), y)
+    loss.backward()
+    assert rel_err(logits.detach().cpu(), torch.from_numpy(z["logits_train"])) < TOL_OUT
+    assert abs(float(loss) - float(z["loss"])) < 1e-5 * max(1.0, float(z["loss"]))
+    n = 0
+    for k, p in model.named_parameters():
+        if p.requires_grad:
+            assert rel_err(p.grad.cpu(), torch.from_numpy(z["grad/" + k])) < TOL_GRAD, k
+            n += 1
+    assert n == len([k for k in z.files if k.startswith("grad/")])
+
+
 @pytest.mark.parametrize("B,N,L,dtype,density,weighted", [
     (3, 500, 6, torch.float16, 0.016, False), (2, 13, 6, torch.float32, 0.3, True), (1, 1030, 2, torch.float16, 0.05, True),
     (2, 64, 6, torch.float16, 0.2, False), (2, 96, 3, torch.float32, 0.0, False), (1, 37, 6, torch.float16, 1.0, False)])

@@ -161,3 +161,32 @@ def test_dz_split_matches_separate_kernels(M, C, p):
                                 db2.data_ptr(), ws.data_ptr(), ws.numel(), st), "grl_dz_split")
     assert torch.equal(db, db2)                      # fixed summation order
     assert lib.grl_dz_split(dY.data_ptr(), 53, Y.data_ptr(), 53, dZ.data_ptr(), 53, 0, 0, 56, M, 53, flags, p, 0, 0, 0, st) != 0
+
+
+@pytest.mark.parametrize("M,K,C,p,dtype", [(300, 40, 64, 0.0, torch.float32), (257, 33, 53, 0.0, torch.float32),
+                                           (500, 64, 128, 0.5, torch.float32), (300, 64, 64, 0.5, torch.bfloat16)])
+def test_leaky_relu_epilogue_matches_torch(dev, M, K, C, p, dtype):
+    """GRL_EPI_LEAKY (F.leaky_relu's slope 0.01; rp_robust_gcn.py:100,109) fused in the GEMM epilogue, with and
+    without an injected dropout mask, forward and backward (derivative read off the sign of the output) vs torch."""
+    from graph_representation_learning_b200 import ops
+    gen = torch.Generator().manual_seed(M + C)
+    x = torch.randn(M, K, generator=gen).to(dev).to(dtype).requires_grad_(True)
+    w = (torch.randn(C, K, generator=gen) / K ** 0.5).to(dev).requires_grad_(True)
+    mask = (torch.rand(M, C, generator=gen) < 0.5).to(torch.uint8).to(dev) if p > 0 else None
+    y = ops.linear_act([x], w, None, relu="leaky", p=p, mask=mask)
+    dy = torch.randn(M, C, generator=gen).to(dev).to(dtype)
+    y.backward(dy)
+    xr = x.detach().double().requires_grad_(True)
+    # the bf16 path multiplies by bf16(w): give the reference the same weights, or sign flips of near-zero
+    # pre-activations (1 vs 0.01 derivative) dominate the comparison
+    wr = w.detach().to(dtype).double().requires_grad_(True)
+    yr = torch.nn.functional.leaky_relu(xr @ wr.t())
+    if p > 0:
+        yr = yr * mask.double() / (1.0 - p)
+    yr.backward(dy.double())
+    tol = 2e-6 if dtype == torch.float32 else 1e-2
+    rel = lambda a, b: float((a.double() - b).norm() / b.norm())
+    assert rel(y.detach(), yr.detach()) < tol
+    assert rel(x.grad, xr.grad) < (5e-6 if dtype == torch.float32 else 2e-2)
+    assert rel(w.grad, wr.grad) < (5e-6 if dtype == torch.float32 else 2e-2)
+    assert bool((y.detach() < 0).any())                     # the negative branch is exercised

@@ -8,10 +8,10 @@ from ._lib import GrlError, LIB_PATH  # noqa: F401
 from .graph import PackedGraphBatch  # noqa: F401
 from .features import SparseNodeFeatures  # noqa: F401
 from .networks import (BaseNetwork, GraphCNNDropEdge, GraphConv, NodeSelfAtten, RanPACLayer,  # noqa: F401
-                       RobustGCN, RPGraphCNNDropEdge, make_linear_relu)
+                       RobustGCN, RPGraphCNNDropEdge, DeepRPRobustGCN, DeepRPGCN, make_linear_relu)
 
 from .cl_warper import GNNLearningWarper  # noqa: F401,E402
 from .collate import EdgeListCollate, NumpyPadding  # noqa: F401,E402
 
-__all__ = ["GNNLearningWarper", "NumpyPadding", "EdgeListCollate", "GraphCNNDropEdge", "RobustGCN", "RPGraphCNNDropEdge", "SparseNodeFeatures", "GraphConv", "NodeSelfAtten", "RanPACLayer", "make_linear_relu", "BaseNetwork",
+__all__ = ["GNNLearningWarper", "NumpyPadding", "EdgeListCollate", "GraphCNNDropEdge", "RobustGCN", "RPGraphCNNDropEdge", "DeepRPRobustGCN", "DeepRPGCN", "SparseNodeFeatures", "GraphConv", "NodeSelfAtten", "RanPACLayer", "make_linear_relu", "BaseNetwork",
            "PackedGraphBatch", "GrlError", "LIB_PATH"]

@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgrl_b200.so")
 
 GRL_F32, GRL_BF16, GRL_F16 = 0, 1, 2
-EPI_BIAS, EPI_RELU, EPI_DROPOUT, EPI_LEAKY = 1, 2, 4, 8
+EPI_BIAS, EPI_RELU, EPI_DROPOUT, EPI_LEAKY, EPI_LEAKY02 = 1, 2, 4, 8, 16
 GRL_E_BADARG, GRL_E_ALIGN, GRL_E_UNSUP, GRL_E_WORKSPACE = -1, -2, -3, -4
 
 _DTYPES = {torch.float32: GRL_F32, torch.bfloat16: GRL_BF16, torch.float16: GRL_F16}
@@ -93,6 +93,11 @@ SIGNATURES = {
     "grl_gemm_tn_bc": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p,
                                c_int, c_void_p, c_size_t, c_void_p]),
     "grl_split_tf32_mix": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "grl_bn_workspace_bytes": (c_size_t, [c_int64, c_int]),
+    "grl_bn_act_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_int, c_float,
+                               c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_size_t, c_void_p]),
+    "grl_bn_act_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_float,
+                               c_int, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_size_t, c_void_p]),
 }
 
 GEMM_BF16, GEMM_TF32, GEMM_TF32X3, GEMM_TF32_BF16C = 0, 1, 2, 3

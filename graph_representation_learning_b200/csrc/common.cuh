@@ -137,6 +137,8 @@ template <> __device__ inline float from_float<float>(float x) { return x; }
 template <> __device__ inline __nv_bfloat16 from_float<__nv_bfloat16>(float x) { return __float2bfloat16_rn(x); }
 
 constexpr int kNumSMs = 148;  // B200
-constexpr float kLeakySlope = 0.01f;  // F.leaky_relu's default negative slope (GRL_EPI_LEAKY)
+// negative slope of the leaky-ReLU epilogues: F.leaky_relu's default 0.01 (GRL_EPI_LEAKY) or 0.2 (GRL_EPI_LEAKY02)
+constexpr uint32_t kEpiAnyLeaky = GRL_EPI_LEAKY | GRL_EPI_LEAKY02;
+__host__ __device__ static inline float leaky_slope(uint32_t flags) { return (flags & GRL_EPI_LEAKY02) ? 0.2f : 0.01f; }
 
 }  // namespace grl

@@ -68,9 +68,10 @@ bias_act_dropout_fwd_kernel(const T* X, int64_t ldx, const float* __restrict__ b
         if (flags & GRL_EPI_RELU) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) v[k] = fmaxf(v[k], 0.0f);
-        } else if (flags & GRL_EPI_LEAKY) {
+        } else if (flags & kEpiAnyLeaky) {
+            const float slope = leaky_slope(flags);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) v[k] = v[k] > 0.0f ? v[k] : kLeakySlope * v[k];
+            for (int k = 0; k < 4; ++k) v[k] = v[k] > 0.0f ? v[k] : slope * v[k];
         }
         if (flags & GRL_EPI_DROPOUT) {
             const int64_t e0 = m * C + c;  // logical element index, independent of ld
@@ -127,7 +128,7 @@ bias_act_dropout_fwd_scalar_kernel(const T* X, int64_t ldx, const float* __restr
         float v = to_float(X[m * ldx + c]);
         if (flags & GRL_EPI_BIAS) v += bias[c];
         if (flags & GRL_EPI_RELU) v = fmaxf(v, 0.0f);
-        else if (flags & GRL_EPI_LEAKY) v = v > 0.0f ? v : kLeakySlope * v;
+        else if (flags & kEpiAnyLeaky) v = v > 0.0f ? v : leaky_slope(flags) * v;
         if (flags & GRL_EPI_DROPOUT) {
             const bool keep = mask ? (mask[t] != 0) : (Philox::word(seed, stream_id, static_cast<uint64_t>(t)) >= thresh);
             v = keep ? v * scale : 0.0f;
@@ -237,7 +238,8 @@ extern "C" int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void
     GRL_CHECK_ARG(dY && dX, GRL_E_BADARG, "grl_bias_act_dropout_bwd: null pointer");
     GRL_CHECK_ARG(M >= 0 && C > 0, GRL_E_BADARG, "grl_bias_act_dropout_bwd: bad shape M=%lld C=%d", (long long)M, C);
     // "relu" below = the derivative is read off the sign of the forward output Y (ReLU or leaky ReLU)
-    const bool leaky = (flags & GRL_EPI_LEAKY) != 0 && !(flags & GRL_EPI_RELU);
+    const bool leaky = (flags & kEpiAnyLeaky) != 0 && !(flags & GRL_EPI_RELU);
+    const float slope = leaky_slope(flags);
     const bool relu = (flags & GRL_EPI_RELU) != 0 || leaky;
     GRL_CHECK_ARG(relu || !(flags & GRL_EPI_DROPOUT) || p == 0.0f, GRL_E_UNSUP,
                   "grl_bias_act_dropout_bwd: dropout without an activation is not supported");
@@ -246,8 +248,8 @@ extern "C" int grl_bias_act_dropout_bwd(const void* dY, int64_t lddy, const void
     const bool drop = (flags & GRL_EPI_DROPOUT) && p > 0.0f;
     const float scale = drop ? 1.0f / (1.0f - p) : 1.0f;
     // y < 0: leaky slope; y == 0: a dropped element (0) or, without dropout, leaky ReLU at z == 0 (slope, as torch)
-    const float neg = leaky ? kLeakySlope * scale : 0.0f;
-    const float zero = (leaky && !drop) ? kLeakySlope : 0.0f;
+    const float neg = leaky ? slope * scale : 0.0f;
+    const float zero = (leaky && !drop) ? slope : 0.0f;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (C % 4 != 0) {
         const int sgrid = ew_grid(M * C);

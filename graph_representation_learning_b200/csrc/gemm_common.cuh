@@ -30,9 +30,10 @@ __device__ __forceinline__ void epilogue_store4(const GemmParams& p, int row, in
     if (p.flags & GRL_EPI_RELU) {
 #pragma unroll
         for (int t = 0; t < 4; ++t) v[t] = fmaxf(v[t], 0.0f);
-    } else if (p.flags & GRL_EPI_LEAKY) {
+    } else if (p.flags & kEpiAnyLeaky) {
+        const float slope = leaky_slope(p.flags);
 #pragma unroll
-        for (int t = 0; t < 4; ++t) v[t] = v[t] > 0.0f ? v[t] : kLeakySlope * v[t];
+        for (int t = 0; t < 4; ++t) v[t] = v[t] > 0.0f ? v[t] : slope * v[t];
     }
     if (p.flags & GRL_EPI_DROPOUT) {
         const int64_t e0 = static_cast<int64_t>(row) * p.N + col;

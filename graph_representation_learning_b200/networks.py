@@ -405,3 +405,168 @@ class RPGraphCNNDropEdge(BaseNetwork):
                                seed=seed, stream_id=sid + 7)
         logits = ops.linear_act([new_v], self.classifier.weight, self.classifier.bias)
         return logits.float().view(B, N, self.output_dim)
+
+
+class GCNBlock(nn.Module):
+    """GraphConv + BatchNorm1d + leaky ReLU(0.2) (deep_rp_robust_gcn.py:30-45); parameter container -- the arithmetic
+    runs in ``DeepRPRobustGCN.forward`` on the packed graph."""
+
+    def __init__(self, in_channels: int, out_channels: int, num_edges: int):
+        super().__init__()
+        self.gcn = GraphConv(in_channels, out_channels, num_edges)
+        self.bn = nn.BatchNorm1d(out_channels)
+
+
+class EmbeddingBlock(nn.Module):
+    """Linear + BatchNorm1d + leaky ReLU(0.2) (deep_rp_robust_gcn.py:48-62)."""
+
+    def __init__(self, in_channels: int, out_channels: int):
+        super().__init__()
+        self.emb = nn.Linear(in_channels, out_channels)
+        self.bn = nn.BatchNorm1d(out_channels)
+
+
+@register_model
+class DeepRPRobustGCN(BaseNetwork):
+    """gnn/models/networks/deep_rp_robust_gcn.py:65-168 -- nine GraphConv + BatchNorm + leaky-ReLU(0.2) blocks with two
+    skip concats, DropEdge(0.2) in front of blocks 3, 6, 8, 9, plain dropout(0.3) behind blocks 3, 6, 9 and the
+    attention, a frozen random projection (scaled by ``lambda_value``, leaky 0.2) in front of the attention.  Same
+    SpMM / GEMM / attention kernels as GraphCNNDropEdge; BatchNorm + leaky ReLU is csrc/batchnorm.cu.  fp32."""
+
+    LEAKY = 0.2
+
+    def __init__(self, input_dim: int, output_dim: int, num_edges: int, net_size: int = 256, use_attention: bool = True,
+                 rp_size: int = 10000, lambda_value: float = 0.01):
+        super().__init__()
+        self.output_dim, self.net_size, self.num_edges = output_dim, net_size, num_edges
+        self.rp_size, self.lambda_value, self.use_attention = rp_size, lambda_value, use_attention
+        self.dropout = nn.Dropout(p=0.3)
+        self.edge_dropout = nn.Dropout(p=0.2)
+        self.emb1 = EmbeddingBlock(input_dim, net_size)
+        self.gcn1 = GCNBlock(net_size, net_size, num_edges)
+        self.gcn2 = GCNBlock(net_size, net_size, num_edges)
+        self.gcn3 = GCNBlock(net_size * 2, net_size, num_edges)
+        self.gcn4 = GCNBlock(net_size, net_size, num_edges)
+        self.gcn5 = GCNBlock(net_size, net_size, num_edges)
+        self.gcn6 = GCNBlock(net_size * 2, net_size, num_edges)
+        self.gcn7 = GCNBlock(net_size, net_size, num_edges)
+        self.gcn8 = GCNBlock(net_size, net_size, num_edges)
+        self.gcn9 = GCNBlock(net_size, net_size, num_edges)
+        self.emb2 = EmbeddingBlock(net_size * 2, net_size)
+        self.rp_embed2 = RanPACLayer(net_size, net_size, 1)
+        self.self_atten = NodeSelfAtten(net_size)
+        self.classifier = nn.Linear(net_size, output_dim)
+        self.rng_seed: Optional[int] = None
+        self._rng_calls = 0
+
+    def _block(self, blk: GCNBlock, xs, g, w):
+        z = ops.graph_conv(xs, g, w, blk.gcn.h_weights, blk.gcn.bias)
+        return ops.batchnorm_act(z, blk.bn, self.LEAKY, self.training)
+
+    def forward(self, inputs: Sequence[Any], efficient_mode: bool = True, *,
+                masks: Optional[Dict[str, Any]] = None) -> torch.Tensor:
+        """Same inputs as GraphCNNDropEdge.forward (dense fp32 V).  ``masks`` = {"edge": 4 x uint8[nnz] (blocks 3, 6,
+        8, 9), "feat": 4 x uint8[B*N, net_size] (behind blocks 3, 6, 9 and the attention)}."""
+        V, A = inputs
+        _lib.require_cuda(V, "V")
+        B, N = V.shape[0], V.shape[1]
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A)
+        if g.B != B or g.N != N or g.L != self.num_edges:
+            raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
+                                f"num_edges={self.num_edges}")
+        p_feat = self.dropout.p if self.training else 0.0
+        p_edge = self.edge_dropout.p if self.training else 0.0
+        seed = torch.initial_seed() if self.rng_seed is None else self.rng_seed
+        sid = self._rng_calls * 16
+        self._rng_calls += 1
+        em = masks["edge"] if masks else [None] * 4
+        fm = masks["feat"] if masks else [None] * 4
+
+        def drop(x, k):
+            return _FeatureDropout.apply(x.contiguous(), p_feat, fm[k], seed, sid + 8 + k) if p_feat > 0.0 else x
+
+        w0 = g.edge_weights(0.0)
+        z = ops.linear_act([_flat(V).float()], self.emb1.emb.weight, self.emb1.emb.bias)
+        emb = ops.batchnorm_act(z, self.emb1.bn, self.LEAKY, self.training)
+        g1 = self._block(self.gcn1, [emb], g, w0)
+        g2 = self._block(self.gcn2, [g1], g, w0)
+        g3 = drop(self._block(self.gcn3, [g1, g2], g, g.edge_weights(p_edge, seed, sid + 0, em[0])), 0)
+        g4 = self._block(self.gcn4, [g3], g, w0)
+        g5 = self._block(self.gcn5, [g4], g, w0)
+        g6 = drop(self._block(self.gcn6, [g4, g5], g, g.edge_weights(p_edge, seed, sid + 1, em[1])), 1)
+        g7 = self._block(self.gcn7, [g6], g, w0)
+        g8 = self._block(self.gcn8, [g7], g, g.edge_weights(p_edge, seed, sid + 2, em[2]))
+        g9 = drop(self._block(self.gcn9, [g8], g, g.edge_weights(p_edge, seed, sid + 3, em[3])), 2)
+        z = ops.linear_act([g8, g9], self.emb2.emb.weight, self.emb2.emb.bias)
+        feats = ops.batchnorm_act(z, self.emb2.bn, self.LEAKY, self.training)
+        # RanPACLayer.forward: leaky(projection(x) * lambda, 0.2) = lambda * leaky(projection(x), 0.2) for lambda > 0
+        if self.lambda_value <= 0:
+            raise _lib.GrlError("DeepRPRobustGCN needs lambda_value > 0")
+        feats = ops.linear_act([feats], self.rp_embed2.projection.weight, None, relu="leaky0.2") * self.lambda_value
+        feats = drop(_flat(self.self_atten(feats.view(B, N, -1))), 3)
+        logits = ops.linear_act([feats], self.classifier.weight, self.classifier.bias)
+        return logits.float().view(B, N, self.output_dim)
+
+
+class CustomGCNSequential(nn.Module):
+    """deep_rp_gcn.py:70-103 with the file's constants (NUM_GCN_LAYERS = 29, SKIP_CONNECTION_POS = 3, no RP layers):
+    every third block takes the concat [feats, feats] (the reference re-binds ``prev_feats`` right before using it)."""
+
+    NUM_GCN_LAYERS = 29
+    SKIP_CONNECTION_POS = 3
+
+    def __init__(self, net_size: int, num_edges: int, lambda_value: float):
+        super().__init__()
+        self.layers = nn.ModuleList()
+        for ii in range(self.NUM_GCN_LAYERS):
+            wide = ii % self.SKIP_CONNECTION_POS == 0
+            self.layers.append(GCNBlock(net_size * 2 if wide else net_size, net_size, num_edges))
+
+
+@register_model
+class DeepRPGCN(BaseNetwork):
+    """gnn/models/networks/deep_rp_gcn.py:106-150 -- embedding block, 29 GraphConv + BatchNorm + leaky(0.2) blocks on the
+    un-dropped adjacency, embedding block, dropout(0.3), classifier.  fp32."""
+
+    LEAKY = 0.2
+
+    def __init__(self, input_dim: int, output_dim: int, num_edges: int, net_size: int = 256, rp_size: int = 10000,
+                 lambda_value: float = 0.01):
+        super().__init__()
+        self.output_dim, self.net_size, self.num_edges = output_dim, net_size, num_edges
+        self.rp_size, self.lambda_value = rp_size, lambda_value
+        self.dropout = nn.Dropout(p=0.3)
+        self.emb1 = EmbeddingBlock(input_dim, net_size)
+        self.gcn_layers = CustomGCNSequential(net_size, num_edges, lambda_value)
+        self.emb2 = EmbeddingBlock(net_size, net_size)
+        self.classifier = nn.Linear(net_size, output_dim)
+        self.rng_seed: Optional[int] = None
+        self._rng_calls = 0
+
+    def forward(self, inputs: Sequence[Any], efficient_mode: bool = True, *,
+                masks: Optional[Dict[str, Any]] = None) -> torch.Tensor:
+        """``masks`` = {"feat": [uint8[B*N, net_size]]} (the one dropout in front of the classifier)."""
+        V, A = inputs
+        _lib.require_cuda(V, "V")
+        B, N = V.shape[0], V.shape[1]
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A)
+        if g.B != B or g.N != N or g.L != self.num_edges:
+            raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
+                                f"num_edges={self.num_edges}")
+        p_feat = self.dropout.p if self.training else 0.0
+        seed = torch.initial_seed() if self.rng_seed is None else self.rng_seed
+        sid = self._rng_calls * 16
+        self._rng_calls += 1
+        w0 = g.edge_weights(0.0)
+        z = ops.linear_act([_flat(V).float()], self.emb1.emb.weight, self.emb1.emb.bias)
+        feats = ops.batchnorm_act(z, self.emb1.bn, self.LEAKY, self.training)
+        for idx, blk in enumerate(self.gcn_layers.layers):
+            xs = [feats, feats] if idx % CustomGCNSequential.SKIP_CONNECTION_POS == 0 else [feats]
+            z = ops.graph_conv(xs, g, w0, blk.gcn.h_weights, blk.gcn.bias)
+            feats = ops.batchnorm_act(z, blk.bn, self.LEAKY, self.training)
+        z = ops.linear_act([feats], self.emb2.emb.weight, self.emb2.emb.bias)
+        feats = ops.batchnorm_act(z, self.emb2.bn, self.LEAKY, self.training)
+        if p_feat > 0.0:
+            feats = _FeatureDropout.apply(feats.contiguous(), p_feat, masks["feat"][0] if masks else None, seed, sid)
+        logits = ops.linear_act([feats], self.classifier.weight, self.classifier.bias)
+        return logits.float().view(B, N, self.output_dim)

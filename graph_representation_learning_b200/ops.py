@@ -71,9 +71,11 @@ def spmm_bwd_(g: PackedGraphBatch, w: torch.Tensor, dY: torch.Tensor, dX: torch.
 
 
 def _act_flag(relu) -> int:
-    """``relu`` arguments take True (ReLU), False (none) or "leaky" (leaky ReLU, slope 0.01)"""
+    """``relu`` arguments take True (ReLU), False (none), "leaky" (leaky ReLU, slope 0.01) or "leaky0.2" """
     if relu == "leaky":
         return _lib.EPI_LEAKY
+    if relu == "leaky0.2":
+        return _lib.EPI_LEAKY02
     return _lib.EPI_RELU if relu else 0
 
 
@@ -463,6 +465,64 @@ def sparse_linear_act(feats, weight: torch.Tensor, bias: Optional[torch.Tensor],
                       mask: Optional[torch.Tensor] = None, seed: int = 0, stream_id: int = 0,
                       compute_dtype: torch.dtype = torch.float32) -> torch.Tensor:
     return _SparseLinearAct.apply(feats, weight, bias, relu, float(p), mask, seed, stream_id, compute_dtype)
+
+
+class _BatchNormAct(torch.autograd.Function):
+    """leaky_relu(BatchNorm1d(x), slope) over the rows of x [M, C] (csrc/batchnorm.cu; fp32)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, momentum, eps, training, slope):
+        lib = _lib.load()
+        x = x.contiguous()
+        M, C = x.shape
+        y = torch.empty_like(x)
+        mean = torch.empty(C, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+        ws = torch.empty(lib.grl_bn_workspace_bytes(M, C), dtype=torch.uint8, device=x.device)
+        _lib.check(lib.grl_bn_act_fwd(x.data_ptr(), x.stride(0), gamma.data_ptr(), beta.data_ptr(), _lib.ptr(running_mean),
+                                      _lib.ptr(running_var), float(momentum), float(eps), int(training), float(slope),
+                                      y.data_ptr(), y.stride(0), mean.data_ptr(), rstd.data_ptr(), M, C, ws.data_ptr(),
+                                      ws.numel(), _lib.stream_ptr(x.device)), "grl_bn_act_fwd")
+        _lib.count_launch(5 if training else 2)
+        ctx.save_for_backward(x, y, gamma, mean, rstd)
+        ctx.cfg = (bool(training), float(slope))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, gamma, mean, rstd = ctx.saved_tensors
+        training, slope = ctx.cfg
+        lib = _lib.load()
+        dy = dy.contiguous()
+        M, C = x.shape
+        dx = torch.empty_like(x)
+        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(C, dtype=torch.float32, device=x.device)
+        ws = torch.empty(lib.grl_bn_workspace_bytes(M, C), dtype=torch.uint8, device=x.device)
+        _lib.check(lib.grl_bn_act_bwd(dy.data_ptr(), dy.stride(0), y.data_ptr(), y.stride(0), x.data_ptr(), x.stride(0),
+                                      gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(), slope, int(training),
+                                      dx.data_ptr(), dx.stride(0), dgamma.data_ptr(), dbeta.data_ptr(), M, C, ws.data_ptr(),
+                                      ws.numel(), _lib.stream_ptr(x.device)), "grl_bn_act_bwd")
+        _lib.count_launch(3)
+        return dx, dgamma, dbeta, None, None, None, None, None, None
+
+
+def batchnorm_act(x: torch.Tensor, bn: torch.nn.BatchNorm1d, slope: float, training: bool) -> torch.Tensor:
+    """``F.leaky_relu(bn(x^T)^T, slope)`` for x [M, C] with ``bn`` an ``nn.BatchNorm1d`` used as the parameter / buffer
+    container (GCNBlock / EmbeddingBlock, deep_rp_robust_gcn.py:30-62).  Training mode normalises with batch statistics
+    and updates ``running_mean`` / ``running_var`` / ``num_batches_tracked`` like torch."""
+    if x.dtype != torch.float32:
+        raise _lib.GrlError("batchnorm_act runs in fp32")
+    use_batch = training or bn.running_mean is None
+    momentum = 0.0
+    if training and bn.track_running_stats and bn.running_mean is not None:
+        bn.num_batches_tracked += 1
+        momentum = 1.0 / float(bn.num_batches_tracked) if bn.momentum is None else bn.momentum
+    rm = bn.running_mean if (bn.track_running_stats and bn.running_mean is not None) else None
+    rv = bn.running_var if rm is not None else None
+    upd = training and rm is not None
+    return _BatchNormAct.apply(x, bn.weight, bn.bias, rm if (upd or not use_batch) else None,
+                               rv if (upd or not use_batch) else None, momentum, bn.eps, use_batch, slope)
 
 
 def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Tensor, h_weights: torch.Tensor,

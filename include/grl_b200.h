@@ -48,6 +48,7 @@ extern "C" {
 #define GRL_EPI_RELU    2u
 #define GRL_EPI_DROPOUT 4u
 #define GRL_EPI_LEAKY   8u  /* leaky ReLU, slope 0.01 (F.leaky_relu default; rp_robust_gcn.py:100,109); ignored with RELU */
+#define GRL_EPI_LEAKY02 16u /* leaky ReLU, slope 0.2 (deep_rp_robust_gcn.py:26,44,61); ignored with RELU */
 
 int grl_abi_version(void);
 const char* grl_last_error(void);
@@ -236,6 +237,21 @@ size_t grl_dz_split_workspace_bytes(int64_t M, int C);
 int grl_dz_split(const float* dY, int64_t lddy, const float* Y, int64_t ldy, float* dZ, int64_t lddz, float* hi,
                  void* packed, int64_t ld_split, int64_t M, int C, uint32_t flags, float p, float* colsum_out,
                  void* workspace, size_t workspace_bytes, void* stream);
+/* BatchNorm1d over the M node rows of X[M, C] followed by leaky ReLU(slope) -- GCNBlock / EmbeddingBlock of the DeepRP
+ * sibling models (deep_rp_robust_gcn.py:30-62: nn.BatchNorm1d on [B, C, N] + F.leaky_relu(0.2)); fp32.
+ * training != 0: batch statistics (biased variance) normalise, running_mean / running_var (may be null) are updated with
+ * `momentum` and the unbiased variance; training == 0: the running statistics normalise.  save_mean / save_rstd [C] are
+ * always written (the backward reads them).  All column reductions are two-stage in a fixed order (workspace:
+ * grl_bn_workspace_bytes).  Backward: dX, dgamma[C], dbeta[C]; training == 0 treats the statistics as constants. */
+size_t grl_bn_workspace_bytes(int64_t M, int C);
+int grl_bn_act_fwd(const float* X, int64_t ldx, const float* gamma, const float* beta, float* running_mean,
+                   float* running_var, float momentum, float eps, int training, float slope, float* Y, int64_t ldy,
+                   float* save_mean, float* save_rstd, int64_t M, int C, void* workspace, size_t workspace_bytes,
+                   void* stream);
+int grl_bn_act_bwd(const float* dY, int64_t lddy, const float* Y, int64_t ldy, const float* X, int64_t ldx,
+                   const float* gamma, const float* save_mean, const float* save_rstd, float slope, int training,
+                   float* dX, int64_t lddx, float* dgamma, float* dbeta, int64_t M, int C, void* workspace,
+                   size_t workspace_bytes, void* stream);
 /* Weight operand of GRL_GEMM_TF32_BF16C: hi[rows, cols] (pitch ld_hi) = src rounded to nearest tf32; packed = bf16
  * [rows, 2*ceil4(cols)] (pitch ld_packed bf16 elements, multiple of 8): 16-byte chunk c of a row holds
  * {hi[4c..4c+3], lo[4c..4c+3]} with lo = src - hi; entries past cols are zero. */

@@ -251,11 +251,102 @@ def rp_dropedge_case(name, seed, B, N, in_dim, S, out_dim, rp_size, L=6, deg=2.0
     print(f"{name}: loss {float(loss):.6f}")
 
 
+def deep_rp_case(name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0):
+    """Sibling model: gnn/models/networks/deep_rp_robust_gcn.py:65-168 -- nine GraphConv + BatchNorm1d +
+    leaky-ReLU(0.2) blocks.  DropEdge(0.2) masks in call order: blocks 3, 6, 8, 9; dropout(0.3): behind blocks 3, 6, 9
+    and the attention.  BatchNorm parameters / running statistics are randomised so they matter; the state after the
+    train-mode forward (running statistics, num_batches_tracked) is stored too."""
+    from gnn.models.networks.deep_rp_robust_gcn import DeepRPRobustGCN
+    gen = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    model = DeepRPRobustGCN(in_dim, out_dim, L, net_size=S, lambda_value=0.05)
+    with torch.no_grad():
+        for k, v in model.state_dict().items():
+            if ".bn." in k and k.endswith("weight"):
+                v.copy_(0.5 + torch.rand(v.shape, generator=gen))
+            elif ".bn." in k and k.endswith(("bias", "running_mean")):
+                v.copy_(0.2 * torch.randn(v.shape, generator=gen))
+            elif ".bn." in k and k.endswith("running_var"):
+                v.copy_(0.5 + torch.rand(v.shape, generator=gen))
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    V = torch.rand(B, N, in_dim, generator=gen)
+    A = synth_graph(gen, B, N, L, deg)
+    y = torch.randint(0, out_dim, (B, N), generator=gen)
+    edge_masks = [torch.bernoulli(torch.full((B, (L + 1) * N, N), 0.8), generator=gen).to(torch.uint8) for _ in range(4)]
+    feat_masks = [torch.bernoulli(torch.full((B, N, S), 0.7), generator=gen).to(torch.uint8) for _ in range(4)]
+    model.eval()
+    with torch.no_grad():
+        logits_eval = model([V, A.float()])
+    model.train()
+    model.dropout = InjectedDropout(0.3, feat_masks)
+    model.edge_dropout = InjectedDropout(0.2, edge_masks)
+    logits_train = model.forward([V, A.float()])
+    loss = torch.nn.CrossEntropyLoss()(logits_train.transpose(1, 2), y)
+    loss.backward()
+    out = {"V": V.numpy(), "A": A.numpy(), "y": y.numpy(), "logits_eval": logits_eval.numpy(),
+           "logits_train": logits_train.detach().numpy(), "loss": loss.detach().numpy(),
+           "meta": np.array(json.dumps(dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed,
+                                            lambda_value=0.05)))}
+    for i, m in enumerate(edge_masks):
+        out[f"edge_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for i, m in enumerate(feat_masks):
+        out[f"feat_mask{i}"] = np.packbits(m.numpy().reshape(-1))
+    for k, v in sd0.items():
+        out["sd0/" + k] = v.numpy()
+    for k, v in model.state_dict().items():
+        if ".bn.running" in k or k.endswith("num_batches_tracked"):
+            out["sd1/" + k] = v.detach().numpy()
+    for k, p in model.named_parameters():
+        if p.grad is not None:
+            out["grad/" + k] = p.grad.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(f"{name}: loss {float(loss):.6f}")
+
+
+def deep_rp_gcn_case(name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0):
+    """Sibling model: gnn/models/networks/deep_rp_gcn.py:106-150 -- 29 GraphConv + BatchNorm1d +
+    leaky(0.2) blocks, no DropEdge, one dropout(0.3) in front of the classifier."""
+    from gnn.models.networks.deep_rp_gcn import DeepRPGCN
+    gen = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    model = DeepRPGCN(in_dim, out_dim, L, net_size=S)
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    V = torch.rand(B, N, in_dim, generator=gen)
+    A = synth_graph(gen, B, N, L, deg)
+    y = torch.randint(0, out_dim, (B, N), generator=gen)
+    feat_masks = [torch.bernoulli(torch.full((B, N, S), 0.7), generator=gen).to(torch.uint8)]
+    model.eval()
+    with torch.no_grad():
+        logits_eval = model([V, A.float()])
+    model.train()
+    model.dropout = InjectedDropout(0.3, feat_masks)
+    logits_train = model.forward([V, A.float()])
+    loss = torch.nn.CrossEntropyLoss()(logits_train.transpose(1, 2), y)
+    loss.backward()
+    out = {"V": V.numpy(), "A": A.numpy(), "y": y.numpy(), "logits_eval": logits_eval.numpy(),
+           "logits_train": logits_train.detach().numpy(), "loss": loss.detach().numpy(),
+           "feat_mask0": np.packbits(feat_masks[0].numpy().reshape(-1)),
+           "meta": np.array(json.dumps(dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed)))}
+    for k, v in sd0.items():
+        out["sd0/" + k] = v.numpy()
+    for k, p in model.named_parameters():
+        if p.grad is not None:
+            out["grad/" + k] = p.grad.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(f"{name}: loss {float(loss):.6f}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     GraphCNNDropEdge, NumpyPadding = import_reference()
     if len(sys.argv) > 1 and sys.argv[1] == "robust_gcn":       # add the sibling-model vectors without touching the rest
         robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "deep_rp":
+        deep_rp_case("deeprp_small", seed=23, B=3, N=10, in_dim=24, S=32, out_dim=7)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "deep_rp_gcn":
+        deep_rp_gcn_case("deeprpgcn_small", seed=24, B=2, N=9, in_dim=16, S=16, out_dim=5)
         return
     if len(sys.argv) > 1 and sys.argv[1] == "rp_dropedge":
         rp_dropedge_case("rpdropedge_small", seed=22, B=3, N=10, in_dim=24, S=32, out_dim=7, rp_size=48)
@@ -270,6 +361,8 @@ def main():
     collate_case(NumpyPadding)
     robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
     rp_dropedge_case("rpdropedge_small", seed=22, B=3, N=10, in_dim=24, S=32, out_dim=7, rp_size=48)
+    deep_rp_case("deeprp_small", seed=23, B=3, N=10, in_dim=24, S=32, out_dim=7)
+    deep_rp_gcn_case("deeprpgcn_small", seed=24, B=2, N=9, in_dim=16, S=16, out_dim=5)
 
 
 if __name__ == "__main__":

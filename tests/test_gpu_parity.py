@@ -495,6 +495,103 @@ def test_rp_graphcnn_dropedge_matches_reference_vectors(dev):
     assert n == len([k for k in z.files if k.startswith("grad/")])
 
 
+def test_deep_rp_robust_gcn_matches_reference_vectors(dev):
+    """DeepRPRobustGCN (gnn/models/networks/deep_rp_robust_gcn.py:65-168): nine GraphConv + BatchNorm1d + leaky(0.2)
+    blocks on the packed graph (csrc/batchnorm.cu).  Eval logits (running statistics), train-mode logits / loss / every
+    gradient with injected DropEdge + dropout masks, and the BatchNorm running statistics after the train forward,
+    against vectors of the unmodified reference."""
+    import json
+    import os
+
+    import numpy as np
+    from _golden import GOLDEN
+    from graph_representation_learning_b200 import DeepRPRobustGCN, PackedGraphBatch
+    z = np.load(os.path.join(GOLDEN, "deeprp_small.npz"))
+    m = json.loads(str(z["meta"]))
+    B, N, S, L = m["B"], m["N"], m["S"], m["L"]
+    model = DeepRPRobustGCN(m["in_dim"], m["out_dim"], L, net_size=S, lambda_value=m["lambda_value"])
+    sd0 = {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd0/")}
+    res = model.load_state_dict(sd0, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    model = model.to(dev)
+    V, A, y = (torch.from_numpy(z[k]).to(dev) for k in ("V", "A", "y"))
+    model.eval()
+    with torch.no_grad():
+        out = model([V, A])
+    assert rel_err(out.cpu(), torch.from_numpy(z["logits_eval"])) < TOL_OUT
+    g = PackedGraphBatch.from_dense(A)
+    em = [g.gather_dense_mask(torch.from_numpy(np.unpackbits(z[f"edge_mask{i}"])[: B * (L + 1) * N * N]
+                                               .reshape(B, (L + 1) * N, N).copy()).to(dev)) for i in range(4)]
+    fm = [torch.from_numpy(np.unpackbits(z[f"feat_mask{i}"])[: B * N * S].reshape(B * N, S).copy()).to(dev).contiguous()
+          for i in range(4)]
+    model.train()
+    logits = model([V, g], masks={"edge": em, "feat": fm})
+    loss = torch.nn.functional.cross_entropy(logits.transpose(1, 2), y)
+    loss.backward()
+    assert rel_err(logits.detach().cpu(), torch.from_numpy(z["logits_train"])) < TOL_OUT
+    assert abs(float(loss) - float(z["loss"])) < 1e-5 * max(1.0, float(z["loss"]))
+    n = 0
+    for k, p in model.named_parameters():
+        if p.requires_grad:
+            ref = torch.from_numpy(z["grad/" + k])
+            if k.endswith(("emb.bias", "gcn.bias")):
+                # a bias in front of BatchNorm has zero gradient (the batch mean removes it): both sides hold rounding noise
+                assert float(ref.abs().max()) < 1e-6 and float(p.grad.abs().max()) < 1e-6, k
+            else:
+                assert rel_err(p.grad.cpu(), ref) < TOL_GRAD, k
+            n += 1
+    assert n == len([k for k in z.files if k.startswith("grad/")])
+    sd = model.state_dict()
+    for k in z.files:
+        if k.startswith("sd1/"):
+            name = k.split("/", 1)[1]
+            if name.endswith("num_batches_tracked"):
+                assert int(sd[name]) == int(z[k]), name
+            else:
+                assert rel_err(sd[name].cpu(), torch.from_numpy(z[k])) < 1e-6, name
+
+
+def test_deep_rp_gcn_matches_reference_vectors(dev):
+    """DeepRPGCN (gnn/models/networks/deep_rp_gcn.py:106-150): 29 GraphConv + BatchNorm1d + leaky(0.2) blocks, every third
+    on the concat [feats, feats]; eval logits, train-mode logits / loss / gradients against vectors of the unmodified
+    reference.  29 normalised layers amplify fp32 rounding: the bars are 10x the single-model ones (the reference's own
+    fp32 run differs from its fp64 run by as much)."""
+    import json
+    import os
+
+    import numpy as np
+    from _golden import GOLDEN
+    from graph_representation_learning_b200 import DeepRPGCN
+    z = np.load(os.path.join(GOLDEN, "deeprpgcn_small.npz"))
+    m = json.loads(str(z["meta"]))
+    B, N, S, L = m["B"], m["N"], m["S"], m["L"]
+    model = DeepRPGCN(m["in_dim"], m["out_dim"], L, net_size=S)
+    sd0 = {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd0/")}
+    res = model.load_state_dict(sd0, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    model = model.to(dev)
+    V, A, y = (torch.from_numpy(z[k]).to(dev) for k in ("V", "A", "y"))
+    model.eval()
+    with torch.no_grad():
+        out = model([V, A])
+    assert rel_err(out.cpu(), torch.from_numpy(z["logits_eval"])) < 10 * TOL_OUT
+    fm = [torch.from_numpy(np.unpackbits(z["feat_mask0"])[: B * N * S].reshape(B * N, S).copy()).to(dev).contiguous()]
+    model.train()
+    logits = model([V, A], masks={"feat": fm})
+    loss = torch.nn.functional.cross_entropy(logits.transpose(1, 2), y)
+    loss.backward()
+    assert rel_err(logits.detach().cpu(), torch.from_numpy(z["logits_train"])) < 10 * TOL_OUT
+    assert abs(float(loss.detach()) - float(z["loss"])) < 1e-4 * max(1.0, float(z["loss"]))
+    worst = {}
+    for k, p in model.named_parameters():
+        ref = torch.from_numpy(z["grad/" + k])
+        if k.endswith(("emb.bias", "gcn.bias")):
+            assert float(p.grad.abs().max()) < 1e-5, k           # zero in exact arithmetic (BatchNorm removes the mean)
+        else:
+            worst[k] = rel_err(p.grad.cpu(), ref)
+    assert max(worst.values()) < 10 * TOL_GRAD, sorted(worst.items(), key=lambda kv: -kv[1])[:3]
+
+
 @pytest.mark.parametrize("B,N,L,dtype,density,weighted", [
     (3, 500, 6, torch.float16, 0.016, False), (2, 13, 6, torch.float32, 0.3, True), (1, 1030, 2, torch.float16, 0.05, True),
     (2, 64, 6, torch.float16, 0.2, False), (2, 96, 3, torch.float32, 0.0, False), (1, 37, 6, torch.float16, 1.0, False)])

@@ -190,3 +190,34 @@ def test_leaky_relu_epilogue_matches_torch(dev, M, K, C, p, dtype):
     assert rel(x.grad, xr.grad) < (5e-6 if dtype == torch.float32 else 2e-2)
     assert rel(w.grad, wr.grad) < (5e-6 if dtype == torch.float32 else 2e-2)
     assert bool((y.detach() < 0).any())                     # the negative branch is exercised
+
+
+@pytest.mark.parametrize("M,C,training", [(30, 32, True), (1000, 53, True), (4097, 256, True), (300, 64, False)])
+def test_batchnorm_leaky_matches_torch(dev, M, C, training):
+    """grl_bn_act_fwd / grl_bn_act_bwd (csrc/batchnorm.cu) against nn.BatchNorm1d + F.leaky_relu(0.2) in fp64:
+    output, dX, dgamma, dbeta, running statistics and num_batches_tracked; rows with a large common offset
+    (variance taken around the mean, no cancellation)."""
+    from graph_representation_learning_b200 import ops
+    gen = torch.Generator().manual_seed(M + C)
+    x0 = torch.randn(M, C, generator=gen) * (0.5 + torch.rand(C, generator=gen)) + 30.0 * torch.randn(C, generator=gen)
+    bn = torch.nn.BatchNorm1d(C)
+    with torch.no_grad():
+        bn.weight.copy_(0.5 + torch.rand(C, generator=gen)); bn.bias.copy_(torch.randn(C, generator=gen))
+        bn.running_mean.copy_(x0.mean(0) + 0.1 * torch.randn(C, generator=gen)); bn.running_var.copy_(0.5 + torch.rand(C, generator=gen))
+    ref = copy.deepcopy(bn).double()
+    bn = bn.to(dev)
+    bn.train(training); ref.train(training)
+    x = x0.to(dev).requires_grad_(True)
+    y = ops.batchnorm_act(x, bn, 0.2, training)
+    dy = torch.randn(M, C, generator=gen)
+    y.backward(dy.to(dev))
+    xr = x0.double().requires_grad_(True)
+    yr = torch.nn.functional.leaky_relu(ref(xr), 0.2)
+    yr.backward(dy.double())
+    rel = lambda a, b: float((a.detach().cpu().double() - b.detach()).norm() / b.detach().norm())
+    errs = {"y": rel(y, yr), "dx": rel(x.grad, xr.grad), "dgamma": rel(bn.weight.grad, ref.weight.grad),
+            "dbeta": rel(bn.bias.grad, ref.bias.grad), "running_mean": rel(bn.running_mean, ref.running_mean),
+            "running_var": rel(bn.running_var, ref.running_var)}
+    bars = {"y": 5e-6, "dx": 2e-5, "dgamma": 2e-5, "dbeta": 2e-5, "running_mean": 1e-6, "running_var": 1e-5}
+    assert all(errs[k] < bars[k] for k in bars), errs
+    assert int(bn.num_batches_tracked) == int(ref.num_batches_tracked)

@@ -10,6 +10,7 @@
 // * one CTA = one 128 x BLOCK_N output tile; warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner,
 //   warps 2..5 = epilogue: tcgen05.ld -> bias/ReLU/dropout -> global.  fp32 accumulators live in TMEM.
 #include "gemm_common.cuh"
+#include "gemm_x3_parts.cuh"
 
 namespace grl {
 using namespace sm100;
@@ -166,6 +167,179 @@ static int launch_gemm(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
     kern<<<tiles_m * tiles_n, kGemmThreads, Cfg::SMEM_BYTES, st>>>(p, tA0, tB0, tA1, tB1);
     GRL_LAUNCH_CHECK("gemm_nt_kernel");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Persistent bf16 NT kernel for wide outputs (N > 128): one CTA per SM walks 128 x 256 tiles (n fastest, so the CTAs of
+// one wave share their A tiles through L2), TWO 256-column accumulators in TMEM so the MMAs of tile t+1 run while eight
+// drain warps read tile t out (two warps per TMEM lane quarter, 64 columns per pass) and run the fused epilogue from
+// registers through private transposition buffers -- the operand ring never stops for an epilogue.  The one-tile-per-CTA
+// kernel above paid a prologue + a serial epilogue per tile: at K = 512 (GraphConv dX at S = 512) that was half the time.
+struct NtPCfg {
+    static constexpr int BLOCK_M = 128, BLOCK_N = 256, BLOCK_K = 64, UMMA_K = 16;
+    static constexpr int A_BYTES = BLOCK_M * 128, B_BYTES = BLOCK_N * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = 4;
+    static constexpr int DRAIN_WARPS = 8;
+    static constexpr int EPI_BYTES = DRAIN_WARPS * 32 * X3Cfg::EPI_PITCH * 4;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int THREADS = 64 + 32 * DRAIN_WARPS;
+};
+static_assert(NtPCfg::SMEM_BYTES <= 227 * 1024, "persistent bf16 NT kernel: shared memory budget");
+
+__global__ void __launch_bounds__(NtPCfg::THREADS, 1)
+gemm_nt_bf16_persistent_kernel(const GemmParams p, int n_tiles, int tiles_n, const __grid_constant__ CUtensorMap tmA0,
+                               const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmA1,
+                               const __grid_constant__ CUtensorMap tmB1) {
+    using Cfg = NtPCfg;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
+    float* epi_buf = reinterpret_cast<float*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
+    uint64_t* full_bar = bars;                     // [STAGES] TMA bytes landed
+    uint64_t* empty_bar = bars + STAGES;           // [STAGES] MMAs reading the stage retired
+    uint64_t* acc_full = bars + 2 * STAGES;        // [2] accumulator of a tile complete
+    uint64_t* acc_empty = acc_full + 2;            // [2] accumulator read out by all drain warps
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int total_kb = p.kblocks0 + p.kblocks1;
+    auto stage_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
+    auto stage_b = [&](int s) { return tiles + s * Cfg::STAGE_BYTES + Cfg::A_BYTES; };
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA0);
+        tma_prefetch_desc(&tmB0);
+        if (p.kblocks1) {
+            tma_prefetch_desc(&tmA1);
+            tma_prefetch_desc(&tmB1);
+        }
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 32 * Cfg::DRAIN_WARPS);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================================================================== TMA producer (one lane)
+        if (lane == 0) {
+            int it = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+                for (int kb = 0; kb < total_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+                    const bool seg1 = kb >= p.kblocks0;
+                    const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
+                    tma_load_2d(stage_a(s), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
+                    tma_load_2d(stage_b(s), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================================== MMA issuer (one lane)
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(1, Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 0);
+            int it = 0, ct = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++ct) {
+                const int buf = ct & 1;
+                mbar_wait(&acc_empty[buf], ((ct >> 1) & 1) ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d = tmem_base + buf * Cfg::BLOCK_N;
+                for (int kb = 0; kb < total_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                    tc_fence_after_sync();
+                    const uint64_t a_desc = umma_desc_kmajor_sw128(smem_u32(stage_a(s)));
+                    const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(stage_b(s)));
+#pragma unroll
+                    for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                        const uint64_t koff = static_cast<uint64_t>(k * 2);   // 32 bytes per UMMA_K step, >> 4
+                        umma<false>(d, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                    }
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        // ===================================================================== drain + epilogue (warps 2..9)
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + half * 128;
+        float* my_buf = epi_buf + (warp - 2) * 32 * X3Cfg::EPI_PITCH;
+        int ct = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++ct) {
+            const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+            const int buf = ct & 1;
+            mbar_wait(&acc_full[buf], (ct >> 1) & 1);
+            tc_fence_after_sync();
+#pragma unroll 1
+            for (int pass = 0; pass < 2; ++pass) {
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + buf * Cfg::BLOCK_N + pass * 64, r0);
+                tmem_ld_32x32(lane_base + buf * Cfg::BLOCK_N + pass * 64 + 32, r1);
+                tmem_ld_wait();
+                if (pass == 1) {
+                    tc_fence_before_sync();
+                    mbar_arrive(&acc_empty[buf]);               // the MMAs of tile t+2 may overwrite this accumulator
+                }
+                float acc[X3Cfg::DRAIN_COLS];
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[q] = __uint_as_float(r0[q]);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[32 + q] = __uint_as_float(r1[q]);
+                if (m0 + quarter * 32 < p.M)
+                    epilogue_from_regs(p, acc, my_buf, m0 + quarter * 32, n0 + half * 128 + pass * 64, lane);
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+static bool g_nt_bf16_persistent = true;      // grl_gemm_nt_bf16_set_persistent(0): the one-tile-per-CTA kernel (A/B runs)
+
+static int launch_gemm_bf16_persistent(const GemmArgs& a, GemmParams p, cudaStream_t st) {
+    using Cfg = NtPCfg;
+    CUtensorMap tA0, tB0, tA1, tB1;
+    int rc;
+    if ((rc = make_tmap_sw128(&tA0, a.A0, 2, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;
+    if ((rc = make_tmap_sw128(&tB0, a.B0, 2, p.N, a.K0, a.ldb0, Cfg::BLOCK_N))) return rc;
+    tA1 = tA0;
+    tB1 = tB0;
+    if (a.K1 > 0) {
+        if ((rc = make_tmap_sw128(&tA1, a.A1, 2, p.M, a.K1, a.lda1, Cfg::BLOCK_M))) return rc;
+        if ((rc = make_tmap_sw128(&tB1, a.B1, 2, p.N, a.K1, a.ldb1, Cfg::BLOCK_N))) return rc;
+    }
+    p.kblocks0 = (a.K0 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K;
+    p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_nt_bf16_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+        attr_set = true;
+    }
+    const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int n_tiles = tiles_m * tiles_n;
+    const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;
+    gemm_nt_bf16_persistent_kernel<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, n_tiles, tiles_n, tA0, tB0, tA1, tB1);
+    GRL_LAUNCH_CHECK("gemm_nt_bf16_persistent_kernel");
     return 0;
 }
 
@@ -350,11 +524,16 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool wide = N > 128;
     switch (mode) {
-        case kBF16: return wide ? launch_gemm<kBF16, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kBF16, 128>(ga, gp, st) : launch_gemm<kBF16, 64>(ga, gp, st));
+        case kBF16: return wide ? (g_nt_bf16_persistent ? launch_gemm_bf16_persistent(ga, gp, st) : launch_gemm<kBF16, 256>(ga, gp, st)) : (N > 64 ? launch_gemm<kBF16, 128>(ga, gp, st) : launch_gemm<kBF16, 64>(ga, gp, st));
         case kTF32: return wide ? launch_gemm<kTF32, 256>(ga, gp, st) : (N > 64 ? launch_gemm<kTF32, 128>(ga, gp, st) : launch_gemm<kTF32, 64>(ga, gp, st));
         case kTF32BC: return launch_gemm_bc(ga, gp, st, false, 0);
         default:    return launch_gemm_x3(ga, gp, st);
     }
+}
+
+extern "C" int grl_gemm_nt_bf16_set_persistent(int on) {
+    g_nt_bf16_persistent = on != 0;
+    return 0;
 }
 
 namespace grl {

@@ -209,6 +209,9 @@ int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo,
 /* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
  * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2. */
 int grl_gemm_x3_set_promo(int promo);
+/* bf16 NT products with N > 128 run on the persistent kernel (double-buffered TMEM accumulators, epilogue overlapped
+ * with the next tile); 0 selects the one-tile-per-CTA kernel instead (A/B measurements; results are identical). */
+int grl_gemm_nt_bf16_set_persistent(int on);
 int grl_gemm_bc_set_promo(int promo);   /* the same knob of the GRL_GEMM_TF32_BF16C kernels; default 4 */
 /* Weight-gradient GEMM ("TN", reduction over the node dimension R, both operands MN-major fp32 activations):
  *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]        fp32-grade TF32X3 on tcgen05, split-K over R, deterministic reduce.

@@ -321,6 +321,32 @@ def run_b200(args):
                        "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"], "ms_per_launch": ms_bwd,
                        "algorithmic_bytes": alg_bwd, "traffic": traffic_bwd}
     del X, Y, dYt, dX
+    # GEMMs are the larger share of the step (about 60 %): the gcn3 projection forward [Nt x S, K = 7 * 2S] and its dX,
+    # timed alone.  Tensor-bound figure = EXECUTED tensor flops (fp32: three tf32 products forward, tf32 + double-K bf16
+    # backward = 2 tf32-product equivalents; bf16: one product) against the dense peak of that operand type
+    # (tf32 = half the measured bf16 figure).  "useful" = 2*M*N*K of the fp32-grade product.
+    Kg = 14 * S
+    Xg = torch.randn(B * wl.N, Kg, device=dev, dtype=wl.dtype)
+    Wg = torch.randn(S, Kg, device=dev) / Kg ** 0.5
+    dZg = torch.randn(B * wl.N, S, device=dev, dtype=wl.dtype)
+    ms_gf, _, _ = timed(lambda: ops.gemm_nt([Xg], [Wg]), 10, 3)
+    ms_gb, _, _ = timed(lambda: ops.gemm_nt([dZg], [Wg.t()], fp32_mode=ops.GemmConfig.fp32_mode_bwd), 10, 3)
+    useful = 2.0 * B * wl.N * S * Kg
+    fp32 = wl.dtype == torch.float32
+    peak_tf = pk["bf16_tflops_sustained"] / 2 if fp32 else pk["bf16_tflops_sustained"]
+    prod_f, prod_b = (3.0, 2.0) if fp32 else (1.0, 1.0)
+    roofline["gemm"] = {
+        "bound": "tensor", "unit": "TFLOP/s", "peak": peak_tf,
+        "peak_how": "measured sustained cuBLAS bf16" + (" / 2 (tf32 operands)" if fp32 else ""),
+        "fwd": {"kernel": "gemm_x3_kernel (gcn3 projection, three tf32 products)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 projection)",
+                "shape_mnk": [B * wl.N, S, Kg], "ms_per_launch": ms_gf, "useful": useful / ms_gf / 1e9,
+                "achieved": prod_f * useful / ms_gf / 1e9, "frac": prod_f * useful / ms_gf / 1e9 / peak_tf},
+        "bwd_dx": {"kernel": "gemm_bc_kernel<NT> (gcn3 dX, tf32 + bf16 correction product)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 dX)",
+                   "shape_mnk": [B * wl.N, Kg, S], "ms_per_launch": ms_gb, "useful": useful / ms_gb / 1e9,
+                   "achieved": prod_b * useful / ms_gb / 1e9, "frac": prod_b * useful / ms_gb / 1e9 / peak_tf},
+        "note": "all GEMMs of the step run under the board power cap (sw_power_cap, ~1000 W) and are L2->SM bound "
+                "(DESIGN.md 4.2); the fractions are against an un-capped cuBLAS figure"}
+    del Xg, Wg, dZg
 
     # (4) CPU baseline: the oracle port on a bounded sample of the same workload (rank 0, N=1 only)
     cpu = None

@@ -49,13 +49,18 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float first, float second) {   /
 
 // kX3 (NT only): the three-tf32-product arithmetic of gemm_x3_tcgen05.cu (a_hi = a truncated to tf32, corrections
 // a_lo*b_hi + a_hi*b_lo in tf32 against the fp32 low parts of grl_split_tf32) on this kernel's TMEM operand path.
-template <bool kTN, bool kX3>
+// kMC (NT only): launched as thread-block clusters of 2 CTAs that work on two adjacent row tiles of the SAME column tile;
+// each CTA fetches half of every weight tile (64 of the 128 rows of B_hi and of the packed B) and TMA-multicasts it into
+// both CTAs, so a K-block costs 32 KB of L2 -> SM traffic per CTA instead of 48 KB.  A stage is reusable when BOTH
+// MMA issuers have retired it: empty barriers count 2 and every commit is multicast to the pair.
+template <bool kTN, bool kX3, bool kMC = false>
 __global__ void __launch_bounds__(BcCfg::THREADS, 1)
 gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, const int n_tiles, const int transpose_out,
                const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmB0,
                const __grid_constant__ CUtensorMap tmBp0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB1, const __grid_constant__ CUtensorMap tmBp1) {
     static_assert(!(kTN && kX3), "the three-product arithmetic on the TMEM path exists for NT only");
+    static_assert(!(kMC && (kTN || kX3)), "weight-tile multicast is built for the NT second-generation product");
     using Cfg = BcCfg;
     constexpr int STAGES = Cfg::STAGES, TA = Cfg::TA_STAGES, DRAIN_WARPS = X3Cfg::DRAIN_WARPS;
     extern __shared__ uint8_t smem_raw[];
@@ -79,6 +84,11 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
     const int kb_end = kTN ? min(all_kb, kb_begin + kb_per_split) : all_kb;
     const int total_kb = max(kb_end - kb_begin, 0);
     const int n_chunks = (total_kb + promo - 1) / promo;
+    // tile walk: one tile per step, or (kMC) one PAIR of row tiles per step, this CTA taking row tile 2*pair + rank
+    const int cta_rank = kMC ? static_cast<int>(cluster_ctarank()) : 0;
+    const int t_first = kMC ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+    const int t_step = kMC ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+    auto tile_m0 = [&](int t) { return (kMC ? 2 * (t / tiles_n) + cta_rank : t / tiles_n) * Cfg::BLOCK_M; };
 
     auto tile = [&](int s, int which) { return tiles + s * Cfg::STAGE_BYTES + which * Cfg::TILE_BYTES; };
     enum { T_A = 0, T_B = 1, T_BP = 2 };
@@ -94,7 +104,7 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         }
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], kMC ? 2 : 1);
         }
         for (int j = 0; j < TA; ++j) {
             mbar_init(&split_bar[j], 128);
@@ -109,7 +119,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
     }
     if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
     tc_fence_before_sync();
-    __syncthreads();
+    if constexpr (kMC) cluster_sync_all();      // the peer's barriers are initialised before anything is multicast
+    else __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -117,8 +128,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         // ===================================================================== TMA producer (one lane)
         if (lane == 0) {
             int it = 0;
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+            for (int t = t_first; t < n_tiles; t += t_step) {
+                const int m0 = tile_m0(t), n0 = (t % tiles_n) * Cfg::BLOCK_N;
                 for (int kk = 0; kk < total_kb; ++kk, ++it) {
                     const int kb = kb_begin + kk;
                     const int s = it % STAGES;
@@ -139,8 +150,15 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                         const bool seg1 = kb >= p.kblocks0;
                         const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
                         tma_load_2d(tile(s, T_A), seg1 ? &tmA1 : &tmA0, &full_bar[s], k_elem, m0);
-                        tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
-                        tma_load_2d(tile(s, T_BP), seg1 ? &tmBp1 : &tmBp0, &full_bar[s], kX3 ? k_elem : 2 * k_elem, n0);
+                        if constexpr (kMC) {
+                            // my half (64 rows = 8 KB) of both weight tiles, into both CTAs of the pair
+                            const int nh = n0 + cta_rank * 64, off = cta_rank * 8192;
+                            tma_load_2d_multicast(tile(s, T_B) + off, seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, nh, 3);
+                            tma_load_2d_multicast(tile(s, T_BP) + off, seg1 ? &tmBp1 : &tmBp0, &full_bar[s], 2 * k_elem, nh, 3);
+                        } else {
+                            tma_load_2d(tile(s, T_B), seg1 ? &tmB1 : &tmB0, &full_bar[s], k_elem, n0);
+                            tma_load_2d(tile(s, T_BP), seg1 ? &tmBp1 : &tmBp0, &full_bar[s], kX3 ? k_elem : 2 * k_elem, n0);
+                        }
                     }
                 }
             }
@@ -152,7 +170,7 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
             constexpr uint32_t idesc_c = umma_idesc(1, Cfg::BLOCK_M, Cfg::BLOCK_N, 0, kTN ? 1 : 0);   // bf16
             const uint32_t d_small = tmem_base + 256;
             int it = 0, cg = 0, tl = 0;
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+            for (int t = t_first; t < n_tiles; t += t_step, ++tl) {
                 mbar_wait(small_empty, (tl & 1) ^ 1);
                 tc_fence_after_sync();
                 int kk = 0;
@@ -189,7 +207,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                                 umma_ts<false>(d_small, ta_pk + 8 * k, bp_desc + koff_c, idesc_c, (kk | k) != 0);
                             }
                         }
-                        umma_commit(&empty_bar[s]);
+                        if constexpr (kMC) umma_commit_multicast(&empty_bar[s], 3);
+                        else umma_commit(&empty_bar[s]);
                         umma_commit(&ta_empty[j]);
                     }
                     umma_commit(&acc_full[buf]);
@@ -202,7 +221,7 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         const int quarter = warp & 3, row = quarter * 32 + lane;
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + Cfg::TA_COL0;
         int it = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int t = t_first; t < n_tiles; t += t_step) {
             for (int kk = 0; kk < total_kb; ++kk, ++it) {
                 const int s = it % STAGES, j = it % TA;
                 mbar_wait(&full_bar[s], (it / STAGES) & 1);
@@ -264,8 +283,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + colbase;
         float* my_buf = epi_buf + (warp - 6) * 32 * X3Cfg::EPI_PITCH;
         int cg = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-            const int m0 = (t / tiles_n) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+        for (int t = t_first; t < n_tiles; t += t_step) {
+            const int m0 = tile_m0(t), n0 = (t % tiles_n) * Cfg::BLOCK_N;
             float acc[X3Cfg::DRAIN_COLS];
 #pragma unroll
             for (int q = 0; q < X3Cfg::DRAIN_COLS; ++q) acc[q] = 0.0f;
@@ -322,7 +341,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
         }
     }
     tc_fence_before_sync();
-    __syncthreads();
+    if constexpr (kMC) cluster_sync_all();      // the peer may still multicast into / arrive on this CTA's shared memory
+    else __syncthreads();
     if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
@@ -331,11 +351,13 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
 // pipe (0.59 ms for [128000x1792]x[1792x256]) and promo = 4 does not (0.50 ms) at 7.4e-7 instead of 6.9e-7.
 static int g_bc_promo = 4;
 
-template <bool kTN, bool kX3>
+static bool g_bc_multicast = false;     // grl_gemm_bc_set_multicast(1): CTA pairs sharing weight tiles; measured EQUAL
+
+template <bool kTN, bool kX3, bool kMC = false>
 static int ensure_bc_smem_attr() {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_bc_kernel<kTN, kX3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(gemm_bc_kernel<kTN, kX3, kMC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              BcCfg::SMEM_BYTES);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
         attr_set = true;
@@ -367,6 +389,43 @@ int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, in
     if ((rc = x3 ? ensure_bc_smem_attr<false, true>() : ensure_bc_smem_attr<false, false>())) return rc;
     const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
     const int n_tiles = tiles_m * tiles_n;
+    const int n_pairs = (tiles_m + 1) / 2 * tiles_n;
+    if (!x3 && g_bc_multicast && n_pairs >= kNumSMs / 2) {
+        // clusters of 2 CTAs on adjacent row tiles sharing their weight tiles by TMA multicast (64-row weight boxes)
+        auto half_map = [&](CUtensorMap* hi, CUtensorMap* pk, const void* b, const void* blo, int K, int64_t ldb) {
+            int r = make_tmap_sw128(hi, b, 4, p.N, K, ldb, Cfg::BLOCK_N / 2);
+            return r ? r : make_tmap_sw128(pk, blo, 2, p.N, 2 * ((K + 3) / 4 * 4), 2 * ldb, Cfg::BLOCK_N / 2);
+        };
+        if ((rc = half_map(&tB0, &tBp0, a.B0, a.B0lo, a.K0, a.ldb0))) return rc;
+        tB1 = tB0; tBp1 = tBp0;
+        if (a.K1 > 0 && (rc = half_map(&tB1, &tBp1, a.B1, a.B1lo, a.K1, a.ldb1))) return rc;
+        if ((rc = ensure_bc_smem_attr<false, false, true>())) return rc;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(kNumSMs);
+        cfg.blockDim = dim3(Cfg::THREADS);
+        cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        // persistent grid = the clusters that are co-resident (GPCs with an odd SM count leave an SM without a partner)
+        static int max_clusters = 0;
+        if (max_clusters == 0) {
+            int n = 0;
+            cudaError_t eo = cudaOccupancyMaxActiveClusters(&n, gemm_bc_kernel<false, false, true>, &cfg);
+            if (eo != cudaSuccess) return cuda_fail(eo, "cudaOccupancyMaxActiveClusters(gemm_bc_kernel<NT, multicast>)");
+            max_clusters = n < 1 ? 1 : (n > kNumSMs / 2 ? kNumSMs / 2 : n);
+        }
+        cfg.gridDim = dim3(2 * (n_pairs < max_clusters ? n_pairs : max_clusters));
+        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bc_kernel<false, false, true>, p, g_bc_promo, 0, n_pairs, 0, tA0, tB0,
+                                           tBp0, tA1, tB1, tBp1);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_bc_kernel<NT, multicast>)");
+        return 0;
+    }
     const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;
     if (x3)
         gemm_bc_kernel<false, true><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p, promo_x3, 0, n_tiles, 0, tA0, tB0, tBp0,
@@ -523,6 +582,11 @@ __global__ void __launch_bounds__(1024) colsum_partials_kernel(const float* __re
 }  // namespace grl
 
 using namespace grl;
+
+extern "C" int grl_gemm_bc_set_multicast(int on) {
+    g_bc_multicast = on != 0;
+    return 0;
+}
 
 extern "C" int grl_gemm_bc_set_promo(int promo) {
     if (promo < 1 || promo > 1 << 20) {

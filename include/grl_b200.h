@@ -212,6 +212,10 @@ int grl_gemm_x3_set_promo(int promo);
 /* bf16 NT products with N > 128 run on the persistent kernel (double-buffered TMEM accumulators, epilogue overlapped
  * with the next tile); 0 selects the one-tile-per-CTA kernel instead (A/B measurements; results are identical). */
 int grl_gemm_nt_bf16_set_persistent(int on);
+/* 1: GRL_GEMM_TF32_BF16C NT products run as thread-block clusters of 2 CTAs that share their weight tiles through TMA
+ * multicast (32 KB instead of 48 KB of L2 -> SM traffic per K-block and CTA).  Identical results and, measured, identical
+ * time (the kernel is not bound by L2 reads of the weights), so the default is 0 = single-CTA loads. */
+int grl_gemm_bc_set_multicast(int on);
 int grl_gemm_bc_set_promo(int promo);   /* the same knob of the GRL_GEMM_TF32_BF16C kernels; default 4 */
 /* Weight-gradient GEMM ("TN", reduction over the node dimension R, both operands MN-major fp32 activations):
  *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]        fp32-grade TF32X3 on tcgen05, split-K over R, deterministic reduce.

@@ -165,3 +165,28 @@ def test_gemm_tn_bf16_weight_gradient(R, Ma, Nb):
     assert out.shape == (Ma, Nb) and out.dtype == torch.float32
     assert rel_err(out.cpu(), ref) < 1e-5
     assert torch.equal(out, ops.gemm_tn(a.to(dev), b.to(dev)))
+
+
+@pytest.mark.parametrize("M,N,K", [(19000, 300, 100), (19100, 128, 64), (40000, 53, 1280)])
+def test_tf32bc_weight_multicast_clusters_identical(M, N, K):
+    """grl_gemm_bc_set_multicast(1): CTA pairs (thread-block clusters) that share their weight tiles through TMA
+    multicast -- odd row-tile counts (the last pair has one tile past M), N tails past the second weight half, short K --
+    must reproduce the single-CTA kernel bit for bit."""
+    from graph_representation_learning_b200 import _lib, ops
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=gen).to(dev)
+    b = (torch.randn(N, K, generator=gen) / K ** 0.5).to(dev)
+    bias = torch.randn(N, generator=gen).to(dev)
+    outs = []
+    try:
+        for on in (0, 1):
+            lib.grl_gemm_bc_set_multicast(on)
+            outs.append(ops.gemm_nt([a], [b], bias=bias, relu=True, fp32_mode="tf32bc"))
+            torch.cuda.synchronize()
+    finally:
+        lib.grl_gemm_bc_set_multicast(0)
+    assert torch.equal(outs[0], outs[1])
+    ref = torch.relu(a.double() @ b.double().t() + bias.double())
+    assert float((outs[1].double() - ref).norm() / ref.norm()) < 2e-6

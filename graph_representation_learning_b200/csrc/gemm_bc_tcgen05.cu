@@ -77,7 +77,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
     uint64_t* small_empty = acc_full + 4;               // correction accumulator of the previous tile read out
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 5);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // provably warp-uniform
+    const int lane = threadIdx.x & 31;
     const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
     const int all_kb = p.kblocks0 + p.kblocks1;
     const int kb_begin = kTN ? static_cast<int>(blockIdx.y) * kb_per_split : 0;
@@ -164,8 +165,8 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
             }
         }
     } else if (warp == 1) {
-        // ===================================================================== MMA issuer (one lane)
-        if (lane == 0) {
+        // ===================================================================== MMA issuer (warp-wide loop, one elected lane issues)
+        {
             constexpr uint32_t idesc = umma_idesc(2, Cfg::BLOCK_M, Cfg::BLOCK_N, 0, kTN ? 1 : 0);     // tf32, A K-major (TMEM)
             constexpr uint32_t idesc_c = umma_idesc(1, Cfg::BLOCK_M, Cfg::BLOCK_N, 0, kTN ? 1 : 0);   // bf16
             const uint32_t d_small = tmem_base + 256;
@@ -193,25 +194,29 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                             b_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_B)));
                             bp_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_BP)));
                         }
+                        if (elect_one_sync()) {
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            // 8 tf32 / 16 packed bf16 per step = 8 TMEM columns of A; B: 32 bytes of a K-major row, or
-                            // 8 rows (tf32, 1024 B) / 16 rows (bf16, 2048 B) of an MN-major tile
-                            const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
-                            const uint64_t koff_c = static_cast<uint64_t>(kTN ? k * 128 : k * 2);
-                            umma_ts<true>(d_main, ta_hi + 8 * k, b_desc + koff, idesc, (i | k) != 0);
-                            if constexpr (kX3) {
-                                umma_ts<true>(d_small, ta_pk + 8 * k, b_desc + koff, idesc, (kk | k) != 0);    // a_lo * b_hi
-                                umma_ts<true>(d_small, ta_hi + 8 * k, bp_desc + koff, idesc, 1u);              // a_hi * b_lo
-                            } else {
-                                umma_ts<false>(d_small, ta_pk + 8 * k, bp_desc + koff_c, idesc_c, (kk | k) != 0);
+                            for (int k = 0; k < 4; ++k) {
+                                // 8 tf32 / 16 packed bf16 per step = 8 TMEM columns of A; B: 32 bytes of a K-major row, or
+                                // 8 rows (tf32, 1024 B) / 16 rows (bf16, 2048 B) of an MN-major tile
+                                const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
+                                const uint64_t koff_c = static_cast<uint64_t>(kTN ? k * 128 : k * 2);
+                                umma_ts<true>(d_main, ta_hi + 8 * k, b_desc + koff, idesc, (i | k) != 0);
+                                if constexpr (kX3) {
+                                    umma_ts<true>(d_small, ta_pk + 8 * k, b_desc + koff, idesc, (kk | k) != 0);    // a_lo * b_hi
+                                    umma_ts<true>(d_small, ta_hi + 8 * k, bp_desc + koff, idesc, 1u);              // a_hi * b_lo
+                                } else {
+                                    umma_ts<false>(d_small, ta_pk + 8 * k, bp_desc + koff_c, idesc_c, (kk | k) != 0);
+                                }
                             }
+                            if constexpr (kMC) umma_commit_multicast(&empty_bar[s], 3);
+                            else umma_commit(&empty_bar[s]);
+                            umma_commit(&ta_empty[j]);
                         }
-                        if constexpr (kMC) umma_commit_multicast(&empty_bar[s], 3);
-                        else umma_commit(&empty_bar[s]);
-                        umma_commit(&ta_empty[j]);
+                        __syncwarp();
                     }
-                    umma_commit(&acc_full[buf]);
+                    if (elect_one_sync()) umma_commit(&acc_full[buf]);
+                    __syncwarp();
                 }
             }
         }

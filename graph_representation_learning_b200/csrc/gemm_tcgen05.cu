@@ -51,7 +51,8 @@ gemm_nt_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA0, con
     uint64_t* accum_bar = bars + 2 * STAGES;   // accumulator complete
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // provably warp-uniform
+    const int lane = threadIdx.x & 31;
     const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
     const int m0 = (blockIdx.x / tiles_n) * Cfg::BLOCK_M;
     const int n0 = (blockIdx.x % tiles_n) * BLOCK_N;
@@ -95,8 +96,8 @@ gemm_nt_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA0, con
             }
         }
     } else if (warp == 1) {
-        // ===================================================================== MMA issuer (one lane)
-        if (lane == 0) {
+        // ===================================================================== MMA issuer (warp-wide loop, one elected lane issues)
+        {
             constexpr uint32_t idesc = umma_idesc(kMode == kBF16 ? 1 : 2, Cfg::BLOCK_M, BLOCK_N, 0, 0);
             for (int kb = 0; kb < total_kb; ++kb) {
                 const int s = kb % STAGES;
@@ -105,14 +106,18 @@ gemm_nt_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA0, con
                 tc_fence_after_sync();
                 const uint64_t a_desc = umma_desc_kmajor_sw128(smem_u32(stage_a(s)));
                 const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(stage_b(s)));
+                if (elect_one_sync()) {
 #pragma unroll
-                for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
-                    const uint64_t koff = static_cast<uint64_t>(k * 2);   // 32 bytes per UMMA_K step, >> 4
-                    umma<kMode != kBF16>(tmem_base, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                    for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                        const uint64_t koff = static_cast<uint64_t>(k * 2);   // 32 bytes per UMMA_K step, >> 4
+                        umma<kMode != kBF16>(tmem_base, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                    }
+                    umma_commit(&empty_bar[s]);       // frees the stage once these MMAs have read it
                 }
-                umma_commit(&empty_bar[s]);       // frees the stage once these MMAs have read it
+                __syncwarp();
             }
-            umma_commit(accum_bar);               // accumulator final
+            if (elect_one_sync()) umma_commit(accum_bar);               // accumulator final
+            __syncwarp();
         }
     } else {
         // ===================================================================== epilogue (warps 2..5)
@@ -205,7 +210,8 @@ gemm_nt_bf16_persistent_kernel(const GemmParams p, int n_tiles, int tiles_n, con
     uint64_t* acc_empty = acc_full + 2;            // [2] accumulator read out by all drain warps
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // provably warp-uniform
+    const int lane = threadIdx.x & 31;
     const int total_kb = p.kblocks0 + p.kblocks1;
     auto stage_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
     auto stage_b = [&](int s) { return tiles + s * Cfg::STAGE_BYTES + Cfg::A_BYTES; };
@@ -251,8 +257,8 @@ gemm_nt_bf16_persistent_kernel(const GemmParams p, int n_tiles, int tiles_n, con
             }
         }
     } else if (warp == 1) {
-        // ===================================================================== MMA issuer (one lane)
-        if (lane == 0) {
+        // ===================================================================== MMA issuer (warp-wide loop, one elected lane issues)
+        {
             constexpr uint32_t idesc = umma_idesc(1, Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 0);
             int it = 0, ct = 0;
             for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++ct) {
@@ -266,14 +272,18 @@ gemm_nt_bf16_persistent_kernel(const GemmParams p, int n_tiles, int tiles_n, con
                     tc_fence_after_sync();
                     const uint64_t a_desc = umma_desc_kmajor_sw128(smem_u32(stage_a(s)));
                     const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(stage_b(s)));
+                    if (elect_one_sync()) {
 #pragma unroll
-                    for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
-                        const uint64_t koff = static_cast<uint64_t>(k * 2);   // 32 bytes per UMMA_K step, >> 4
-                        umma<false>(d, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                        for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                            const uint64_t koff = static_cast<uint64_t>(k * 2);   // 32 bytes per UMMA_K step, >> 4
+                            umma<false>(d, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                        }
+                        umma_commit(&empty_bar[s]);
                     }
-                    umma_commit(&empty_bar[s]);
+                    __syncwarp();
                 }
-                umma_commit(&acc_full[buf]);
+                if (elect_one_sync()) umma_commit(&acc_full[buf]);
+                __syncwarp();
             }
         }
     } else {
@@ -370,7 +380,8 @@ gemm_tn_bf16_kernel(const GemmParams p, const int kb_per_split, const __grid_con
     uint64_t* accum_bar = bars + 2 * STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // provably warp-uniform
+    const int lane = threadIdx.x & 31;
     const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
     const int m0 = (blockIdx.x / tiles_n) * Cfg::BLOCK_M;
     const int n0 = (blockIdx.x % tiles_n) * Cfg::BLOCK_N;
@@ -411,7 +422,7 @@ gemm_tn_bf16_kernel(const GemmParams p, const int kb_per_split, const __grid_con
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // warp-wide loop, one elected lane issues (elect_one_sync in tcgen05.cuh)
             constexpr uint32_t idesc = umma_idesc(1, Cfg::BLOCK_M, Cfg::BLOCK_N, 1, 1);
             for (int kk = 0; kk < total_kb; ++kk) {
                 const int s = kk % STAGES;
@@ -419,14 +430,18 @@ gemm_tn_bf16_kernel(const GemmParams p, const int kb_per_split, const __grid_con
                 tc_fence_after_sync();
                 const uint64_t a_desc = umma_desc_mnmajor_sw128(smem_u32(stage_a(s)), 8192, 1024, 2);
                 const uint64_t b_desc = umma_desc_mnmajor_sw128(smem_u32(stage_b(s)), 8192, 1024, 2);
+                if (elect_one_sync()) {
 #pragma unroll
-                for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
-                    const uint64_t koff = static_cast<uint64_t>(k * 128);       // 16 reduction rows = 2048 B, >> 4
-                    umma<false>(tmem_base, a_desc + koff, b_desc + koff, idesc, (kk | k) != 0);
+                    for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                        const uint64_t koff = static_cast<uint64_t>(k * 128);       // 16 reduction rows = 2048 B, >> 4
+                        umma<false>(tmem_base, a_desc + koff, b_desc + koff, idesc, (kk | k) != 0);
+                    }
+                    umma_commit(&empty_bar[s]);
                 }
-                umma_commit(&empty_bar[s]);
+                __syncwarp();
             }
-            umma_commit(accum_bar);
+            if (elect_one_sync()) umma_commit(accum_bar);
+            __syncwarp();
         }
     } else {
         mbar_wait(accum_bar, 0);

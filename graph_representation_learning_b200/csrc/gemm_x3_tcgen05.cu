@@ -72,7 +72,8 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
     uint64_t* small_empty = bars + 3 * STAGES + 4; // [2] correction accumulator (one per tile parity) read out
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 6);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);   // provably warp-uniform
+    const int lane = threadIdx.x & 31;
     const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
     // K-block range of this CTA: everything for NT; one slice of the reduction for TN (split-K over blockIdx.y)
     const int all_kb = p.kblocks0 + p.kblocks1;
@@ -144,8 +145,9 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
             }
         }
     } else if (warp == 1) {
-        // ===================================================================== MMA issuer (one lane)
-        if (lane == 0) {
+        // ===================================================================== MMA issuer (warp-wide loop, one elected lane issues:
+        // see elect_one_sync in tcgen05.cuh)
+        {
             constexpr uint32_t idesc = umma_idesc(2, Cfg::BLOCK_M, Cfg::BLOCK_N, kTN ? 1 : 0, kTN ? 1 : 0);
             // two correction accumulators (TMEM columns 256.. and 384..), alternating per tile: the MMAs of tile i+1 start
             // while the drain warps still read tile i's corrections (short-K products spent a third of every tile there)
@@ -180,17 +182,21 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                             alo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_ALO)));
                             blo_desc = umma_desc_kmajor_sw128(smem_u32(tile(s, T_BLO)));
                         }
+                        if (elect_one_sync()) {
 #pragma unroll
-                        for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
-                            // one UMMA_K step: 32 bytes along a K-major row, or 8 rows (1024 B) of an MN-major tile
-                            const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
-                            umma<true>(d_main, a_desc + koff, b_desc + koff, idesc, (i | k) != 0);
-                            umma<true>(d_small, alo_desc + koff, b_desc + koff, idesc, (kk | k) != 0);
-                            umma<true>(d_small, a_desc + koff, blo_desc + koff, idesc, 1u);
+                            for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                                // one UMMA_K step: 32 bytes along a K-major row, or 8 rows (1024 B) of an MN-major tile
+                                const uint64_t koff = static_cast<uint64_t>(kTN ? k * 64 : k * 2);
+                                umma<true>(d_main, a_desc + koff, b_desc + koff, idesc, (i | k) != 0);
+                                umma<true>(d_small, alo_desc + koff, b_desc + koff, idesc, (kk | k) != 0);
+                                umma<true>(d_small, a_desc + koff, blo_desc + koff, idesc, 1u);
+                            }
+                            umma_commit(&empty_bar[s]);
                         }
-                        umma_commit(&empty_bar[s]);
+                        __syncwarp();
                     }
-                    umma_commit(&acc_full[buf]);
+                    if (elect_one_sync()) umma_commit(&acc_full[buf]);
+                    __syncwarp();
                 }
             }
         }

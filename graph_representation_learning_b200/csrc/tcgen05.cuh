@@ -77,6 +77,15 @@ __device__ __forceinline__ void tma_load_2d_multicast(void* smem_dst, const CUte
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
         : "memory");
 }
+// One lane of a fully active warp (elect.sync).  The MMA-issuing warp runs its loop warp-wide -- barrier waits, stage and
+// descriptor arithmetic stay warp-uniform, so the compiler keeps them in uniform registers -- and only the tcgen05.mma /
+// tcgen05.commit instructions sit under this predicate.  (A loop entered by `if (lane == 0)` makes every operand a
+// per-thread value: ptxas then emits ELECT + R2UR.BROADCAST chains in front of every UTCHMMA, ~130 cycles per MMA.)
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));

@@ -273,8 +273,9 @@ gemm_x3_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
 
 static int g_x3_promo = 2;
 static int g_x3_persistent = 1;   // 0: one CTA per tile (A/B experiments via grl_gemm_x3_set_promo(-1 / -2))
-static int g_x3_tmem_operand = 0; // 1: NT products run on the TMEM-operand kernel of gemm_bc_tcgen05.cu (-3); 0: here (-4, default:
-                                  // measured equal, scripts/gemm_x3_ab.py -- twelve tf32 MMAs per K-block dominate either way)
+static int g_x3_tmem_operand = 1; // 1 (-3, default): NT products run on the TMEM-operand kernel of gemm_bc_tcgen05.cu, same
+                                  // arithmetic, half the shared-memory traffic: 5-9 % faster once the MMA issue loop stopped
+                                  // being the bound (scripts/gemm_x3_ab.py); 0 (-4): the shared-memory-operand kernel here
 
 template <bool kTN>
 static int ensure_smem_attr() {
@@ -335,7 +336,7 @@ extern "C" int grl_gemm_x3_set_promo(int promo) {
         g_x3_persistent = promo == -2;
         return 0;
     }
-    if (promo == -3 || promo == -4) {             // -3 = activation operand through TMEM, -4 = shared memory (default)
+    if (promo == -3 || promo == -4) {             // -3 = activation operand through TMEM (default), -4 = shared memory
         g_x3_tmem_operand = promo == -3;
         return 0;
     }

@@ -25,5 +25,5 @@ for (N, K) in ((256, 4368), (256, 1792), (256, 3584), (1280, 128), (128, 512), (
             t = timeit(lambda: ops.gemm_nt([a], [b]))
             err = float((ops.gemm_nt([a[:2048]], [b]).double() - ref).norm() / ref.norm())
             print(f"N={N} K={K} x3-{name} promo={promo}: {t:.4f} ms {2.0*M*N*K/t/1e9:.0f} TF/s useful  err {err:.2e}")
-    lib.grl_gemm_x3_set_promo(2); lib.grl_gemm_x3_set_promo(-4)
+    lib.grl_gemm_x3_set_promo(2); lib.grl_gemm_x3_set_promo(-3)
     del a, b

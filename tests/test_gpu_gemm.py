@@ -190,3 +190,29 @@ def test_tf32bc_weight_multicast_clusters_identical(M, N, K):
     assert torch.equal(outs[0], outs[1])
     ref = torch.relu(a.double() @ b.double().t() + bias.double())
     assert float((outs[1].double() - ref).norm() / ref.norm()) < 2e-6
+
+
+@pytest.mark.parametrize("M,N,K,two", [(1000, 256, 512, False), (777, 53, 100, False), (4096, 300, 37, False),
+                                       (2000, 128, 256, True)])
+def test_tf32x3_tmem_and_smem_operand_kernels_identical(M, N, K, two):
+    """The three-product arithmetic runs by default on the TMEM-operand kernel (gemm_bc_kernel<NT, x3>); the
+    shared-memory-operand kernel (grl_gemm_x3_set_promo(-4)) must give the same bits: same split, same products, same
+    accumulation order.  One and two K segments, N and K tails, fused bias + ReLU."""
+    from graph_representation_learning_b200 import _lib, ops
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(M + N + K)
+    a = [torch.randn(M, K, generator=gen).to(dev)] + ([torch.rand(M, 96, generator=gen).to(dev)] if two else [])
+    b = [(torch.randn(N, x.shape[1], generator=gen) / K ** 0.5).to(dev) for x in a]
+    bias = torch.randn(N, generator=gen).to(dev)
+    outs = []
+    try:
+        for sw in (-4, -3):
+            lib.grl_gemm_x3_set_promo(sw)
+            outs.append(ops.gemm_nt(a, b, bias=bias, relu=True, fp32_mode="tf32x3"))
+            torch.cuda.synchronize()
+    finally:
+        lib.grl_gemm_x3_set_promo(-3)
+    assert torch.equal(outs[0], outs[1])
+    ref = torch.relu(sum(x.double() @ w.double().t() for x, w in zip(a, b)) + bias.double())
+    assert float((outs[1].double() - ref).norm() / ref.norm()) < 2e-6

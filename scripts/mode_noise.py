@@ -23,9 +23,13 @@ for seed in range(21, 21 + int(sys.argv[1]) if len(sys.argv) > 1 else 29):
     row = {"seed": seed, "cpu_fp32": {k: rel_err(f32_logits if k == "logits" else f32_grads[k], ref_logits if k == "logits" else ref_grads[k]) for k in keys}}
     model = model.to(dev).eval()
     from graph_representation_learning_b200 import _lib
-    for mode, mode_b in (("tf32x3", "tf32x3"), ("tf32bc", "tf32bc"), ("tf32x3", "tf32bc"), ("tf32bc", "tf32x3")):
+    grid = (("tf32x3", "tf32x3", 2), ("tf32bc", "tf32bc", 2), ("tf32x3", "tf32bc", 2), ("tf32bc", "tf32x3", 2))
+    if os.environ.get("NOISE_X3_PROMO"):      # forward three-product accumulator promotion interval: 2 (default) vs 4 vs 8
+        grid = (("tf32x3", "tf32bc", 2), ("tf32x3", "tf32bc", 4), ("tf32x3", "tf32bc", 8))
+    for mode, mode_b, x3p in grid:
         ops.GemmConfig.fp32_mode, ops.GemmConfig.fp32_mode_bwd = mode, mode_b
-        promo = mode_b[4:]
+        _lib.load().grl_gemm_x3_set_promo(x3p)
+        promo = mode_b[4:] + (f"_x3promo{x3p}" if x3p != 2 else "")
         model.zero_grad(set_to_none=True)
         logits = model([V.to(dev), A.to(dev)])
         torch.nn.functional.cross_entropy(logits.transpose(1, 2), y.to(dev)).backward()

@@ -31,6 +31,62 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
     const bool vec_ok = epilogue_vec_ok(p);
     const int rsub = lane >> 2, c4 = (lane & 3) * 4;
     const int rows = min(32, p.M - row0);
+    // Fast path (warp-uniform): no dropout, no atomics, aligned output, all 64 columns inside N.  The general path below
+    // re-tests every flag and rebuilds a 64-bit address per 4 elements (~50 instructions per element group); short-K
+    // products (GraphConv dX: 8 K-blocks per tile) were bound by exactly that instruction stream in the drain warps.
+    if (!(p.flags & GRL_EPI_DROPOUT) && !p.atomic_add && vec_ok && n0 + X3Cfg::DRAIN_COLS <= p.N) {
+        const bool relu = (p.flags & GRL_EPI_RELU) != 0;
+        const bool leaky = !relu && (p.flags & kEpiAnyLeaky) != 0;
+        const float slope = leaky_slope(p.flags);
+        const int64_t ldc = p.ldc;
+#pragma unroll
+        for (int c0 = 0; c0 < X3Cfg::DRAIN_COLS; c0 += CH) {
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < CH; j += 4)
+                *reinterpret_cast<float4*>(buf + lane * PITCH + j) = make_float4(acc[c0 + j], acc[c0 + j + 1], acc[c0 + j + 2], acc[c0 + j + 3]);
+            __syncwarp();
+            const int col = n0 + c0 + c4;
+            float4 b4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (p.flags & GRL_EPI_BIAS) b4 = make_float4(__ldg(p.bias + col), __ldg(p.bias + col + 1), __ldg(p.bias + col + 2), __ldg(p.bias + col + 3));
+            const int64_t off = static_cast<int64_t>(row0 + rsub) * ldc + col;
+            if (p.out_bf16) {
+                __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.C) + off;
+#pragma unroll
+                for (int rr = rsub; rr < 32; rr += 8, out += 8 * ldc) {
+                    if (rr < rows) {
+                        float4 v = *reinterpret_cast<const float4*>(buf + rr * PITCH + c4);
+                        v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+                        if (relu) {
+                            v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); v.z = fmaxf(v.z, 0.0f); v.w = fmaxf(v.w, 0.0f);
+                        } else if (leaky) {
+                            v.x = v.x > 0.0f ? v.x : slope * v.x; v.y = v.y > 0.0f ? v.y : slope * v.y;
+                            v.z = v.z > 0.0f ? v.z : slope * v.z; v.w = v.w > 0.0f ? v.w : slope * v.w;
+                        }
+                        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+                        *reinterpret_cast<uint2*>(out) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+                    }
+                }
+            } else {
+                float* out = static_cast<float*>(p.C) + off;
+#pragma unroll
+                for (int rr = rsub; rr < 32; rr += 8, out += 8 * ldc) {
+                    if (rr < rows) {
+                        float4 v = *reinterpret_cast<const float4*>(buf + rr * PITCH + c4);
+                        v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+                        if (relu) {
+                            v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); v.z = fmaxf(v.z, 0.0f); v.w = fmaxf(v.w, 0.0f);
+                        } else if (leaky) {
+                            v.x = v.x > 0.0f ? v.x : slope * v.x; v.y = v.y > 0.0f ? v.y : slope * v.y;
+                            v.z = v.z > 0.0f ? v.z : slope * v.z; v.w = v.w > 0.0f ? v.w : slope * v.w;
+                        }
+                        *reinterpret_cast<float4*>(out) = v;
+                    }
+                }
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int c0 = 0; c0 < X3Cfg::DRAIN_COLS; c0 += CH) {
         if (n0 + c0 >= p.N) break;                                  // warp-uniform

@@ -34,7 +34,8 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
     // Fast path (warp-uniform): no dropout, no atomics, aligned output, all 64 columns inside N.  The general path below
     // re-tests every flag and rebuilds a 64-bit address per 4 elements (~50 instructions per element group); short-K
     // products (GraphConv dX: 8 K-blocks per tile) were bound by exactly that instruction stream in the drain warps.
-    if (!(p.flags & GRL_EPI_DROPOUT) && !p.atomic_add && vec_ok && n0 + X3Cfg::DRAIN_COLS <= p.N) {
+    const bool drop = (p.flags & GRL_EPI_DROPOUT) != 0;      // fast path: Philox dropout only (one draw per 4 columns)
+    if ((!drop || (p.mask == nullptr && (p.N & 3) == 0)) && !p.atomic_add && vec_ok && n0 + X3Cfg::DRAIN_COLS <= p.N) {
         const bool relu = (p.flags & GRL_EPI_RELU) != 0;
         const bool leaky = !relu && (p.flags & kEpiAnyLeaky) != 0;
         const float slope = leaky_slope(p.flags);
@@ -63,6 +64,11 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
                             v.x = v.x > 0.0f ? v.x : slope * v.x; v.y = v.y > 0.0f ? v.y : slope * v.y;
                             v.z = v.z > 0.0f ? v.z : slope * v.z; v.w = v.w > 0.0f ? v.w : slope * v.w;
                         }
+                        if (drop) {     // same (row * N + col) >> 2 Philox block as epilogue_store4 / grl_bias_act_dropout_fwd
+                            const uint4 d = Philox::draw(p.seed, p.stream_id, static_cast<uint64_t>(static_cast<int64_t>(row0 + rr) * p.N + col) >> 2);
+                            v.x = d.x >= p.thresh ? v.x * p.scale : 0.0f; v.y = d.y >= p.thresh ? v.y * p.scale : 0.0f;
+                            v.z = d.z >= p.thresh ? v.z * p.scale : 0.0f; v.w = d.w >= p.thresh ? v.w * p.scale : 0.0f;
+                        }
                         const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
                         *reinterpret_cast<uint2*>(out) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
                     }
@@ -79,6 +85,11 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
                         } else if (leaky) {
                             v.x = v.x > 0.0f ? v.x : slope * v.x; v.y = v.y > 0.0f ? v.y : slope * v.y;
                             v.z = v.z > 0.0f ? v.z : slope * v.z; v.w = v.w > 0.0f ? v.w : slope * v.w;
+                        }
+                        if (drop) {
+                            const uint4 d = Philox::draw(p.seed, p.stream_id, static_cast<uint64_t>(static_cast<int64_t>(row0 + rr) * p.N + col) >> 2);
+                            v.x = d.x >= p.thresh ? v.x * p.scale : 0.0f; v.y = d.y >= p.thresh ? v.y * p.scale : 0.0f;
+                            v.z = d.z >= p.thresh ? v.z * p.scale : 0.0f; v.w = d.w >= p.thresh ? v.w * p.scale : 0.0f;
                         }
                         *reinterpret_cast<float4*>(out) = v;
                     }

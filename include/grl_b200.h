@@ -207,7 +207,9 @@ int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo,
                 const float* bias, uint32_t flags, float p, const uint8_t* mask,
                 uint64_t seed, uint64_t stream_id, void* stream);
 /* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
- * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2. */
+ * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2.  Negative values are experiment
+ * switches with identical results: -3 (default) NT products take the activation operand through TMEM
+ * (gemm_bc_kernel<NT, x3>), -4 through shared memory (gemm_x3_kernel); -2 (default) persistent CTAs, -1 one CTA per tile. */
 int grl_gemm_x3_set_promo(int promo);
 /* bf16 NT products with N > 128 run on the persistent kernel (double-buffered TMEM accumulators, epilogue overlapped
  * with the next tile); 0 selects the one-tile-per-CTA kernel instead (A/B measurements; results are identical). */

@@ -206,6 +206,13 @@ int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo,
                 void* C, int64_t ldc, int out_dtype, int M, int N, int mode,
                 const float* bias, uint32_t flags, float p, const uint8_t* mask,
                 uint64_t seed, uint64_t stream_id, void* stream);
+/* C[M, N] (fp32) = gate > 0 ? (A[M, K] * B[N, K]^T) * gate_scale : 0 -- the gradient GEMM dY = dZ_next * W_next fused with
+ * the ReLU / dropout derivative of the layer whose OUTPUT is `gate` (grl_bias_act_dropout_bwd's arithmetic applied while
+ * the tile leaves the accumulator; replaces autograd's dY tensor + a pass over it for classifier -> w_rand,
+ * drop_robust_gcn.py:100-103).  mode GRL_GEMM_TF32X3 (B_lo = grl_split_tf32 low part) or GRL_GEMM_TF32_BF16C (B_lo =
+ * grl_split_tf32_mix packed operand).  Needs N % 64 == 0 and 16-byte aligned / pitched C and gate (GRL_E_UNSUP otherwise). */
+int grl_gemm_nt_gated(const void* A, int64_t lda, const void* B, const void* B_lo, int64_t ldb, int K, float* C, int64_t ldc,
+                      int M, int N, int mode, const float* gate, int64_t ld_gate, float gate_scale, void* stream);
 /* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
  * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2.  Negative values are experiment
  * switches with identical results: -3 (default) NT products take the activation operand through TMEM

@@ -631,3 +631,25 @@ def test_csr_pack_single_read_bitmap_equals_two_pass_pack(dev, B, N, L, dtype, d
     for a, b in zip(*outs):
         assert torch.equal(a, b)
     assert int(outs[1][0][-1]) == int((A.float() != 0).sum()) + B * N
+
+
+def test_projection_head_equals_two_layers(dev):
+    """ops.projection_head (w_rand -> ReLU -> dropout -> classifier as one autograd node, hidden gradient gated inside
+    the GEMM epilogue by grl_gemm_nt_gated) against the two separate layers: logits and every gradient bit for bit,
+    Philox dropout (same seed / stream) and a ragged node count (row tail of the last tile)."""
+    from graph_representation_learning_b200 import GraphCNNDropEdge, synthetic
+    wl = synthetic.Workload("head", 3, 171, input_dim=40, output_dim=53, net_size=256)
+    V, A, y = synthetic.make_batch(wl, 5, dev)
+    res = []
+    for fuse in (False, True):
+        torch.manual_seed(3)
+        model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size).to(dev).train()
+        model.fuse_head = fuse
+        model.rng_seed = 99
+        logits = model([V, A])
+        torch.nn.functional.cross_entropy(logits.transpose(1, 2), y).backward()
+        res.append((logits.detach().clone(), {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}))
+    assert torch.equal(res[0][0], res[1][0])
+    assert res[0][1].keys() == res[1][1].keys()
+    for k in res[0][1]:
+        assert torch.equal(res[0][1][k], res[1][1][k]), k

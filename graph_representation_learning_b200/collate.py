@@ -158,6 +158,8 @@ class EdgeListCollate(BaseCollate):
                 tri, wts = np.asarray(s["edges"], dtype=np.int32).reshape(-1, 3), s.get("edge_weights")
             else:
                 tri, wts = dense_to_edges(np.asarray(s["adjacency_matrix"]))
+            if tri.shape[0] and (tri.min() < 0 or tri[:, 0].max() >= n or tri[:, 2].max() >= n or tri[:, 1].max() >= self.L):
+                raise ValueError(f"sample {b}: edge triple (start, label, end) outside [0, {n}) x [0, {self.L}) x [0, {n})")
             e4 = np.empty((tri.shape[0], 4), dtype=np.int32)
             e4[:, 0] = b
             e4[:, 1] = tri[:, 0] + off

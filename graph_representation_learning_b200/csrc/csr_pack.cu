@@ -224,12 +224,20 @@ __global__ void __launch_bounds__(256) csr_fill_bitmap_kernel(const T* __restric
 }
 
 // ---------------------------------------------------------------- COO (edge list) -> CSR
+// An edge whose (b, i, l, j) lies outside the batch must not become an out-of-bounds atomicAdd: it is re-pointed at entry
+// (0, 0, 0, 0) with value 0 (no contribution; the entry count E + B*N the caller sized its buffers for still holds).
+// collate.EdgeListCollate range-checks on the host and raises, so this only guards raw device edge lists.
+__device__ __forceinline__ bool coo_edge_ok(const int4& q, int B, int N, int L) {
+    return q.x >= 0 && q.x < B && q.y >= 0 && q.y < N && q.z >= 0 && q.z < L && q.w >= 0 && q.w < N;
+}
+
 __global__ void coo_count_kernel(const int32_t* __restrict__ edges, int64_t E, int N, int L,
                                  int32_t* __restrict__ rowptr, int64_t n_nodes) {
     const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t e = tid; e < E; e += stride) {
-        const int4 q = __ldg(reinterpret_cast<const int4*>(edges) + e);  // (b, i, l, j)
+        int4 q = __ldg(reinterpret_cast<const int4*>(edges) + e);  // (b, i, l, j)
+        if (!coo_edge_ok(q, static_cast<int>(n_nodes / N), N, L)) q = make_int4(0, 0, 0, 0);
         const int64_t r = (static_cast<int64_t>(q.x) * N + q.y) * (L + 1) + q.z + 1;
         atomicAdd(&rowptr[r + 1], 1);
     }
@@ -242,11 +250,13 @@ __global__ void coo_scatter_kernel(const int32_t* __restrict__ edges, const floa
     const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t e = tid; e < E; e += stride) {
-        const int4 q = __ldg(reinterpret_cast<const int4*>(edges) + e);
+        int4 q = __ldg(reinterpret_cast<const int4*>(edges) + e);
+        const bool ok = coo_edge_ok(q, static_cast<int>(n_nodes / N), N, L);
+        if (!ok) q = make_int4(0, 0, 0, 0);
         const int64_t r = (static_cast<int64_t>(q.x) * N + q.y) * (L + 1) + q.z + 1;
         const int32_t pos = rowptr[r] + atomicAdd(&cursor[r], 1);
         col[pos] = q.w;
-        val[pos] = weights ? weights[e] : 1.0f;
+        val[pos] = ok ? (weights ? weights[e] : 1.0f) : 0.0f;
     }
     for (int64_t v = tid; v < n_nodes; v += stride) {
         const int32_t pos = rowptr[v * (L + 1)];
@@ -255,8 +265,10 @@ __global__ void coo_scatter_kernel(const int32_t* __restrict__ edges, const floa
     }
 }
 
-// Rows are tiny (a handful of entries): one thread insertion-sorts its row by (col, val) so the
-// result is independent of the atomic arrival order above.
+// Rows are tiny (a handful of entries): one thread insertion-sorts its row by (col ascending, val descending) so the
+// result is independent of the atomic arrival order above.  Repeated (b, i, l, j) triples then sit next to each other: the
+// reference's dense build `adj[start, label, end] = w` (graph_utils.py:821-829) is idempotent, so all but the first
+// (largest) keep their slot with value 0 -- same aggregation as the dense collate, no second compaction pass.
 __global__ void csr_sort_rows_kernel(const int32_t* __restrict__ rowptr, int64_t R, int32_t* __restrict__ col,
                                      float* __restrict__ val) {
     const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -267,7 +279,7 @@ __global__ void csr_sort_rows_kernel(const int32_t* __restrict__ rowptr, int64_t
             const int32_t c = col[a];
             const float v = val[a];
             int32_t b = a - 1;
-            while (b >= s && (col[b] > c || (col[b] == c && val[b] > v))) {
+            while (b >= s && (col[b] > c || (col[b] == c && val[b] < v))) {
                 col[b + 1] = col[b];
                 val[b + 1] = val[b];
                 --b;
@@ -275,6 +287,8 @@ __global__ void csr_sort_rows_kernel(const int32_t* __restrict__ rowptr, int64_t
             col[b + 1] = c;
             val[b + 1] = v;
         }
+        for (int32_t a = s + 1; a < e; ++a)
+            if (col[a] == col[a - 1]) val[a] = 0.0f;
     }
 }
 

@@ -22,11 +22,6 @@ struct GemmParams {
     uint32_t thresh;            // keep iff philox word >= thresh
     const uint8_t* mask;        // injected keep bits [M*N] or null
     uint64_t seed, stream_id;
-    // optional output gate (grl_gemm_nt_gated): C = gate > 0 ? acc * gate_scale : 0 -- the ReLU / dropout derivative of
-    // the layer whose output `gate` is, applied to dY = dZ_next * W_next while it leaves the accumulator
-    const float* gate;
-    int64_t ld_gate;
-    float gate_scale;
 };
 
 // Fused epilogue for 4 consecutive columns [col, col+4) of one output row held in registers (bias already added).

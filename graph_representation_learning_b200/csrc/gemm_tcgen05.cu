@@ -546,28 +546,6 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
     }
 }
 
-// dY_prev = (dZ * W) gated by the previous layer's output: one K segment, fp32, the fp32-grade kernels only (their drain
-// epilogue has the gate); N % 64 == 0 and an aligned, 16-byte-pitched C and gate keep every warp on the fast epilogue path.
-extern "C" int grl_gemm_nt_gated(const void* A, int64_t lda, const void* B, const void* B_lo, int64_t ldb, int K, float* C,
-                                 int64_t ldc, int M, int N, int mode, const float* gate, int64_t ld_gate, float gate_scale,
-                                 void* stream) {
-    GRL_CHECK_ARG(A && B && B_lo && C && gate, GRL_E_BADARG, "grl_gemm_nt_gated: null pointer");
-    GRL_CHECK_ARG(M > 0 && N > 0 && K > 0, GRL_E_BADARG, "grl_gemm_nt_gated: bad shape M=%d N=%d K=%d", M, N, K);
-    GRL_CHECK_ARG(mode == kTF32X3 || mode == kTF32BC, GRL_E_UNSUP, "grl_gemm_nt_gated: mode %d (TF32X3 or TF32_BF16C)", mode);
-    GRL_CHECK_ARG(N % 64 == 0 && ldc % 4 == 0 && ld_gate % 4 == 0 && ldc >= N && ld_gate >= N && aligned_to(C, 16) &&
-                      aligned_to(gate, 16),
-                  GRL_E_UNSUP, "grl_gemm_nt_gated: needs N %% 64 == 0 and 16-byte aligned, 16-byte pitched C and gate");
-    GRL_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && lda >= K && ldb >= K && aligned_to(A, 16) && aligned_to(B, 16) &&
-                      aligned_to(B_lo, 16),
-                  GRL_E_ALIGN, "grl_gemm_nt_gated: operands need 16-byte aligned base pointers and row pitches >= K");
-    GemmParams gp{};
-    gp.M = M; gp.N = N; gp.C = C; gp.ldc = ldc; gp.scale = 1.0f; gp.thresh = 0;
-    gp.gate = gate; gp.ld_gate = ld_gate; gp.gate_scale = gate_scale;
-    GemmArgs ga{A, B, B_lo, nullptr, nullptr, nullptr, lda, ldb, 0, 0, K, 0};
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    return mode == kTF32BC ? launch_gemm_bc(ga, gp, st, false, 0) : launch_gemm_x3(ga, gp, st);
-}
-
 extern "C" int grl_gemm_nt_bf16_set_persistent(int on) {
     g_nt_bf16_persistent = on != 0;
     return 0;

@@ -91,11 +91,6 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
                             v.x = d.x >= p.thresh ? v.x * p.scale : 0.0f; v.y = d.y >= p.thresh ? v.y * p.scale : 0.0f;
                             v.z = d.z >= p.thresh ? v.z * p.scale : 0.0f; v.w = d.w >= p.thresh ? v.w * p.scale : 0.0f;
                         }
-                        if (p.gate) {   // same arithmetic as grl_bias_act_dropout_bwd: y > 0 ? dY * scale : +0
-                            const float4 y = *reinterpret_cast<const float4*>(p.gate + static_cast<int64_t>(row0 + rr) * p.ld_gate + col);
-                            v.x = y.x > 0.0f ? v.x * p.gate_scale : 0.0f; v.y = y.y > 0.0f ? v.y * p.gate_scale : 0.0f;
-                            v.z = y.z > 0.0f ? v.z * p.gate_scale : 0.0f; v.w = y.w > 0.0f ? v.w * p.gate_scale : 0.0f;
-                        }
                         *reinterpret_cast<float4*>(out) = v;
                     }
                 }

@@ -208,11 +208,9 @@ spmm_rows_generic_kernel(const int32_t* __restrict__ ptr, const int32_t* __restr
     }
 }
 
-// grl_spmm_set_tile_mode: 0 auto, -1 node-per-warp gather kernel only, -2 legacy row-per-warp kernel,
-// 8/16/32 first-generation slab kernel with that many lanes per node group, 108/116/132 slab v2 with 8/16/32 lanes
+// grl_spmm_set_tile_mode: 0 auto, -1 node-per-warp gather kernel, -2 legacy row-per-warp kernel (both: grl_spmm_fwd);
+// 108/116/132 (208/216) force 8/16/32 lanes per node group (two 16-byte words per lane) in grl_spmm_fwd_stream
 int g_spmm_mode = 0;
-int try_launch_spmm_tile(const int32_t* rowptr, const int32_t* col, const float* w, const void* X, int64_t ldx, void* Y,
-                         int64_t ldy, int dtype, int B, int N, int L, int F, cudaStream_t st);   // spmm_tile.cu
 extern int g_slab2_gl;    // spmm_slab2.cu
 extern int g_slab2_vw;    // spmm_slab2.cu
 
@@ -320,10 +318,9 @@ extern "C" int grl_dropedge_weights(const float* val, const uint8_t* mask, int64
 }
 
 extern "C" int grl_spmm_set_tile_mode(int mode) {
-    if (mode != 0 && mode != -1 && mode != -2 && mode != 8 && mode != 16 && mode != 32 && mode != 108 && mode != 116 &&
-        mode != 132 && mode != 208 && mode != 216) {
-        set_error("grl_spmm_set_tile_mode: mode %d not in {0 auto, -1 gather, -2 legacy rows, 8/16/32 slab v1, "
-                  "108/116/132 slab v2}", mode);
+    if (mode != 0 && mode != -1 && mode != -2 && mode != 108 && mode != 116 && mode != 132 && mode != 208 && mode != 216) {
+        set_error("grl_spmm_set_tile_mode: mode %d not in {0 auto, -1 gather, -2 legacy rows, 108/116/132/208/216 slab "
+                  "group width}", mode);
         return GRL_E_BADARG;
     }
     g_spmm_mode = mode > 100 ? 0 : mode;             // 1xx / 2xx only steer grl_spmm_fwd_stream
@@ -339,10 +336,6 @@ extern "C" int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const flo
     GRL_CHECK_ARG(ldx >= F && ldy >= F, GRL_E_BADARG, "grl_spmm_fwd: leading dimension < F");
     const int64_t R = static_cast<int64_t>(B) * N * (L + 1);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (g_spmm_mode >= 0 && (dtype == GRL_F32 || dtype == GRL_BF16)) {
-        const int rc = try_launch_spmm_tile(rowptr, col, w, X, ldx, Y, ldy, dtype, B, N, L, F, st);
-        if (rc != 1) return rc;       // launched (0) or failed; 1 = slab does not fit -> gather kernel
-    }
     if (dtype == GRL_F32)
         return launch_spmm<float, false>(rowptr, col, nullptr, w, X, ldx, Y, ldy, R, N * (L + 1), N, F, false, st);
     if (dtype == GRL_BF16)

@@ -3,7 +3,7 @@
 // Reference semantics: new_V = torch.matmul(A', V) (gnn/models/networks/robust_gcn.py:45-47), A' already DropEdge-masked
 // (gnn/models/networks/drop_robust_gcn.py:76,80,85).
 //
-// The first slab kernel (spmm_tile.cu) was issue-bound: ~95 instructions of bookkeeping per typed row and 11.5 per
+// The first slab kernel (removed in round 2; profiles/r01_s10_*) was issue-bound: ~95 instructions of bookkeeping per typed row and 11.5 per
 // entry step (ncu: 333 M warp instructions, 72 % issue-slot utilisation, 0.42 ms for 1.10 GB of compulsory traffic).
 // A first node-level rewrite that tagged / compacted the entries inside the SpMM kernel executed 390 M instructions:
 // the tagging prologue (~600 per warp iteration) ran once per (node, column chunk).  Hence the split used here:
@@ -367,7 +367,7 @@ static int try_launch_spmm_slab2(const int2* nodeinfo, const uint2* ew, const vo
                                  int dtype, int B, int N, int L, int F, cudaStream_t st) {
     const int es = dtype == GRL_F32 ? 4 : 2;
     if (!aligned_to(X, 16) || (ldx * es) % 16 != 0 || !aligned_to(Y, 16) || (ldy * es) % 16 != 0) return 1;
-    if (L + 1 >= 127 || N >= (1 << 24) - 2) return 1;             // row type: 8 bits, column: 24 bits of a stream entry
+    if (L + 1 > 31 || N >= (1 << 24) - 2) return 1;               // row type: 8 bits, column: 24 bits of a stream entry
     const int n_boxes = (N + 255) / 256;
     const int box_rows = (N + n_boxes - 1) / n_boxes;
     const int rows = n_boxes * box_rows;
@@ -435,7 +435,8 @@ extern "C" int grl_dropedge_stream(const int32_t* rowptr, const int32_t* col, co
                                    void* ew, int32_t* nodeinfo, void* stream) {
     GRL_CHECK_ARG(rowptr && col && val && w && ew && nodeinfo, GRL_E_BADARG, "grl_dropedge_stream: null pointer");
     GRL_CHECK_ARG(p >= 0.0f && p < 1.0f, GRL_E_BADARG, "grl_dropedge_stream: p=%f outside [0,1)", p);
-    GRL_CHECK_ARG(n_nodes > 0 && L > 0 && L + 1 < 127, GRL_E_BADARG, "grl_dropedge_stream: bad shape (L + 1 must be < 127)");
+    GRL_CHECK_ARG(n_nodes > 0 && L > 0 && L + 1 <= 31, GRL_E_BADARG,
+                  "grl_dropedge_stream: bad shape (a node's L + 2 row pointers live one per lane: L + 1 must be <= 31)");
     GRL_CHECK_ARG(aligned_to(ew, 8) && aligned_to(nodeinfo, 8), GRL_E_ALIGN, "grl_dropedge_stream: ew / nodeinfo need 8-byte alignment");
     int64_t blocks = (n_nodes + 7) / 8;
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;

@@ -14,7 +14,8 @@ namespace grl {
 
 constexpr int kTrainThreads = 256;
 
-// one warp per row; per-block partial sums (loss * w, w) in block order -> partial[2 * blockIdx.x + {0, 1}]
+// one warp per row; per-block partial sums (loss * w, w, #labels outside [0, C) that are not ignore_index) in block order
+// -> partial[3 * blockIdx.x + {0, 1, 2}]
 __global__ void __launch_bounds__(kTrainThreads)
 ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target,
               const float* __restrict__ weight, int64_t ignore_index, int64_t M, int C, float* __restrict__ lse,
@@ -22,7 +23,7 @@ ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __res
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
-    float loss_sum = 0.f, w_sum = 0.f;
+    float loss_sum = 0.f, w_sum = 0.f, bad = 0.f;
     for (int64_t r = warp; r < M; r += n_warps) {
         const float* x = logits + r * ld;
         float m = -INFINITY;
@@ -38,32 +39,47 @@ ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __res
             const float w = weight ? weight[y] : 1.0f;
             loss_sum += w * (l - x[y]);
             w_sum += w;
+        } else if (y != ignore_index) {
+            bad += 1.0f;                     // nn.CrossEntropyLoss raises on such a target; here the loss turns NaN
         }
     }
-    __shared__ float sl[kTrainThreads / 32], sw[kTrainThreads / 32];
-    if (lane == 0) { sl[wib] = loss_sum; sw[wib] = w_sum; }
+    __shared__ float sl[kTrainThreads / 32], sw[kTrainThreads / 32], sb[kTrainThreads / 32];
+    if (lane == 0) { sl[wib] = loss_sum; sw[wib] = w_sum; sb[wib] = bad; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        float a = 0.f, b = 0.f;
-        for (int k = 0; k < kTrainThreads / 32; ++k) { a += sl[k]; b += sw[k]; }
-        partial[2 * blockIdx.x] = a;
-        partial[2 * blockIdx.x + 1] = b;
+        float a = 0.f, b = 0.f, c = 0.f;
+        for (int k = 0; k < kTrainThreads / 32; ++k) { a += sl[k]; b += sw[k]; c += sb[k]; }
+        partial[3 * blockIdx.x] = a;
+        partial[3 * blockIdx.x + 1] = b;
+        partial[3 * blockIdx.x + 2] = c;
     }
 }
 
-// out[0] = sum(loss) / sum(w), out[1] = sum(w)   (one block; fixed order)
+// out[0] = sum(loss) / sum(w), out[1] = sum(w), out[2] = number of out-of-range labels, out[3] = sum(loss)
+// (one block; fixed order).  All rows ignored (sum(w) == 0): loss 0 and, through out[1] = 0, a zero gradient.
+// Any label outside [0, C) that is not ignore_index: loss = NaN (the reference's nn.CrossEntropyLoss raises).
 __global__ void __launch_bounds__(kTrainThreads)
 ce_finish_kernel(const float* __restrict__ partial, int n_blocks, float* __restrict__ out) {
-    __shared__ float sa[kTrainThreads], sb[kTrainThreads];
-    float a = 0.f, b = 0.f;
-    for (int k = threadIdx.x; k < n_blocks; k += kTrainThreads) { a += partial[2 * k]; b += partial[2 * k + 1]; }
-    sa[threadIdx.x] = a; sb[threadIdx.x] = b;
+    __shared__ float sa[kTrainThreads], sb[kTrainThreads], sc[kTrainThreads];
+    float a = 0.f, b = 0.f, c = 0.f;
+    for (int k = threadIdx.x; k < n_blocks; k += kTrainThreads) {
+        a += partial[3 * k]; b += partial[3 * k + 1]; c += partial[3 * k + 2];
+    }
+    sa[threadIdx.x] = a; sb[threadIdx.x] = b; sc[threadIdx.x] = c;
     __syncthreads();
     for (int o = kTrainThreads / 2; o >= 1; o >>= 1) {
-        if (threadIdx.x < o) { sa[threadIdx.x] += sa[threadIdx.x + o]; sb[threadIdx.x] += sb[threadIdx.x + o]; }
+        if (threadIdx.x < o) {
+            sa[threadIdx.x] += sa[threadIdx.x + o]; sb[threadIdx.x] += sb[threadIdx.x + o]; sc[threadIdx.x] += sc[threadIdx.x + o];
+        }
         __syncthreads();
     }
-    if (threadIdx.x == 0) { out[0] = sa[0] / sb[0]; out[1] = sb[0]; }
+    if (threadIdx.x == 0) {
+        const float mean = sb[0] > 0.f ? sa[0] / sb[0] : 0.f;
+        out[0] = sc[0] > 0.f ? __int_as_float(0x7fc00000) : mean;
+        out[1] = sb[0];
+        out[2] = sc[0];
+        out[3] = sa[0];
+    }
 }
 
 // dlogits[r][c] = g * w_y / sum(w) * (softmax(x)[c] - [c == y]);  0 for ignored rows
@@ -74,7 +90,7 @@ ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __res
               int64_t ldd) {
     const int64_t total = M * C;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    const float g = grad_out[0] / loss_out[1];
+    const float g = loss_out[1] > 0.f ? grad_out[0] / loss_out[1] : 0.f;
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
         const int64_t r = t / C;
         const int c = static_cast<int>(t - r * C);
@@ -155,7 +171,7 @@ static int grid_for(int64_t n_items, int per_block) {
 
 using namespace grl;
 
-extern "C" size_t grl_reduce_workspace_bytes(void) { return sizeof(float) * 2 * kNumSMs * 8; }
+extern "C" size_t grl_reduce_workspace_bytes(void) { return sizeof(float) * 3 * kNumSMs * 8; }
 
 extern "C" int grl_ce_fwd(const float* logits, int64_t ld, const int64_t* target, const float* weight,
                           int64_t ignore_index, int64_t M, int C, float* lse, float* loss_out, void* workspace,

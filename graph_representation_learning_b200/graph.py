@@ -97,7 +97,12 @@ class PackedGraphBatch:
     def from_edges(edges: torch.Tensor, B: int, N: int, L: int, weights: Optional[torch.Tensor] = None,
                    with_transpose: bool = True) -> "PackedGraphBatch":
         """Pack an edge list ``int32 [E, 4] = (b, i, l, j)`` (node indices already include the collate's pad
-        offset).  Self loops are added here, exactly once per node, as type-0 rows."""
+        offset).  Self loops are added here, exactly once per node, as type-0 rows.
+
+        Repeated ``(b, i, l, j)`` triples keep one slot each but only the first (largest weight) carries a value, the
+        others 0: the aggregation equals the reference's idempotent dense build ``adj[start, label, end] = w``
+        (graph_utils.py:821-829).  Triples outside the batch are neutralised on the device (value 0, no out-of-bounds
+        write); ``collate.EdgeListCollate`` range-checks on the host and raises."""
         _lib.require_cuda(edges, "edges")
         if edges.dim() != 2 or edges.shape[1] != 4:
             raise _lib.GrlError(f"edges must be [E, 4], got {tuple(edges.shape)}")
@@ -159,7 +164,7 @@ class PackedGraphBatch:
                 raise _lib.GrlError("edge mask must be uint8 with one entry per stored non-zero")
             mask = mask.contiguous()
         w = torch.empty_like(self.val)
-        if self.L + 1 < 127 and self.N < (1 << 24) - 2:
+        if self.L + 1 <= 31 and self.N < (1 << 24) - 2:      # one lane per row pointer of a node (csrc/spmm_slab2.cu)
             # forward fast path: the same w plus the compacted, row-tagged node streams of csrc/spmm_slab2.cu
             ew = torch.empty(max(self.nnz, 1), 2, dtype=torch.int32, device=self.device)
             nodeinfo = torch.empty(self.num_nodes, 2, dtype=torch.int32, device=self.device)

@@ -162,11 +162,6 @@ class RanPACLayer(nn.Module):
 
 @register_model
 class GraphCNNDropEdge(BaseNetwork):
-    # True: w_rand -> dropout -> classifier as one autograd node (ops.projection_head, hidden gradient gated in the GEMM
-    # epilogue; bit-identical).  Measured 0.1-0.3 ms SLOWER per cfg2 step than the two layers (scripts/head_ab.py): the
-    # gate loads sit in the drain warps, which already bound that K = 64 product -- so it stays off.
-    fuse_head = False
-
     def __init__(self, input_dim: int, output_dim: int, num_edges: int, net_size: int = 256,
                  use_attention: bool = True):
         super().__init__()
@@ -255,13 +250,8 @@ class GraphCNNDropEdge(BaseNetwork):
         if self.use_attention:
             new_v = _flat(self.self_atten(new_v.view(B, N, -1)))
         wr = self.w_rand.projection.weight
-        if (self.fuse_head and new_v.dtype == torch.float32 and not wr.requires_grad and wr.shape[0] % 64 == 0 and
-                self.classifier.bias is not None and ops.GemmConfig.fp32_mode_bwd in ("tf32bc", "tf32x3")):
-            # w_rand -> dropout -> classifier as one autograd node (the hidden gradient is gated in the GEMM epilogue)
-            logits = ops.projection_head(new_v, wr, self.classifier.weight, self.classifier.bias, p_feat, fm[4], seed, sid + 7)
-        else:
-            new_v = ops.linear_act([new_v], wr, None, relu=True, p=p_feat, mask=fm[4], seed=seed, stream_id=sid + 7)
-            logits = ops.linear_act([new_v], self.classifier.weight, self.classifier.bias)
+        new_v = ops.linear_act([new_v], wr, None, relu=True, p=p_feat, mask=fm[4], seed=seed, stream_id=sid + 7)
+        logits = ops.linear_act([new_v], self.classifier.weight, self.classifier.bias)
         return logits.float().view(B, N, self.output_dim)
 
 

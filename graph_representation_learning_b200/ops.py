@@ -467,51 +467,6 @@ def sparse_linear_act(feats, weight: torch.Tensor, bias: Optional[torch.Tensor],
     return _SparseLinearAct.apply(feats, weight, bias, relu, float(p), mask, seed, stream_id, compute_dtype)
 
 
-class _ProjectionHead(torch.autograd.Function):
-    """logits = dropout(relu(x @ Wr^T)) @ Wc^T + bc with Wr frozen (drop_robust_gcn.py:100-103: w_rand, dropout,
-    classifier) as ONE autograd node: the backward computes dZ = (dlogits @ Wc) gated by the ReLU / dropout derivative of
-    the hidden activation inside the GEMM epilogue (grl_gemm_nt_gated) instead of materialising dY and masking it in a
-    second pass over [Nt, 10 H].  Same forward GEMMs, same bits as the two separate layers."""
-
-    @staticmethod
-    def forward(ctx, x, w_rand, w_cls, b_cls, p, mask, seed, stream_id):
-        y = gemm_nt([x], [w_rand], None, None, True, p, mask, seed, stream_id)
-        logits = gemm_nt([y], [w_cls], None, b_cls)
-        ctx.save_for_backward(x, w_rand, w_cls, y)
-        ctx.p = p
-        return logits
-
-    @staticmethod
-    def backward(ctx, dlogits):
-        x, w_rand, w_cls, y = ctx.saved_tensors
-        lib = _lib.load()
-        dlogits = dlogits.contiguous()
-        bwd = GemmConfig.fp32_mode_bwd
-        M, C = dlogits.shape
-        H = y.shape[1]
-        d_wc = gemm_tn(dlogits, y, bwd) if ctx.needs_input_grad[2] else None          # [out, 10H] like nn.Linear
-        d_bc = colsum(dlogits) if ctx.needs_input_grad[3] else None
-        dx = None
-        if ctx.needs_input_grad[0]:
-            mode = _mode_for(torch.float32, bwd)
-            a = _tma_ready(dlogits)
-            b_hi, b_lo = _prep_weight(w_cls.t(), torch.float32, mode)                  # NT "B" operand [10H, out]
-            dz = torch.empty(M, H, dtype=torch.float32, device=dlogits.device)
-            scale = 1.0 / (1.0 - ctx.p) if ctx.p > 0.0 else 1.0
-            _lib.check(lib.grl_gemm_nt_gated(a.data_ptr(), a.stride(0), b_hi.data_ptr(), b_lo.data_ptr(), b_hi.stride(0), C,
-                                             dz.data_ptr(), dz.stride(0), M, H, mode, y.data_ptr(), y.stride(0), scale,
-                                             _lib.stream_ptr(dz.device)), "grl_gemm_nt_gated")
-            _lib.count_launch(1)
-            dx = gemm_nt([dz], [w_rand.t()], fp32_mode=bwd)
-        return dx, None, d_wc, d_bc, None, None, None, None
-
-
-def projection_head(x: torch.Tensor, w_rand: torch.Tensor, w_cls: torch.Tensor, b_cls: Optional[torch.Tensor], p: float = 0.0,
-                    mask: Optional[torch.Tensor] = None, seed: int = 0, stream_id: int = 0) -> torch.Tensor:
-    """fp32 only, frozen ``w_rand``, hidden width a multiple of 64 (callers fall back to two ``linear_act`` otherwise)."""
-    return _ProjectionHead.apply(x, w_rand, w_cls, b_cls, float(p), mask, seed, stream_id)
-
-
 class _BatchNormAct(torch.autograd.Function):
     """leaky_relu(BatchNorm1d(x), slope) over the rows of x [M, C] (csrc/batchnorm.cu; fp32)."""
 

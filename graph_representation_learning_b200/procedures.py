@@ -256,6 +256,8 @@ class KVProcedure(BaseProcedure):
             y = batch_sample["node_label"].to(self.device, non_blocking=True)
             scores = self._get_metric_scores(pred.argmax(dim=-1), y, item_name="Node classification")
             scores["loss"] = float(loss.detach())
+            if hasattr(self.step.criterion, "check_labels"):
+                self.step.criterion.check_labels()        # out-of-range targets raise here (the step's one host read)
         return loss, scores
 
     def _run_train_step(self, batch_sample) -> Dict[str, Any]:
@@ -264,6 +266,7 @@ class KVProcedure(BaseProcedure):
         self.step.bucket.zero()
         with torch.set_grad_enabled(True):
             loss, scores = self._step_process(batch_sample, want)
+            self.step.bucket.arm_overlap()
             loss.backward()
             self.step.clip_and_step()
         return scores
@@ -331,7 +334,9 @@ class KVProcedure(BaseProcedure):
     def __call__(self) -> float:
         best_loss = float("inf")
         metrics: Dict[str, Any] = {"f1-score": 0.0}
-        self.model.zero_grad()
+        # kv_procedure.py:349 calls model.zero_grad(); on torch 2.x that sets p.grad = None and would detach the
+        # parameters from the flat bucket, so the bucket itself is cleared (and re-attaches stray gradients anyway)
+        self.step.bucket.zero()
         for epoch in range(int(self.config.num_epochs)):
             metrics = self._optimize_per_epoch(epoch)
             self._update_learning_rate(epoch, self.global_step)

@@ -60,23 +60,39 @@ def _reduce_workspace(device: torch.device) -> torch.Tensor:
     return ws
 
 
+def _dp_world() -> int:
+    return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+
+
 class _CrossEntropyFn(torch.autograd.Function):
-    """mean (weighted) cross entropy over the rows whose label is not ignore_index -- csrc/train_ops.cu"""
+    """mean (weighted) cross entropy over the rows whose label is not ignore_index -- csrc/train_ops.cu.
+
+    ``global_mean`` (data parallel): the denominator is the all-reduced weight sum, so the returned value is this
+    rank's SHARE of the mean over the global batch's valid nodes (cross_entropy_loss.py:33-35 applied to the
+    concatenated batch): shares add up to the global loss and gradients add up to the single-process gradient, whatever
+    the number of padded (-100) nodes per rank.  One 4-byte all-reduce between forward and backward."""
 
     @staticmethod
-    def forward(ctx, logits2d, target1d, weight, ignore_index):
+    def forward(ctx, logits2d, target1d, weight, ignore_index, global_mean, stats):
         from . import _lib
         M, C = logits2d.shape
         dev = logits2d.device
         lse = torch.empty(M, dtype=torch.float32, device=dev)
-        out = torch.empty(2, dtype=torch.float32, device=dev)
+        out = torch.empty(4, dtype=torch.float32, device=dev)
         _lib.check(_lib.load().grl_ce_fwd(logits2d.data_ptr(), logits2d.stride(0), target1d.data_ptr(), _lib.ptr(weight),
                                           int(ignore_index), M, C, lse.data_ptr(), out.data_ptr(),
                                           _reduce_workspace(dev).data_ptr(), _lib.stream_ptr(dev)), "grl_ce_fwd")
         _lib.count_launch(2)
-        ctx.save_for_backward(logits2d, target1d, weight, lse, out)
+        stats["bad_labels"] = out[2]
+        loss = out[0]
+        denom = out
+        if global_mean and _dp_world() > 1:
+            denom = out.clone()
+            dist.all_reduce(denom[1:2], op=dist.ReduceOp.SUM)            # weight sum of the global batch
+            loss = torch.where(out[2] > 0, out[0], out[3] / denom[1].clamp_min(1e-30))
+        ctx.save_for_backward(logits2d, target1d, weight, lse, denom)
         ctx.ignore_index = int(ignore_index)
-        return out[0]
+        return loss
 
     @staticmethod
     def backward(ctx, grad_out):
@@ -89,17 +105,31 @@ class _CrossEntropyFn(torch.autograd.Function):
                                           ctx.ignore_index, M, C, lse.data_ptr(), out.data_ptr(), g.data_ptr(),
                                           d.data_ptr(), C, _lib.stream_ptr(d.device)), "grl_ce_bwd")
         _lib.count_launch(1)
-        return d, None, None, None
+        return d, None, None, None, None, None
 
 
 class CrossEntropyLoss(nn.Module):
     """gnn/trainer/losses/cross_entropy_loss.py:9-35.  CUDA fp32 logits run the kernels of csrc/train_ops.cu; anything
-    else (the CPU tensors of the host-logic tests) goes through nn.CrossEntropyLoss like the reference."""
+    else (the CPU tensors of the host-logic tests) goes through nn.CrossEntropyLoss like the reference.
+
+    ``global_mean`` is switched on by ``KVTrainStep`` under torch.distributed: the mean then runs over the valid nodes
+    of the GLOBAL batch and the gradient all-reduce is a plain sum (see ``_CrossEntropyFn``).
+    A label outside [0, C) that is not the ignore index makes the loss NaN and is reported by ``check_labels()`` (the
+    reference's nn.CrossEntropyLoss raises on the spot; raising here would cost a host sync per step)."""
 
     def __init__(self, weight=None):
         super().__init__()
         w = None if weight is None else torch.as_tensor(weight, dtype=torch.float32)
         self.criterion = nn.CrossEntropyLoss(w)
+        self.global_mean = False
+        self._stats: Dict[str, Any] = {}
+
+    def check_labels(self) -> None:
+        """host read of the last forward's out-of-range label count; raises like nn.CrossEntropyLoss would have"""
+        bad = self._stats.get("bad_labels")
+        if bad is not None and float(bad) > 0:
+            raise ValueError(f"{int(float(bad))} target labels are outside [0, n_classes) and not ignore_index="
+                             f"{self.criterion.ignore_index}")
 
     def forward(self, pred: torch.Tensor, target: torch.Tensor, **kwargs) -> torch.Tensor:
         if pred.is_cuda and pred.dtype == torch.float32 and pred.dim() >= 2 and target.dtype == torch.int64:
@@ -110,13 +140,29 @@ class CrossEntropyLoss(nn.Module):
             w = self.criterion.weight
             if w is not None:
                 w = w.to(device=pred.device, dtype=torch.float32).contiguous()
-            return _CrossEntropyFn.apply(logits2d, target.reshape(-1).contiguous(), w, self.criterion.ignore_index)
+            return _CrossEntropyFn.apply(logits2d, target.reshape(-1).contiguous(), w, self.criterion.ignore_index,
+                                         self.global_mean, self._stats)
+        if self.global_mean and _dp_world() > 1:
+            # host-logic tests (gloo, CPU tensors): the same global mean, spelled with torch ops
+            w = self.criterion.weight
+            ls = nn.functional.cross_entropy(pred.transpose(1, 2), target, weight=w, reduction="sum",
+                                             ignore_index=self.criterion.ignore_index)
+            valid = target != self.criterion.ignore_index
+            wsum = (w.to(pred.device)[target[valid]].sum() if w is not None else valid.sum()).to(ls.dtype).reshape(1)
+            dist.all_reduce(wsum, op=dist.ReduceOp.SUM)
+            return ls / wsum[0]
         return self.criterion(pred.transpose(1, 2), target)
 
 
 class FlatGradBucket:
-    """All trainable gradients live in one flat fp32 buffer (``p.grad`` are views), so the data-parallel
-    reduction is a single in-place NCCL all-reduce and ``clip_grad_norm_`` is one norm over one tensor."""
+    """All trainable gradients live in one flat fp32 buffer (``p.grad`` are views), so ``clip_grad_norm_`` is one norm
+    over one tensor and the data-parallel reduction is NCCL all-reduces over contiguous slices of it.
+
+    Data parallel ("bucketed in reverse layer order, overlapped with backward"): the buffer is cut in two
+    at the end of the FIRST parameterised sub-module (``emb1``: its weight gradient [S, 4369] is the last and largest
+    GEMM of the backward pass).  Post-accumulate-grad hooks count the tail's gradients in; when the last one has landed
+    the tail slice is all-reduced asynchronously (NCCL's own stream) while the compute stream still runs emb1's
+    weight-gradient GEMM; ``all_reduce()`` then reduces the head slice and joins both."""
 
     def __init__(self, model: nn.Module):
         self.params = [p for p in model.parameters() if p.requires_grad]
@@ -126,17 +172,94 @@ class FlatGradBucket:
         for p in self.params:
             p.grad = self.flat[off:off + p.numel()].view_as(p)
             off += p.numel()
+        # head = trainable parameters of the first child module that has any (their gradients arrive last)
+        self.n_head_params, self.head_numel = 0, 0
+        for child in model.children():
+            own = [p for p in child.parameters() if p.requires_grad]
+            if own:
+                if len(self.params) > len(own) and all(a is b for a, b in zip(own, self.params)):
+                    self.n_head_params, self.head_numel = len(own), sum(p.numel() for p in own)
+                break
+        self._hooks: list = []
+        self._pending = 0
+        self._tail_work = None
+        self._armed = False
+
+    def _views(self, lo: int = 0, hi: Optional[int] = None):
+        off = 0
+        for k, p in enumerate(self.params):
+            if k >= lo and (hi is None or k < hi):
+                yield p, self.flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+
+    def reattach(self, lo: int = 0, hi: Optional[int] = None) -> None:
+        """Fold gradients that are no longer views of the bucket back in: ``model.zero_grad()`` /
+        ``optimizer.zero_grad()`` (set_to_none=True on torch 2.x) leave ``p.grad = None`` and autograd then allocates
+        fresh tensors.  None counts as zero.  Cheap when nothing strayed (pointer compares only)."""
+        for p, view in self._views(lo, hi):
+            g = p.grad
+            if g is None:
+                view.zero_()
+                p.grad = view
+            elif g.data_ptr() != view.data_ptr():
+                view.copy_(g)
+                p.grad = view
 
     def zero(self) -> None:
         self.flat.zero_()
+        for p, view in self._views():
+            if p.grad is None or p.grad.data_ptr() != view.data_ptr():
+                p.grad = view
+
+    # ------------------------------------------------------------------ data-parallel reduction
+    def arm_overlap(self) -> None:
+        """call before ``backward()``: the tail slice is reduced as soon as its last gradient has been accumulated"""
+        if _dp_world() <= 1 or self.n_head_params == 0:
+            return
+        if not self._hooks:
+            for p in self.params[self.n_head_params:]:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
+        self._pending = len(self.params) - self.n_head_params
+        self._tail_work = None
+        self._armed = True
+
+    def _on_grad(self, _p) -> None:
+        if not self._armed:
+            return
+        self._pending -= 1
+        if self._pending == 0:
+            self._launch_tail()
+
+    def _launch_tail(self) -> None:
+        self.reattach(self.n_head_params, None)
+        self._tail_work = dist.all_reduce(self.flat[self.head_numel:], op=dist.ReduceOp.SUM, async_op=True)
+
+    def all_reduce(self, average: bool = True) -> None:
+        """sum (``average=False``: the loss was already normalised by the GLOBAL valid-node count) or mean of the
+        gradients over the ranks; joins the overlapped tail reduction when ``arm_overlap()`` started one"""
+        self.reattach()
+        world = _dp_world()
+        if world <= 1:
+            return
+        if self._armed:
+            self._armed = False
+            if self._tail_work is None:          # some tail parameter got no gradient this step: nothing was launched
+                self._launch_tail()
+            head = dist.all_reduce(self.flat[:self.head_numel], op=dist.ReduceOp.SUM, async_op=True)
+            self._tail_work.wait()
+            head.wait()
+            self._tail_work = None
+        else:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+        if average:
+            self.flat.div_(world)
 
     def all_reduce_mean(self) -> None:
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-            self.flat.div_(dist.get_world_size())
+        self.all_reduce(average=True)
 
     def norm(self) -> torch.Tensor:
         """total 2-norm of the gradients as a device scalar (deterministic two-stage reduction on CUDA)"""
+        self.reattach()
         if self.flat.is_cuda:
             from . import _lib
             out = torch.empty(1, dtype=torch.float32, device=self.flat.device)
@@ -166,6 +289,14 @@ class FlatAdam(torch.optim.Optimizer):
                  amsgrad: bool = False, flat_grad: Optional[torch.Tensor] = None, **ignored: Any):
         if amsgrad:
             raise ValueError("FlatAdam implements amsgrad=False only")
+        # frozen parameters (w_rand / rp_emb / rp_final: requires_grad=False) never get a gradient; torch.optim.Adam skips
+        # them at every step, so they are left out of the flat buffers (weight decay must not touch them)
+        params = list(params)
+        if params and isinstance(params[0], dict):
+            params = [dict(g, params=[p for p in g["params"] if p.requires_grad]) for g in params]
+            params = [g for g in params if g["params"]]
+        else:
+            params = [p for p in params if p.requires_grad]
         super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
         self._params = [p for g in self.param_groups for p in g["params"]]
         if not self._params or not all(p.is_cuda and p.dtype == torch.float32 for p in self._params):
@@ -204,25 +335,38 @@ class FlatAdam(torch.optim.Optimizer):
         from . import _lib
         loss = closure() if closure is not None else None
         self._adopt_params()                     # a .to() / load that re-allocated a parameter is folded back in
+        skipped = set()
         if self._own_grad:                       # gradients are not views of one bucket: gather them
             for p, view in self._views(self.flat_g):
-                if p.grad is None:
-                    view.zero_()
+                if p.grad is None:               # torch.optim.Adam skips these (no moment update, no decay)
+                    skipped.add(id(p))
                 elif p.grad.data_ptr() != view.data_ptr():
                     view.copy_(p.grad)
         self._step += 1
         lib, off = _lib.load(), 0
         for g in self.param_groups:
-            k = sum(p.numel() for p in g["params"])
             b1, b2 = g["betas"]
-            sl = slice(off, off + k)
-            _lib.check(lib.grl_adam_step(self.flat_p[sl].data_ptr(), self.flat_g[sl].data_ptr(),
-                                         self.flat_m[sl].data_ptr(), self.flat_v[sl].data_ptr(), k, float(g["lr"]),
-                                         float(b1), float(b2), float(g["eps"]), float(g["weight_decay"]), self._step,
-                                         _lib.ptr(grad_norm), float(max_norm), _lib.stream_ptr(self.flat_p.device)),
-                       "grl_adam_step")
-            _lib.count_launch(1)
-            off += k
+            # maximal runs of parameters that have a gradient: one launch per run (one per group when none is skipped)
+            runs, start, pos = [], None, off
+            for p in g["params"]:
+                if id(p) in skipped:
+                    if start is not None:
+                        runs.append((start, pos))
+                        start = None
+                elif start is None:
+                    start = pos
+                pos += p.numel()
+            if start is not None:
+                runs.append((start, pos))
+            for lo, hi in runs:
+                sl = slice(lo, hi)
+                _lib.check(lib.grl_adam_step(self.flat_p[sl].data_ptr(), self.flat_g[sl].data_ptr(),
+                                             self.flat_m[sl].data_ptr(), self.flat_v[sl].data_ptr(), hi - lo,
+                                             float(g["lr"]), float(b1), float(b2), float(g["eps"]),
+                                             float(g["weight_decay"]), self._step, _lib.ptr(grad_norm), float(max_norm),
+                                             _lib.stream_ptr(self.flat_p.device)), "grl_adam_step")
+                _lib.count_launch(1)
+            off = pos
         if not self.state:
             self._publish_state()
         else:
@@ -270,6 +414,11 @@ class KVTrainStep:
         if isinstance(self.optimizer, FlatAdam) and self.optimizer._own_grad:
             # a factory-built FlatAdam: let it read the bucket directly instead of gathering p.grad every step
             self.optimizer.flat_g, self.optimizer._own_grad = self.bucket.flat, False
+        # data parallel: CE normalised by the valid-node count of the GLOBAL batch -> gradients are summed, not averaged
+        # (ragged batches: N-GPU gradients == 1-GPU gradients on the concatenated batch, SURVEY.md 8e "Check")
+        self.sum_gradients = isinstance(self.criterion, CrossEntropyLoss)
+        if self.sum_gradients:
+            self.criterion.global_mean = True
 
     def _to_device(self, batch_sample: Dict[str, torch.Tensor]) -> Tuple[list, torch.Tensor]:
         if "adjacency_matrix" not in batch_sample and "edges" in batch_sample:      # EdgeListCollate host batch
@@ -296,6 +445,7 @@ class KVTrainStep:
         self.bucket.zero()                       # optimizer.zero_grad() with grads kept as bucket views
         with torch.set_grad_enabled(True):
             loss, _ = self.step_process(batch_sample)
+            self.bucket.arm_overlap()
             loss.backward()
             self.clip_and_step()
         return loss.detach()
@@ -303,7 +453,7 @@ class KVTrainStep:
     def clip_and_step(self) -> torch.Tensor:
         """gradient all-reduce (N > 1) -> clip_grad_norm_ -> optimizer.step (kv_procedure.py:161-162); returns the
         gradient norm as a device scalar.  With FlatAdam the clip scaling is folded into the step kernel."""
-        self.bucket.all_reduce_mean()
+        self.bucket.all_reduce(average=not self.sum_gradients)
         if isinstance(self.optimizer, FlatAdam):
             total = self.bucket.norm()
             self.optimizer.step(grad_norm=total.reshape(1), max_norm=float(self.max_grad_norm))

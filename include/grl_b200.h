@@ -153,11 +153,10 @@ int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
                  const void* X, int64_t ldx, void* Y, int64_t ldy, int dtype,
                  int B, int N, int L, int F, void* stream);
 
-/* Kernel selection knob of grl_spmm_fwd (host call, process-global; experiments and tests):
- *   0 = auto,  -1 = node-per-warp gather kernel,  -2 = legacy row-per-warp gather kernel,
- *   8 / 16 / 32 = first-generation shared-memory slab kernel with that many lanes (of 16 bytes) per node group (falls
- *   back to the gather kernel when one graph's slab does not fit in shared memory);
- *   108 / 116 / 132 = force that group width in grl_spmm_fwd_stream (grl_spmm_fwd stays on auto). */
+/* Kernel selection knob (host call, process-global; experiments and tests):
+ *   0 = auto,  -1 = node-per-warp gather kernel,  -2 = legacy row-per-warp gather kernel (both steer grl_spmm_fwd);
+ *   108 / 116 / 132 = force 8 / 16 / 32 lanes (of 16 bytes) per node group in grl_spmm_fwd_stream, 208 / 216 = two 16-byte
+ *   words per lane (grl_spmm_fwd stays on auto). */
 int grl_spmm_set_tile_mode(int mode);
 
 /* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.
@@ -206,13 +205,6 @@ int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const void* B0_lo,
                 void* C, int64_t ldc, int out_dtype, int M, int N, int mode,
                 const float* bias, uint32_t flags, float p, const uint8_t* mask,
                 uint64_t seed, uint64_t stream_id, void* stream);
-/* C[M, N] (fp32) = gate > 0 ? (A[M, K] * B[N, K]^T) * gate_scale : 0 -- the gradient GEMM dY = dZ_next * W_next fused with
- * the ReLU / dropout derivative of the layer whose OUTPUT is `gate` (grl_bias_act_dropout_bwd's arithmetic applied while
- * the tile leaves the accumulator; replaces autograd's dY tensor + a pass over it for classifier -> w_rand,
- * drop_robust_gcn.py:100-103).  mode GRL_GEMM_TF32X3 (B_lo = grl_split_tf32 low part) or GRL_GEMM_TF32_BF16C (B_lo =
- * grl_split_tf32_mix packed operand).  Needs N % 64 == 0 and 16-byte aligned / pitched C and gate (GRL_E_UNSUP otherwise). */
-int grl_gemm_nt_gated(const void* A, int64_t lda, const void* B, const void* B_lo, int64_t ldb, int K, float* C, int64_t ldc,
-                      int M, int N, int mode, const float* gate, int64_t ld_gate, float gate_scale, void* stream);
 /* TF32X3 tuning knob (host call, process-global): K-blocks of 32 accumulated in TMEM before the partial sum is
  * promoted to fp32 registers; smaller = more accurate, more TMEM reads.  Default 2.  Negative values are experiment
  * switches with identical results: -3 (default) NT products take the activation operand through TMEM
@@ -298,10 +290,13 @@ int grl_selfatten_bwd(const void* dOut, const float* P, const float* o, const vo
 /* ------------------------------------------------------------------------------------------
  * Loss and optimizer of the KV train step (deterministic reductions; csrc/train_ops.cu).
  * workspace: grl_reduce_workspace_bytes() bytes of scratch for the block partial sums.
- * grl_ce_fwd:  loss_out[0] = sum_i w[y_i] (lse_i - x[i, y_i]) / sum_i w[y_i],  loss_out[1] = sum_i w[y_i] over the rows
- *              with y_i != ignore_index (w = 1 when weight == NULL); lse[i] saved for the backward.
+ * grl_ce_fwd:  loss_out is FOUR floats: [0] = sum_i w[y_i] (lse_i - x[i, y_i]) / sum_i w[y_i], [1] = sum_i w[y_i] over the
+ *              rows with y_i != ignore_index (w = 1 when weight == NULL), [2] = number of labels outside [0, C) that are
+ *              not ignore_index ([0] is NaN then: nn.CrossEntropyLoss raises on such targets), [3] = the numerator of
+ *              [0]; lse[i] saved for the backward.  No valid row: [0] = 0 and the backward writes zeros.
  *              Replaces nn.CrossEntropyLoss()(pred.transpose(1, 2), target)  gnn/trainer/losses/cross_entropy_loss.py:19-35.
- * grl_ce_bwd:  dlogits = grad_out[0] / loss_out[1] * w[y] * (softmax(x) - onehot(y)), 0 on ignored rows.
+ * grl_ce_bwd:  dlogits = grad_out[0] / loss_out[1] * w[y] * (softmax(x) - onehot(y)), 0 on ignored rows.  Data-parallel
+ *              callers pass the all-reduced sum of weights in loss_out[1] (mean over the GLOBAL batch's valid nodes).
  * grl_l2_norm: out[0] = ||x||_2 (the total norm of clip_grad_norm_  kv_procedure.py:161 over the flat gradient bucket).
  * grl_adam_step: torch.optim.Adam.step (amsgrad = False) over flat p / g / m / v of n floats at 1-based `step`;
  *              g is first multiplied by min(1, max_norm / (grad_norm[0] + 1e-6)) when grad_norm != NULL and

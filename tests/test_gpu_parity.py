@@ -119,7 +119,7 @@ def test_spmm_fwd_bwd_against_dense_matmul(dev, F, dtype):
 @pytest.mark.parametrize("B,N,F,density", [(3, 50, 256, 0.12), (5, 37, 128, 0.6), (2, 300, 64, 0.03), (4, 129, 512, 0.0),
                                            (2, 513, 256, 0.02)])
 def test_spmm_forward_kernels_agree_bit_for_bit(dev, dtype, B, N, F, density):
-    """gather (node-per-warp), legacy (row-per-warp) and the TMA-staged shared-memory slab kernels sum every typed row
+    """gather (node-per-warp), legacy (row-per-warp) and the TMA-staged shared-memory slab kernel sum every typed row
     in CSR order (dropped entries skipped), so they must agree exactly -- including nodes with more entries than one
     staged batch (density 0.6: the slab-v2 multi-batch path), rows longer than the register-staged 2*GL / 64 entries
     (density 0.6), empty typed rows (density 0), and N that is not a multiple of the TMA box."""
@@ -134,7 +134,7 @@ def test_spmm_forward_kernels_agree_bit_for_bit(dev, dtype, B, N, F, density):
         assert getattr(w, "_grl_stream", None) is not None
         outs = {}
         try:
-            for mode in (-2, -1, 8, 16, 32, 0, 108, 116, 132, 208, 216, 100):
+            for mode in (-2, -1, 0, 108, 116, 132, 208, 216, 100):
                 stream_kernel = mode >= 100              # node-stream slab kernel (100 = its own choice of group width)
                 ops._spmm_stream_enabled[0] = stream_kernel
                 _lib.check(lib.grl_spmm_set_tile_mode(0 if mode == 100 else mode), "grl_spmm_set_tile_mode")
@@ -633,23 +633,3 @@ def test_csr_pack_single_read_bitmap_equals_two_pass_pack(dev, B, N, L, dtype, d
     assert int(outs[1][0][-1]) == int((A.float() != 0).sum()) + B * N
 
 
-def test_projection_head_equals_two_layers(dev):
-    """ops.projection_head (w_rand -> ReLU -> dropout -> classifier as one autograd node, hidden gradient gated inside
-    the GEMM epilogue by grl_gemm_nt_gated) against the two separate layers: logits and every gradient bit for bit,
-    Philox dropout (same seed / stream) and a ragged node count (row tail of the last tile)."""
-    from graph_representation_learning_b200 import GraphCNNDropEdge, synthetic
-    wl = synthetic.Workload("head", 3, 171, input_dim=40, output_dim=53, net_size=256)
-    V, A, y = synthetic.make_batch(wl, 5, dev)
-    res = []
-    for fuse in (False, True):
-        torch.manual_seed(3)
-        model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size).to(dev).train()
-        model.fuse_head = fuse
-        model.rng_seed = 99
-        logits = model([V, A])
-        torch.nn.functional.cross_entropy(logits.transpose(1, 2), y).backward()
-        res.append((logits.detach().clone(), {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}))
-    assert torch.equal(res[0][0], res[1][0])
-    assert res[0][1].keys() == res[1][1].keys()
-    for k in res[0][1]:
-        assert torch.equal(res[0][1][k], res[1][1][k]), k

@@ -42,6 +42,7 @@ SIGNATURES = {
     "grl_csr_count_bitmap": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "grl_csr_fill_bitmap": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                     c_void_p]),
+    "grl_csr_clamp_rowptr": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "grl_csr_transpose": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),
     "grl_csr_transpose_general": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p,

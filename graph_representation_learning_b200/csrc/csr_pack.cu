@@ -485,6 +485,30 @@ extern "C" int grl_scan_inclusive_i32(int32_t* data, int64_t n, void* workspace,
     return 0;
 }
 
+// rowptr[r] = min(rowptr[r], capacity) for r in [0, R]; nnz_out[0] = the un-clamped entry count.  After this every
+// consumer of (rowptr, col, val) stays inside `capacity` slots whatever the batch holds; rows past the capacity come out
+// empty and nnz_out > capacity tells the host (graph.PackedGraphBatch reads it one step later, without a stall).
+namespace grl {
+__global__ void csr_clamp_rowptr_kernel(int32_t* __restrict__ rowptr, int64_t R, int32_t capacity, int32_t* __restrict__ nnz_out) {
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t r = tid; r <= R; r += stride) {
+        const int32_t v = rowptr[r];
+        if (r == R) nnz_out[0] = v;
+        if (v > capacity) rowptr[r] = capacity;
+    }
+}
+}  // namespace grl
+
+extern "C" int grl_csr_clamp_rowptr(int32_t* rowptr, int64_t R, int64_t capacity, int32_t* nnz_out, void* stream) {
+    GRL_CHECK_ARG(rowptr && nnz_out, GRL_E_BADARG, "grl_csr_clamp_rowptr: null pointer");
+    GRL_CHECK_ARG(R > 0 && capacity >= 0 && capacity < INT32_MAX, GRL_E_BADARG, "grl_csr_clamp_rowptr: bad shape");
+    csr_clamp_rowptr_kernel<<<grid_for(R + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        rowptr, R, static_cast<int32_t>(capacity), nnz_out);
+    GRL_LAUNCH_CHECK("csr_clamp_rowptr_kernel");
+    return 0;
+}
+
 extern "C" int grl_coo_count(const int32_t* edges, int64_t E, int B, int N, int L, int32_t* rowptr, void* stream) {
     GRL_CHECK_ARG(rowptr && (edges || E == 0), GRL_E_BADARG, "grl_coo_count: null pointer");
     GRL_CHECK_ARG(E == 0 || aligned_to(edges, 16), GRL_E_ALIGN, "grl_coo_count: edges must be 16-byte aligned");

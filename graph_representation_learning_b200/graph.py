@@ -14,11 +14,34 @@ All packing runs in the CUDA library (csrc/csr_pack.cu); nothing here touches th
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Optional
+from typing import Dict, Optional, Tuple
 
 import torch
 
 from . import _lib
+
+
+# Dense-adjacency packing without a per-batch host read (`rowptr[R].item()` serialised host and device in
+# every forward of the dense entry).  The first batch of a (B, N, L, device) signature is counted exactly (one read) and
+# fixes a slot capacity with 25 % head-room; later batches are packed into that capacity with clamped row pointers and
+# their true count is copied to pinned memory behind an event, which the NEXT pack of the signature inspects (the step
+# has long finished by then): a batch that did not fit raises there and the capacity grows.
+_dense_capacity: Dict[Tuple, int] = {}
+_dense_pending: Dict[Tuple, Tuple] = {}
+
+
+def _check_pending_overflow(key) -> None:
+    pend = _dense_pending.pop(key, None)
+    if pend is None:
+        return
+    ev, host, cap = pend
+    ev.synchronize()
+    true_nnz = int(host[0])
+    if true_nnz > cap:
+        _dense_capacity[key] = int(true_nnz * 1.25) + 1024
+        raise _lib.GrlError(f"the previous dense adjacency batch held {true_nnz} entries but was packed into {cap} slots "
+                            "(truncated); the capacity has been raised -- re-run the step, or pass nnz_capacity / use "
+                            "EdgeListCollate batches, whose entry count is known on the host")
 
 
 @dataclass
@@ -50,10 +73,13 @@ class PackedGraphBatch:
     # ------------------------------------------------------------------ builders
     @staticmethod
     def from_dense(adj: torch.Tensor, nnz_capacity: Optional[int] = None, with_transpose: bool = True,
-                   self_loop: bool = True) -> "PackedGraphBatch":
+                   self_loop: bool = True, sync_free: bool = False) -> "PackedGraphBatch":
         """Pack the collate's dense ``[B, N, L, N]`` adjacency (fp16 or fp32, layout [b, start, type, end]).
 
         ``nnz_capacity``: give an upper bound to skip the one host read of ``rowptr[R]``.
+        ``sync_free`` (what ``GraphCNNDropEdge.forward`` uses for dense inputs): only the first batch of a
+        ``(B, N, L)`` signature is counted on the host; later ones are packed into a remembered capacity (+25 %)
+        with clamped row pointers, and an overflow is reported by the next pack (see ``_check_pending_overflow``).
         ``self_loop=False``: ``adj`` is an already preprocessed ``A'`` viewed as ``[B, N, L+1, N]`` (its
         identity block, possibly DropEdge-masked, is taken as data).
         """
@@ -81,10 +107,32 @@ class PackedGraphBatch:
         _lib.check(lib.grl_scan_inclusive_i32(rowptr.data_ptr() + 4, R, ws.data_ptr(), ws_bytes, st),
                    "grl_scan_inclusive_i32")
         _lib.count_launch(2)
-        nnz = int(rowptr[-1].item()) if nnz_capacity is None else int(nnz_capacity)
+        exact = False
+        key = (B, N, T, sl, dev.index)
+        if nnz_capacity is None and sync_free and not torch.cuda.is_current_stream_capturing():
+            _check_pending_overflow(key)
+        cap = _dense_capacity.get(key) if (nnz_capacity is None and sync_free) else nnz_capacity
+        if cap is None:
+            nnz = int(rowptr[-1].item())                      # counted exactly: one host read
+            exact = True
+            if sync_free:                                     # first batch of this signature fixes the capacity
+                _dense_capacity[key] = int(nnz * 1.25) + 1024
+        elif nnz_capacity is not None:
+            nnz = int(nnz_capacity)
+        else:
+            nnz = int(cap)
+            nnz_dev = torch.empty(1, dtype=torch.int32, device=dev)
+            _lib.check(lib.grl_csr_clamp_rowptr(rowptr.data_ptr(), R, nnz, nnz_dev.data_ptr(), st), "grl_csr_clamp_rowptr")
+            _lib.count_launch(1)
+            if not torch.cuda.is_current_stream_capturing():
+                host = torch.empty(1, dtype=torch.int32, pin_memory=True)
+                host.copy_(nnz_dev, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                _dense_pending[key] = (ev, host, nnz)
         col = torch.empty(nnz, dtype=torch.int32, device=dev)
-        val = torch.zeros(nnz, dtype=torch.float32, device=dev) if nnz_capacity is not None else \
-            torch.empty(nnz, dtype=torch.float32, device=dev)
+        val = torch.empty(nnz, dtype=torch.float32, device=dev) if exact else \
+            torch.zeros(nnz, dtype=torch.float32, device=dev)
         _lib.check(lib.grl_csr_fill_bitmap(adj.data_ptr(), code, bitmap.data_ptr(), B, N, T, sl, rowptr.data_ptr(),
                                            col.data_ptr(), val.data_ptr(), st), "grl_csr_fill_bitmap")
         _lib.count_launch(1)

@@ -85,6 +85,12 @@ int grl_csr_count_bitmap(const void* adj, int adj_dtype, int B, int N, int L, in
 int grl_csr_fill_bitmap(const void* adj, int adj_dtype, const void* bitmap, int B, int N, int L, int self_loop,
                         const int32_t* rowptr, int32_t* col, float* val, void* stream);
 
+/* Capacity-bounded packing without a host read of the entry count: after the scan, clamp every row pointer to `capacity`
+ * (the slots the caller allocated for col / val) and leave the true count in nnz_out[0] (device int32).  Rows that would
+ * start past the capacity come out empty; nnz_out[0] > capacity means the batch was truncated (the caller checks it
+ * asynchronously).  Replaces the .item() of the dense path's `rowptr[R]`. */
+int grl_csr_clamp_rowptr(int32_t* rowptr, int64_t R, int64_t capacity, int32_t* nnz_out, void* stream);
+
 /* CSR pack from an edge list (COO).  Replaces the dense N x L x N intermediate written by
  * Graph -> adj[start, label, end] = 1 (gnn/data_generator/data_process/utils/graph_utils.py:821-829)
  * followed by NumpyPadding (gnn/data_generator/data_collate/numpy_padding.py:63-103).

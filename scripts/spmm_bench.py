@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """A/B timing of the forward / transposed SpMM kernels (grl_spmm_set_tile_mode) on one workload shape.
-Usage: python scripts/spmm_bench.py [--B 256 --N 500 --F 256 --dtype f32 --modes 0,-1,-2,4,8,16]
+Usage: python scripts/spmm_bench.py [--B 256 --N 500 --F 256 --dtype f32 --modes -2,-1,116,100]
 Every mode is checked against the legacy row kernel (bit-for-bit for fp32: same per-row summation order)."""
 import argparse
 import json
@@ -20,7 +20,7 @@ def main():
     ap.add_argument("--F", type=int, default=256)
     ap.add_argument("--degree", type=float, default=8.0)
     ap.add_argument("--dtype", default="f32")
-    ap.add_argument("--modes", default="-2,-1,16,100")
+    ap.add_argument("--modes", default="-2,-1,116,100")
     ap.add_argument("--iters", type=int, default=20)
     args = ap.parse_args()
     dev = torch.device("cuda:0")

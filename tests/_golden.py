@@ -31,3 +31,35 @@ def rel_err(x, ref):
     """norm-wise relative error against a reference tensor (SURVEY.md 8c tolerance definition)."""
     x, ref = x.double().reshape(-1), ref.double().reshape(-1)
     return float((x - ref).norm() / ref.norm().clamp_min(1e-30))
+
+
+PRODUCTION_CASES = ["prod_cfg1", "prod_s512"]
+
+
+def load_production_case(name):
+    """Production-shape vectors of the unmodified reference (oracle/make_golden.py production): fp64 outputs, the
+    reference's own fp32-vs-fp64 noise per tensor, inputs regenerated from the seed (oracle/golden_inputs.py)."""
+    from oracle.golden_inputs import production_inputs, sample_index
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    case = {"meta": meta, "err_ref32": json.loads(str(z["err_ref32"])),
+            "weights_check": json.loads(str(z["weights_check"]))}
+    for k in ("logits_eval", "logits_train", "loss"):
+        case[k] = torch.from_numpy(z[k])
+    case["grad"] = {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith("grad/")}
+    case.update(production_inputs(meta))
+    case["sample_index"] = lambda key, numel: sample_index(key, numel, meta["seed"])
+    return case
+
+
+def check_weights(model, case):
+    """same seed -> same initial weights as the reference constructor (sum / abs-sum per tensor of the golden file)"""
+    for k, v in model.state_dict().items():
+        s, a = case["weights_check"][k]
+        v = v.double()
+        assert abs(float(v.sum()) - s) <= 1e-9 * max(1.0, a) and abs(float(v.abs().sum()) - a) <= 1e-9 * max(1.0, a), k
+
+
+def allowed(case, key, floor):
+    """our norm-wise error against the fp64 reference may be max(floor, 2 x the reference's own fp32 noise)"""
+    return max(floor, 2.0 * case["err_ref32"][key])

@@ -10,7 +10,8 @@ import numpy as np
 import pytest
 import torch
 
-from _golden import GOLDEN, MODEL_CASES, load_model_case, rel_err
+from _golden import (GOLDEN, MODEL_CASES, PRODUCTION_CASES, allowed, check_weights, load_model_case,
+                     load_production_case, rel_err)
 from oracle import reference_port as rp
 
 pytestmark = pytest.mark.gpu
@@ -265,7 +266,68 @@ def test_model_bf16_within_stated_tolerance(dev):
     with torch.no_grad():
         out = model([c["V"].to(dev), c["A"].to(dev)])
     assert out.dtype == torch.float32
-    assert rel_err(out.cpu(), c["logits_eval"]) < 3 * TOL_BF16   # 8 chained bf16 layers; per-op tolerance is 1e-2
+    assert rel_err(out.cpu(), c["logits_eval"]) < TOL_BF16
+
+
+def _production_errors(dev, name, dtype):
+    """CUDA model (same seed -> the reference constructor's weights, checked) on the regenerated inputs and injected masks
+    of a production-shape case; returns {tensor: (our norm-wise error vs the reference's fp64 run, the reference's own
+    fp32 noise)} for eval logits, train logits, loss and every gradient (at the stored sample positions)."""
+    from graph_representation_learning_b200 import GraphCNNDropEdge, PackedGraphBatch
+    c = load_production_case(name)
+    m = c["meta"]
+    B, N = m["B"], m["N"]
+    torch.manual_seed(m["seed"])
+    model = GraphCNNDropEdge(m["in_dim"], m["out_dim"], m["L"], net_size=m["S"])
+    check_weights(model, c)
+    model = model.to(dev).set_compute_dtype(dtype)
+    V, A, y = c["V"].to(dev), c["A"].to(dev), c["y"].to(dev)
+    errs = {}
+    model.eval()
+    with torch.no_grad():
+        errs["logits_eval"] = rel_err(model([V, A]).cpu(), c["logits_eval"])
+    model.train()
+    g = PackedGraphBatch.from_dense(A)
+    masks = {"edge": [g.gather_dense_mask(x.to(dev)) for x in c["edge_masks"]],
+             "feat": [x.to(dev).reshape(B * N, -1).contiguous() for x in c["feat_masks"]]}
+    logits = model([V, g], masks=masks)
+    loss = torch.nn.functional.cross_entropy(logits.transpose(1, 2), y)
+    loss.backward()
+    errs["logits_train"] = rel_err(logits.detach().cpu(), c["logits_train"])
+    errs["loss"] = abs(float(loss) - float(c["loss"])) / float(c["loss"])
+    for k, p in model.named_parameters():
+        if p.requires_grad:
+            idx = c["sample_index"](k, p.numel())
+            errs["grad/" + k] = rel_err(p.grad.reshape(-1).cpu()[idx], c["grad"][k])
+    table = {k: (v, c["err_ref32"][k]) for k, v in errs.items()}
+    out_dir = os.path.join(os.path.dirname(GOLDEN), "..", "gpurun_out")
+    try:                                              # the per-tensor table of DESIGN.md section 2 comes from here
+        os.makedirs(out_dir, exist_ok=True)
+        import json
+        with open(os.path.join(out_dir, f"parity_{name}_{'f32' if dtype == torch.float32 else 'bf16'}.json"), "w") as f:
+            json.dump({k: {"ours": a, "ref_fp32": b} for k, (a, b) in table.items()}, f, indent=1)
+    except OSError:
+        pass
+    return c, table
+
+
+@pytest.mark.parametrize("name", PRODUCTION_CASES)
+def test_production_shape_fp32_against_reference_fp64_run(dev, name):
+    """cfg1 EXACTLY (8 x 200, in_dim 4369, S=256: tiled attention (128,16), K=4369 emb1, long-K promoted accumulators,
+    200-node slabs) and an S=512 case (attention (256,32), K=7168), fp32, against vectors of the unmodified reference.
+    Tolerance per tensor: max(1e-5, 2 x the reference's own fp32-vs-fp64 noise on that tensor)."""
+    c, table = _production_errors(dev, name, torch.float32)
+    bad = {k: (ours, allowed(c, k, TOL_OUT)) for k, (ours, _) in table.items() if not ours < allowed(c, k, TOL_OUT)}
+    assert not bad, f"(ours, allowed): {bad}"
+
+
+@pytest.mark.parametrize("name", PRODUCTION_CASES)
+def test_production_shape_bf16_train_step(dev, name):
+    """bf16 activations (cfg3's dtype), fp32 master weights: logits and EVERY gradient within the stated 1e-2 (or twice
+    the reference's own fp32 noise where that is larger) of the reference's fp64 run."""
+    c, table = _production_errors(dev, name, torch.bfloat16)
+    bad = {k: (ours, allowed(c, k, TOL_BF16)) for k, (ours, _) in table.items() if not ours < allowed(c, k, TOL_BF16)}
+    assert not bad, f"(ours, allowed): {bad}"
 
 
 def _medium_case_errors(dev, seed):
@@ -633,3 +695,56 @@ def test_csr_pack_single_read_bitmap_equals_two_pass_pack(dev, B, N, L, dtype, d
     assert int(outs[1][0][-1]) == int((A.float() != 0).sum()) + B * N
 
 
+
+
+# ---------------------------------------------------------------------------------------- advisor findings (round 1)
+@pytest.mark.parametrize("L", [30, 31, 45])
+def test_aggregation_with_many_edge_types(dev, L):
+    """dropedge_stream_kernel keeps a node's L + 2 row pointers one per lane, so it serves L + 1 <= 31; wider models go
+    through grl_dropedge_weights + the gather kernels.  Both sides of the boundary against the dense matmul."""
+    from graph_representation_learning_b200 import PackedGraphBatch, ops
+    gen = torch.Generator().manual_seed(L)
+    B, N, F = 2, 40, 64
+    A = (torch.rand(B, N, L, N, generator=gen) < 0.1).float()
+    Ap = rp.preprocess_adj(A.permute(0, 1, 3, 2))
+    keep = torch.rand(Ap.shape, generator=gen) < 0.7
+    X = torch.randn(B, N, F, generator=gen)
+    dY = torch.randn(B * N, (L + 1) * F, generator=gen)
+    ref_Y = torch.matmul((Ap * keep / 0.7).double(), X.double()).reshape(B * N, (L + 1) * F)
+    ref_dX = torch.matmul((Ap * keep / 0.7).double().transpose(1, 2), dY.double().reshape(B, N * (L + 1), F)).reshape(B * N, F)
+    g = PackedGraphBatch.from_dense(A.to(dev))
+    w = g.edge_weights(0.3, mask=g.gather_dense_mask(keep.to(dev)))
+    assert (getattr(w, "_grl_stream", None) is not None) == (L + 1 <= 31)
+    Xd = X.reshape(B * N, F).to(dev).requires_grad_(True)
+    Y = ops.spmm_aggregate(g, w, [Xd])
+    Y.backward(dY.to(dev))
+    assert rel_err(Y.detach().cpu(), ref_Y) < TOL_OUT and rel_err(Xd.grad.cpu(), ref_dX) < TOL_OUT
+    # the Philox path writes every weight, too
+    w2 = g.edge_weights(0.3, seed=9, stream_id=2)
+    assert bool(torch.isfinite(w2).all()) and set(torch.unique(w2 * 0.7).round(decimals=4).tolist()) <= {0.0, 1.0}
+
+
+def test_edge_list_duplicates_and_out_of_range_entries(dev):
+    """Repeated (b, i, l, j) triples aggregate like the reference's idempotent dense build adj[start, label, end] = 1
+    (graph_utils.py:821-829); triples outside the batch are neutralised on the device (no out-of-bounds write) and
+    rejected by the host collate."""
+    from graph_representation_learning_b200 import PackedGraphBatch, ops
+    from graph_representation_learning_b200.collate import EdgeListCollate
+    gen = torch.Generator().manual_seed(3)
+    B, N, L, F = 2, 20, 6, 32
+    A = (torch.rand(B, N, L, N, generator=gen) < 0.15).float()
+    edges = A.nonzero().to(torch.int32)
+    dup = torch.cat([edges, edges[::3], edges[::5]])[torch.randperm(edges.shape[0] + len(edges[::3]) + len(edges[::5]), generator=gen)]
+    bad = torch.tensor([[0, N, 0, 1], [B, 0, 0, 0], [0, 1, L, 2], [1, 2, 3, -1]], dtype=torch.int32)
+    X = torch.randn(B * N, F, generator=gen).to(dev)
+    gd = PackedGraphBatch.from_dense(A.to(dev))
+    ge = PackedGraphBatch.from_edges(torch.cat([dup, bad]).to(dev), B, N, L)
+    assert ge.nnz == dup.shape[0] + 4 + B * N
+    Yd = ops.spmm_aggregate(gd, gd.edge_weights(0.0), [X])
+    Ye = ops.spmm_aggregate(ge, ge.edge_weights(0.0), [X])
+    assert torch.equal(Yd, Ye)
+    assert torch.equal(ge.to_dense().cpu(), rp.preprocess_adj(A.permute(0, 1, 3, 2)))
+    sample = {"textline_encoding": np.zeros((5, 4), np.float32), "node_label": np.zeros(5, np.int64),
+              "edges": np.array([[0, 0, 5]], np.int32)}
+    with pytest.raises(ValueError):
+        EdgeListCollate(num_edges=L, pin_memory=False)([sample])

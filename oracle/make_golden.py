@@ -336,18 +336,27 @@ def deep_rp_gcn_case(name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0):
     print(f"{name}: loss {float(loss):.6f}")
 
 
-def production_case(GraphCNNDropEdge, name, seed, B, N, in_dim, S, out_dim, L=6, deg=8.0):
+def production_case(GraphCNNDropEdge, name, seed, B, N, in_dim, S, out_dim, L=6, deg=8.0, w_rand_scale=None):
     """Production-shape vectors: the UNMODIFIED reference run in fp64 (the truth every tensor is judged
     against) and in fp32 (its own rounding noise, stored as one norm-wise number per tensor: SURVEY.md 8c's
     ``max(1e-5, 2 * err_ref32)`` rule).  Inputs / masks are NOT stored: ``oracle/golden_inputs.production_inputs``
-    regenerates them from the seed.  Gradient tensors above 65 536 elements keep 32 768 seeded sample positions."""
+    regenerates them from the seed.  Gradient tensors above 65 536 elements keep 32 768 seeded sample positions.
+
+    ``w_rand_scale``: the frozen N(0,1) projection (drop_robust_gcn.py:20-25) is multiplied by this factor in the state
+    dict of BOTH sides.  At its initial scale the logits are O(300) and the cross entropy is saturated (loss ~ 4e2): the
+    gradient then hinges on which class wins at each node and is chaotic in the last bits -- the reference's own fp32 run
+    is 3-6e-3 away from its fp64 run at cfg1.  The "tame" cases (scale 0.005, logits O(1)) are the well-conditioned
+    check of the same kernels at the same shapes (fp32 at ~1e-5, bf16 at 1e-2)."""
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
     from oracle.golden_inputs import production_inputs, sample_index
-    meta = dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed, deg=deg, use_attention=True)
+    meta = dict(B=B, N=N, in_dim=in_dim, S=S, out_dim=out_dim, L=L, seed=seed, deg=deg, use_attention=True,
+                w_rand_scale=w_rand_scale)
     inp = production_inputs(meta)
     torch.manual_seed(seed)
     model32 = GraphCNNDropEdge(in_dim, out_dim, L, net_size=S)
     sd0 = {k: v.detach().clone() for k, v in model32.state_dict().items()}
+    if w_rand_scale is not None:
+        sd0["w_rand.projection.weight"] = sd0["w_rand.projection.weight"] * w_rand_scale
 
     def run(dtype):
         torch.manual_seed(seed)
@@ -393,6 +402,10 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "production":       # cfg1 exactly + one S=512 case (no stored inputs)
         production_case(GraphCNNDropEdge, "prod_cfg1", seed=41, B=8, N=200, in_dim=4369, S=256, out_dim=53)
         production_case(GraphCNNDropEdge, "prod_s512", seed=42, B=2, N=300, in_dim=600, S=512, out_dim=53)
+        production_case(GraphCNNDropEdge, "prod_cfg1_tame", seed=43, B=8, N=200, in_dim=4369, S=256, out_dim=53,
+                        w_rand_scale=0.005)
+        production_case(GraphCNNDropEdge, "prod_s512_tame", seed=44, B=2, N=300, in_dim=600, S=512, out_dim=53,
+                        w_rand_scale=0.005)
         return
     if len(sys.argv) > 1 and sys.argv[1] == "robust_gcn":       # add the sibling-model vectors without touching the rest
         robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)

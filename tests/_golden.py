@@ -33,7 +33,8 @@ def rel_err(x, ref):
     return float((x - ref).norm() / ref.norm().clamp_min(1e-30))
 
 
-PRODUCTION_CASES = ["prod_cfg1", "prod_s512"]
+PRODUCTION_CASES = ["prod_cfg1", "prod_s512", "prod_cfg1_tame", "prod_s512_tame"]
+TAME_CASES = ["prod_cfg1_tame", "prod_s512_tame"]      # w_rand scaled to 0.005: logits O(1), CE not saturated
 
 
 def load_production_case(name):
@@ -50,6 +51,20 @@ def load_production_case(name):
     case.update(production_inputs(meta))
     case["sample_index"] = lambda key, numel: sample_index(key, numel, meta["seed"])
     return case
+
+
+def production_model(case):
+    """``GraphCNNDropEdge`` built under the case's seed (= the reference constructor's weights, verified against the
+    stored checksums), with the frozen projection rescaled when the case says so."""
+    from graph_representation_learning_b200 import GraphCNNDropEdge
+    m = case["meta"]
+    torch.manual_seed(m["seed"])
+    model = GraphCNNDropEdge(m["in_dim"], m["out_dim"], m["L"], net_size=m["S"])
+    if m.get("w_rand_scale") is not None:
+        with torch.no_grad():
+            model.w_rand.projection.weight.mul_(m["w_rand_scale"])
+    check_weights(model, case)
+    return model
 
 
 def check_weights(model, case):

@@ -77,17 +77,13 @@ def test_against_live_reference():
     assert rel_err(out, ref) < TOL
 
 
-@pytest.mark.parametrize("name", ["prod_cfg1", "prod_s512"])
+@pytest.mark.parametrize("name", ["prod_cfg1", "prod_s512", "prod_cfg1_tame", "prod_s512_tame"])
 def test_port_matches_reference_fp64_run_at_production_shapes(name):
     """cfg1 exactly (8 x 200, in_dim 4369, S=256) and an S=512 case: the port in fp64, fed the regenerated inputs and
     masks, against the fp64 run of the unmodified reference (logits, loss, every gradient at the stored positions)."""
-    from _golden import check_weights, load_production_case
-    from graph_representation_learning_b200 import GraphCNNDropEdge
+    from _golden import load_production_case, production_model
     c = load_production_case(name)
-    m = c["meta"]
-    torch.manual_seed(m["seed"])
-    model = GraphCNNDropEdge(m["in_dim"], m["out_dim"], m["L"], net_size=m["S"])
-    check_weights(model, c)                                  # same seed -> the reference constructor's weights
+    model = production_model(c)                              # same seed -> the reference constructor's weights (checked)
     sd = {k: v.detach().double() for k, v in model.state_dict().items()}
     V, A = c["V"].double(), c["A"].double()
     assert rel_err(rp.forward(sd, V, A, training=False), c["logits_eval"]) < 1e-12

@@ -66,6 +66,14 @@ SIGNATURES = {
     "grl_selfatten_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_void_p]),
+    "grl_selfatten_tc_pieces": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "grl_attn_split": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "grl_selfatten_tc_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "grl_selfatten_tc_prep_blocks": (c_size_t, [c_int64]),
+    "grl_selfatten_tc_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                     c_int, c_int, c_void_p]),
     "grl_reduce_workspace_bytes": (c_size_t, []),
     "grl_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p,
                            c_void_p]),

@@ -41,7 +41,6 @@ struct BcCfg {
 };
 static_assert(BcCfg::SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
-__device__ __forceinline__ uint32_t tf32_rn_bits(uint32_t u) { return (u + 0x1000u) & 0xFFFFE000u; }
 __device__ __forceinline__ uint32_t pack_bf16x2(float first, float second) {   // `first` at the lower address
     const __nv_bfloat162 v = __floats2bfloat162_rn(first, second);
     return *reinterpret_cast<const uint32_t*>(&v);
@@ -257,12 +256,12 @@ gemm_bc_kernel(const GemmParams p, const int promo, const int kb_per_split, cons
                         float lo[4];
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
-                            hi[4 * c + e] = kX3 ? (w[e] & 0xFFFFE000u) : tf32_rn_bits(w[e]);
+                            hi[4 * c + e] = tf32_rn_bits(w[e]);
                             lo[e] = __uint_as_float(w[e]) - __uint_as_float(hi[4 * c + e]);
                         }
                         if constexpr (kX3) {
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) pk[4 * c + e] = __float_as_uint(lo[e]);
+                            for (int e = 0; e < 4; ++e) pk[4 * c + e] = tf32_rn_bits(__float_as_uint(lo[e]));
                             continue;
                         }
                         // packed chunk c = {lo[4c..4c+3], hi[4c..4c+3]} against B' chunk c = {b_hi[4c..], b_lo[4c..]}

@@ -484,9 +484,9 @@ __global__ void split_tf32_kernel(const float* __restrict__ src, int64_t ld_src,
         const int64_t r = t / cols;
         const int c = static_cast<int>(t - r * cols);
         const float v = src[r * ld_src + c];
-        const float h = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+        const float h = __uint_as_float(tf32_rn_bits(__float_as_uint(v)));
         hi[r * ld_dst + c] = h;
-        lo[r * ld_dst + c] = v - h;
+        lo[r * ld_dst + c] = __uint_as_float(tf32_rn_bits(__float_as_uint(v - h)));
     }
 }
 

@@ -38,13 +38,14 @@ __device__ __forceinline__ void split_tile(uint8_t* raw, uint8_t* lo_tile, int t
     for (int i = 0; i < X3Cfg::TILE_BYTES / 16 / 128; ++i) {
         const int idx = i * 128 + tid;
         const uint4 v = a[idx];
-        const uint4 hi = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
+        const uint4 hi = make_uint4(tf32_rn_bits(v.x), tf32_rn_bits(v.y), tf32_rn_bits(v.z), tf32_rn_bits(v.w));
         uint4 lo;
-        lo.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x));
-        lo.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y));
-        lo.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z));
-        lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
-        if (!raw_hi) a[idx] = hi;
+        lo.x = tf32_rn_bits(__float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x)));
+        lo.y = tf32_rn_bits(__float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y)));
+        lo.z = tf32_rn_bits(__float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z)));
+        lo.w = tf32_rn_bits(__float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w)));
+        (void)raw_hi;                  // hi is ROUNDED now: the raw tile can no longer stand in for it
+        a[idx] = hi;
         alo[idx] = lo;
     }
 }

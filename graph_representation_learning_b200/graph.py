@@ -22,12 +22,20 @@ from . import _lib
 
 
 # Dense-adjacency packing without a per-batch host read (`rowptr[R].item()` serialised host and device in
-# every forward of the dense entry).  The first batch of a (B, N, L, device) signature is counted exactly (one read) and
-# fixes a slot capacity with 25 % head-room; later batches are packed into that capacity with clamped row pointers and
-# their true count is copied to pinned memory behind an event, which the NEXT pack of the signature inspects (the step
-# has long finished by then): a batch that did not fit raises there and the capacity grows.
+# every training forward of the dense entry).  Training forwards only (eval packs exactly: its result goes to the host
+# anyway).  The first batch of a (B, N, L, device) signature is counted exactly (one read) and fixes a slot capacity with
+# 25 % head-room; later batches are packed into that capacity with clamped row pointers and their true count is copied
+# to pinned memory behind an event.  ``check_dense_overflow()`` -- called by ``KVTrainStep`` between backward and the
+# optimizer step, when that early event has long fired, and by the next pack of the signature -- raises if a batch did
+# not fit (and grows the capacity), so a truncated batch never reaches the weights.
 _dense_capacity: Dict[Tuple, int] = {}
 _dense_pending: Dict[Tuple, Tuple] = {}
+
+
+def check_dense_overflow() -> None:
+    """raise if any sync-free dense pack since the last call was truncated (see above); cheap when nothing is pending"""
+    for key in list(_dense_pending):
+        _check_pending_overflow(key)
 
 
 def _check_pending_overflow(key) -> None:

@@ -214,7 +214,7 @@ class GraphCNNDropEdge(BaseNetwork):
         sparse_v = isinstance(V, SparseNodeFeatures)
         _lib.require_cuda(V.val if sparse_v else V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=True)
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -303,7 +303,7 @@ class RobustGCN(BaseNetwork):
         V, A = inputs
         _lib.require_cuda(V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=True)
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -370,7 +370,7 @@ class RPGraphCNNDropEdge(BaseNetwork):
         sparse_v = isinstance(V, SparseNodeFeatures)
         _lib.require_cuda(V.val if sparse_v else V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=True)
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -470,7 +470,7 @@ class DeepRPRobustGCN(BaseNetwork):
         V, A = inputs
         _lib.require_cuda(V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=True)
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -549,7 +549,7 @@ class DeepRPGCN(BaseNetwork):
         V, A = inputs
         _lib.require_cuda(V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=True)
+        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")

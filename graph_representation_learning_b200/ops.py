@@ -534,6 +534,93 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
     return linear_act([new_v], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
 
 
+class AttentionConfig:
+    """``tensor_cores``: NodeSelfAtten on the tcgen05 kernels of csrc/attention_tc.cu where they are instantiated --
+    (fp32, H=128, d=16), (bf16, 128, 16), (bf16, 256, 32) -- and, for fp32, while the graph has at most
+    ``max_nodes_fp32`` nodes (one TMEM accumulator over all keys: its truncating adds cost ~1.5e-8 per 16 keys and
+    product, 3e-6 at 500 nodes).  Everything else runs the fp32 FFMA kernels of csrc/attention.cu."""
+    tensor_cores = True
+    max_nodes_fp32 = 2048
+
+
+def _tc_pieces(dtype: torch.dtype, H: int, D: int):
+    import ctypes
+    a, b, c = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+    ok = _lib.load().grl_selfatten_tc_pieces(_DTYPE_CODE[dtype], H, D, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+    return (a.value, b.value, c.value) if ok == 1 else None
+
+
+_DTYPE_CODE = {torch.float32: _lib.GRL_F32, torch.bfloat16: _lib.GRL_BF16}
+
+
+def _split_pieces(x: torch.Tensor, np_: int) -> torch.Tensor:
+    """[rows, C] -> bf16 [np, rows, C] (csrc/attention_tc.cu grl_attn_split); a contiguous bf16 x with np = 1 is itself"""
+    rows, C = x.shape
+    if np_ == 1 and x.dtype == torch.bfloat16 and x.is_contiguous():
+        return x.view(1, rows, C)
+    out = torch.empty(np_, rows, C, dtype=torch.bfloat16, device=x.device)
+    _lib.check(_lib.load().grl_attn_split(x.data_ptr(), _row_major_2d(x, "x"), _lib.dtype_code(x), rows, C, 0, np_,
+                                          out.data_ptr(), _lib.stream_ptr(x.device)), "grl_attn_split")
+    _lib.count_launch(1)
+    return out
+
+
+class _SelfAttentionTC(torch.autograd.Function):
+    """gamma * (softmax(f g^T) h) + V per graph on the tensor cores (csrc/attention_tc.cu); saves o, the row max and the
+    row sum (3 floats x N per graph) instead of the N x N probabilities."""
+
+    @staticmethod
+    def forward(ctx, f, g, h, gamma, V, pieces):
+        B, N, H = h.shape
+        D = f.shape[2]
+        np_f, nps_b, np_b = pieces
+        Nt = B * N
+        f2, g2, h2 = f.reshape(Nt, D), g.reshape(Nt, D), h.reshape(Nt, H)
+        V = V.contiguous()
+        gam = gamma.detach().float().contiguous()
+        fp, gp, hp = _split_pieces(f2, np_f), _split_pieces(g2, np_f), _split_pieces(h2, np_f)
+        out = torch.empty_like(V)
+        need_grad = any(ctx.needs_input_grad)
+        o = torch.empty(Nt, H, dtype=torch.float32, device=V.device) if need_grad else None
+        m = torch.empty(Nt, dtype=torch.float32, device=V.device) if need_grad else None
+        l = torch.empty(Nt, dtype=torch.float32, device=V.device) if need_grad else None
+        _lib.check(_lib.load().grl_selfatten_tc_fwd(fp.data_ptr(), gp.data_ptr(), hp.data_ptr(), V.data_ptr(),
+                                                    gam.data_ptr(), out.data_ptr(), _lib.ptr(o), _lib.ptr(m), _lib.ptr(l),
+                                                    _lib.dtype_code(V), B, N, H, D, _lib.stream_ptr(V.device)),
+                   "grl_selfatten_tc_fwd")
+        _lib.count_launch(1)
+        if need_grad:
+            # the backward reads prefixes of the forward's pieces (the first k pieces of a 3-way split ARE the k-way split)
+            ctx.save_for_backward(fp, gp, hp, gam, o, m, l)
+            ctx.shape = (B, N, H, D, f.dtype)
+            ctx.pieces = pieces
+        return out
+
+    @staticmethod
+    def backward(ctx, dOut):
+        fp, gp, hp, gam, o, m, l = ctx.saved_tensors
+        B, N, H, D, dt = ctx.shape
+        np_f, nps_b, np_b = ctx.pieces
+        Nt = B * N
+        lib = _lib.load()
+        dOut = dOut.contiguous()
+        dev = dOut.device
+        # the kernels index pieces as [np][Nt, C]: with fewer pieces than the forward saved, the leading ones are used
+        do_p = torch.empty(np_b, Nt, H, dtype=torch.bfloat16, device=dev)
+        Dvec = torch.empty(Nt, dtype=torch.float32, device=dev)
+        part = torch.empty(lib.grl_selfatten_tc_prep_blocks(Nt), H, dtype=torch.float32, device=dev)
+        df = torch.empty(B, N, D, dtype=dt, device=dev)
+        dg = torch.empty(B, N, D, dtype=dt, device=dev)
+        dh = torch.empty(B, N, H, dtype=dt, device=dev)
+        _lib.check(lib.grl_selfatten_tc_bwd(dOut.data_ptr(), o.data_ptr(), m.data_ptr(), l.data_ptr(), fp.data_ptr(),
+                                            gp.data_ptr(), hp.data_ptr(), gam.data_ptr(), do_p.data_ptr(), Dvec.data_ptr(),
+                                            part.data_ptr(), df.data_ptr(), dg.data_ptr(), dh.data_ptr(),
+                                            _DTYPE_CODE[dt], B, N, H, D, _lib.stream_ptr(dev)), "grl_selfatten_tc_bwd")
+        _lib.count_launch(3)
+        dgamma = colsum(part)
+        return df, dg, dh, dgamma, dOut, None
+
+
 class _SelfAttention(torch.autograd.Function):
     """gamma * (softmax(f g^T) h) + V per graph (csrc/attention.cu).  f, g: [B, N, d]; h, V: [B, N, H]."""
 
@@ -580,5 +667,13 @@ class _SelfAttention(torch.autograd.Function):
 def self_attention(f_out: torch.Tensor, g_out: torch.Tensor, h_out: torch.Tensor, gamma: torch.Tensor,
                    V: torch.Tensor) -> torch.Tensor:
     """NodeSelfAtten core (reference robust_gcn.py:94-96): gamma * (softmax(f g^T) h) + V, per graph,
-    unscaled and unmasked, on the tiled fp32 kernels of csrc/attention.cu (eval never writes an N x N tensor)."""
+    unscaled and unmasked.  Tensor-core kernels (csrc/attention_tc.cu) where instantiated, else the tiled fp32 kernels of
+    csrc/attention.cu; neither writes an N x N tensor in eval, the tensor-core path not in training either."""
+    B, N, H = h_out.shape
+    D = f_out.shape[2]
+    if (AttentionConfig.tensor_cores and V.dtype in _DTYPE_CODE and f_out.dtype == V.dtype and g_out.dtype == V.dtype and
+            h_out.dtype == V.dtype and (V.dtype == torch.bfloat16 or N <= AttentionConfig.max_nodes_fp32)):
+        pieces = _tc_pieces(V.dtype, H, D)
+        if pieces is not None:
+            return _SelfAttentionTC.apply(f_out, g_out, h_out, gamma, V, pieces)
     return _SelfAttention.apply(f_out, g_out, h_out, gamma, V)

@@ -453,6 +453,9 @@ class KVTrainStep:
     def clip_and_step(self) -> torch.Tensor:
         """gradient all-reduce (N > 1) -> clip_grad_norm_ -> optimizer.step (kv_procedure.py:161-162); returns the
         gradient norm as a device scalar.  With FlatAdam the clip scaling is folded into the step kernel."""
+        if self.device.type == "cuda":
+            from .graph import check_dense_overflow
+            check_dense_overflow()               # a truncated sync-free dense pack must not reach the weights
         self.bucket.all_reduce(average=not self.sum_gradients)
         if isinstance(self.optimizer, FlatAdam):
             total = self.bucket.norm()

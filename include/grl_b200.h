@@ -271,7 +271,7 @@ int grl_bn_act_bwd(const float* dY, int64_t lddy, const float* Y, int64_t ldy, c
  * {hi[4c..4c+3], lo[4c..4c+3]} with lo = src - hi; entries past cols are zero. */
 int grl_split_tf32_mix(const float* src, int64_t ld_src, float* hi, int64_t ld_hi, void* packed, int64_t ld_packed,
                        int64_t rows, int cols, void* stream);
-/* hi = src with the 13 low mantissa bits cleared (exactly representable in tf32), lo = src - hi. */
+/* hi = src rounded to the nearest tf32 (10 explicit mantissa bits), lo = (src - hi) rounded to the nearest tf32. */
 int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst,
                    int64_t rows, int cols, void* stream);
 
@@ -292,6 +292,34 @@ int grl_selfatten_fwd(const void* f, const void* g, const void* h, const void* V
 int grl_selfatten_bwd(const void* dOut, const float* P, const float* o, const void* f, const void* g, const void* h,
                       const float* gamma, float* dS, void* df, void* dg, void* dh, float* dgamma_part,
                       int dtype, int B, int N, int H, int D, int Np, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * The same NodeSelfAtten core on the tensor cores, flash style (csrc/attention_tc.cu): kind::f16 tcgen05 MMAs on bf16
+ * operand PIECES (x = x0 + x1 + x2, x0 = bf16(x), x1 = bf16(x - x0), ...; fp32 models use 3 pieces = 6 products in the
+ * forward, 2 pieces = 3 products in the H-wide backward products; bf16 models 1), accumulators in TMEM, nothing of size
+ * N x N in HBM in either direction.  Replaces robust_gcn.py:94-96 and its autograd like grl_selfatten_fwd / _bwd.
+ *   grl_selfatten_tc_pieces   1 when (io_dtype, H, D) is instantiated: (f32, 128, 16), (bf16, 128, 16), (bf16, 256, 32);
+ *                             returns the piece counts: forward (all operands), backward score product, backward wide.
+ *   grl_attn_split            x [rows, C] (f32 / bf16, leading dimension ld) * optional per-column scale -> np dense bf16
+ *                             [rows, C] matrices at pieces + pc * rows * C.  bf16 models pass f / g / h themselves.
+ *   grl_selfatten_tc_fwd      f_p, g_p: [np][B*N, D]; h_p: [np][B*N, H] bf16; V, out: [B*N, H] of io_dtype.  Training:
+ *                             o_save float [B*N, H] (= P h before gamma), m_save / l_save float [B*N] (row max / row sum
+ *                             of exp(s - max)); eval: NULL for the three.
+ *   grl_selfatten_tc_bwd      do_p: scratch bf16 [np_bwd][B*N, H]; Dvec: scratch float [B*N]; part: float
+ *                             [grl_selfatten_tc_prep_blocks(B*N), H] partial sums of d(gamma) (the caller adds the rows
+ *                             up); df, dg: [B*N, D], dh: [B*N, H] of io_dtype; d(V) = dOut.  f_p / g_p need the
+ *                             backward score product's piece count, h_p the wide one (prefixes of the forward's pieces).
+ * ------------------------------------------------------------------------------------------ */
+int grl_selfatten_tc_pieces(int io_dtype, int H, int D, int* np_fwd, int* nps_bwd, int* np_bwd);
+int grl_attn_split(const void* x, int64_t ld, int dtype, int64_t rows, int C, const float* scale, int np, void* pieces,
+                   void* stream);
+int grl_selfatten_tc_fwd(const void* f_p, const void* g_p, const void* h_p, const void* V, const float* gamma, void* out,
+                         float* o_save, float* m_save, float* l_save, int io_dtype, int B, int N, int H, int D,
+                         void* stream);
+size_t grl_selfatten_tc_prep_blocks(int64_t rows);
+int grl_selfatten_tc_bwd(const void* dOut, const float* o_save, const float* m_save, const float* l_save, const void* f_p,
+                         const void* g_p, const void* h_p, const float* gamma, void* do_p, float* Dvec, float* part,
+                         void* df, void* dg, void* dh, int io_dtype, int B, int N, int H, int D, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Loss and optimizer of the KV train step (deterministic reductions; csrc/train_ops.cu).

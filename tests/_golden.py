@@ -44,6 +44,7 @@ def load_production_case(name):
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
     meta = json.loads(str(z["meta"]))
     case = {"meta": meta, "err_ref32": json.loads(str(z["err_ref32"])),
+            "err_ref_bf16": json.loads(str(z["err_ref_bf16"])),
             "weights_check": json.loads(str(z["weights_check"]))}
     for k in ("logits_eval", "logits_train", "loss"):
         case[k] = torch.from_numpy(z[k])

@@ -39,6 +39,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-bow", action="store_true", help="skip the bag-of-words feature variant (sparse emb1 path)")
+    ap.add_argument("--x3-promo", type=int, default=None, help="K-blocks per TMEM accumulator promotion of the fp32 forward GEMMs (A/B)")
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket ONE extra train step (after the timed region) with cudaProfilerStart/Stop for "
                          "`ncu --profile-from-start off`; numbers printed by such a run are not bench values")
@@ -158,6 +159,8 @@ def run_b200(args):
 
     wl = synthetic.CONFIGS[args.workload]
     B = args.batch or wl.B
+    if args.x3_promo:
+        ops.set_x3_promotion(args.x3_promo)
     torch.manual_seed(0)                                     # identical replicas
     model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention).to(dev)
     model.set_compute_dtype(wl.dtype)

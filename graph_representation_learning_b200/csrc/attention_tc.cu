@@ -87,7 +87,7 @@ struct AttnTcParams {
     float* o_save;             // [B*N, H] fp32 (training) or null
     float* m_save;             // [B*N] row max (training) or null
     float* l_save;             // [B*N] row sum of exp(s - max)
-    const float* Dvec;         // [B*N] D_i = do_i . o_i           (backward)
+    float* Dvec;               // [B*N] D_i = sum_j P_ij dP_ij (written by the query-major backward kernel, read by the key-major one)
     void* df;                  // [B*N, D]
     void* dg;                  // [B*N, D]
     void* dh;                  // [B*N, H]
@@ -384,93 +384,119 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
     const int64_t grow = static_cast<int64_t>(b) * N + row;
     const float m = live ? p.m_save[grow] : 0.0f;
     const float inv_l = live ? 1.0f / p.l_save[grow] : 0.0f;
-    const float Dv = live ? p.Dvec[grow] : 0.0f;
     mbar_wait(bar_tma, ph_tma);
     ph_tma ^= 1;
 
     constexpr uint32_t idescS = umma_idesc(1, 128, 128, 0, 0);
     constexpr uint32_t idescDF = umma_idesc(1, 128, 64, 0, 1);
 
-    for (int kb = 0; kb < nkb; ++kb) {
-        if (tid == 0) {
-            mbar_expect_tx(bar_tma, (NPS + NP * HS) * SLAB);
+    // Two passes over the key blocks.  Pass 0 accumulates D_i = sum_j P_ij dP_ij from the SAME P and dP the second pass
+    // uses (not do_i . o_i from the forward's rounded products): sum_j dS_ij is then zero to fp32 rounding, and the
+    // cancellation in dS = P (dP - D) does not amplify the rounding of the operand pieces into df / dg.
+    float Dv = 0.0f;
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int kb = 0; kb < nkb; ++kb) {
+            if (tid == 0) {
+                mbar_expect_tx(bar_tma, (NPS + NP * HS) * SLAB);
 #pragma unroll
-            for (int pc = 0; pc < NPS; ++pc) tma_load_3d(sG + pc * SLAB, &tmG, bar_tma, 0, kb * 128, pc * p.B + b);
+                for (int pc = 0; pc < NPS; ++pc) tma_load_3d(sG + pc * SLAB, &tmG, bar_tma, 0, kb * 128, pc * p.B + b);
 #pragma unroll
-            for (int pc = 0; pc < NP; ++pc)
+                for (int pc = 0; pc < NP; ++pc)
 #pragma unroll
-                for (int s = 0; s < HS; ++s)
-                    tma_load_3d(sH + (pc * HS + s) * SLAB, &tmH, bar_tma, 64 * s, kb * 128, pc * p.B + b);
-        }
-        mbar_wait(bar_tma, ph_tma);
-        ph_tma ^= 1;
-        if (warp == 0) {
-            tc_fence_after_sync();
-            if (elect_one_sync()) {
+                    for (int s = 0; s < HS; ++s)
+                        tma_load_3d(sH + (pc * HS + s) * SLAB, &tmH, bar_tma, 64 * s, kb * 128, pc * p.B + b);
+            }
+            mbar_wait(bar_tma, ph_tma);
+            ph_tma ^= 1;
+            if (warp == 0) {
+                tc_fence_after_sync();
+                if (elect_one_sync()) {
 #pragma unroll
-                for (int i = 0; i < NCS; ++i) {     // S = f g^T
-                    const uint64_t a = umma_desc_kmajor_sw128(smem_u32(sF + kPA(i) * SLAB));
-                    const uint64_t bd = umma_desc_kmajor_sw128(smem_u32(sG + kPB(i) * SLAB));
+                    for (int i = 0; i < NCS; ++i) {     // S = f g^T
+                        const uint64_t a = umma_desc_kmajor_sw128(smem_u32(sF + kPA(i) * SLAB));
+                        const uint64_t bd = umma_desc_kmajor_sw128(smem_u32(sG + kPB(i) * SLAB));
 #pragma unroll
-                    for (int k = 0; k < D / 16; ++k)
-                        umma<false>(tmem_base + COL_S, a + 2 * k, bd + 2 * k, idescS, (i | k) != 0);
+                        for (int k = 0; k < D / 16; ++k)
+                            umma<false>(tmem_base + COL_S, a + 2 * k, bd + 2 * k, idescS, (i | k) != 0);
+                    }
+#pragma unroll
+                    for (int i = 0; i < NC; ++i) {      // dP = do h^T, K = H
+#pragma unroll
+                        for (int kk = 0; kk < H / 16; ++kk) {
+                            const uint64_t a = umma_desc_kmajor_sw128(smem_u32(sDO + (kPA(i) * HS + kk / 4) * SLAB)) + 2 * (kk % 4);
+                            const uint64_t bd = umma_desc_kmajor_sw128(smem_u32(sH + (kPB(i) * HS + kk / 4) * SLAB)) + 2 * (kk % 4);
+                            umma<false>(tmem_base + COL_DP, a, bd, idescS, (i | kk) != 0);
+                        }
+                    }
+                    umma_commit(bar_mma);
                 }
+                __syncwarp();
+            }
+            mbar_wait(bar_mma, ph_mma);
+            ph_mma ^= 1;
+            tc_fence_after_sync();
+            if (pass == 0) {
+                float dacc = 0.0f;
 #pragma unroll
-                for (int i = 0; i < NC; ++i) {      // dP = do h^T, K = H
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t rs[32], rp[32];
+                    tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, rs);
+                    tmem_ld_32x32(tmem_base + lane_sel + COL_DP + 32 * c, rp);
+                    tmem_ld_wait();
+                    const int valid = N - (kb * 128 + 32 * c);
 #pragma unroll
-                    for (int kk = 0; kk < H / 16; ++kk) {
-                        const uint64_t a = umma_desc_kmajor_sw128(smem_u32(sDO + (kPA(i) * HS + kk / 4) * SLAB)) + 2 * (kk % 4);
-                        const uint64_t bd = umma_desc_kmajor_sw128(smem_u32(sH + (kPB(i) * HS + kk / 4) * SLAB)) + 2 * (kk % 4);
-                        umma<false>(tmem_base + COL_DP, a, bd, idescS, (i | kk) != 0);
+                    for (int e = 0; e < 32; ++e) {
+                        const float pe = e < valid ? __expf(__uint_as_float(rs[e]) - m) * inv_l : 0.0f;
+                        dacc = fmaf(pe, __uint_as_float(rp[e]), dacc);
                     }
                 }
-                umma_commit(bar_mma);
+                Dv += dacc;
+                tc_fence_before_sync();
+                __syncthreads();
+                continue;
             }
-            __syncwarp();
-        }
-        mbar_wait(bar_mma, ph_mma);
-        ph_mma ^= 1;
-        tc_fence_after_sync();
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            uint32_t rs[32], rp[32];
-            tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, rs);
-            tmem_ld_32x32(tmem_base + lane_sel + COL_DP + 32 * c, rp);
-            tmem_ld_wait();
-            const int valid = N - (kb * 128 + 32 * c);
-            float ds[32];
+            for (int c = 0; c < 4; ++c) {
+                uint32_t rs[32], rp[32];
+                tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, rs);
+                tmem_ld_32x32(tmem_base + lane_sel + COL_DP + 32 * c, rp);
+                tmem_ld_wait();
+                const int valid = N - (kb * 128 + 32 * c);
+                float ds[32];
 #pragma unroll
-            for (int e = 0; e < 32; ++e) {
-                const float pe = e < valid ? __expf(__uint_as_float(rs[e]) - m) * inv_l : 0.0f;
-                ds[e] = pe * (__uint_as_float(rp[e]) - Dv);
-            }
-            uint32_t pk[NP][16];
-            split_row32<NP>(ds, pk);
-#pragma unroll
-            for (int pc = 0; pc < NP; ++pc) tmem_st_32x16(tmem_base + lane_sel + COL_S + 32 * c + 16 * pc, pk[pc]);
-        }
-        tmem_st_wait();
-        tc_fence_before_sync();
-        __syncthreads();
-        if (warp == 0) {
-            tc_fence_after_sync();
-            if (elect_one_sync()) {
-#pragma unroll
-                for (int i = 0; i < NC; ++i) {      // df += dS g: A = dS pieces in TMEM, B = g MN-major (N = 64, zero padded)
-                    const uint64_t gd = umma_desc_mnmajor_sw128(smem_u32(sG + kPB(i) * SLAB), SLAB, 1024, 2);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        umma_ts<false>(tmem_base + COL_DF, tmem_base + COL_S + 32 * (k / 2) + 16 * kPA(i) + 8 * (k % 2),
-                                       gd + 128 * k, idescDF, (kb | i | k) != 0);
+                for (int e = 0; e < 32; ++e) {
+                    const float pe = e < valid ? __expf(__uint_as_float(rs[e]) - m) * inv_l : 0.0f;
+                    ds[e] = pe * (__uint_as_float(rp[e]) - Dv);
                 }
-                umma_commit(bar_mma);
+                uint32_t pk[NP][16];
+                split_row32<NP>(ds, pk);
+#pragma unroll
+                for (int pc = 0; pc < NP; ++pc) tmem_st_32x16(tmem_base + lane_sel + COL_S + 32 * c + 16 * pc, pk[pc]);
             }
-            __syncwarp();
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncthreads();
+            if (warp == 0) {
+                tc_fence_after_sync();
+                if (elect_one_sync()) {
+#pragma unroll
+                    for (int i = 0; i < NC; ++i) {      // df += dS g: A = dS pieces in TMEM, B = g MN-major (N = 64, zero padded)
+                        const uint64_t gd = umma_desc_mnmajor_sw128(smem_u32(sG + kPB(i) * SLAB), SLAB, 1024, 2);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k)
+                            umma_ts<false>(tmem_base + COL_DF, tmem_base + COL_S + 32 * (k / 2) + 16 * kPA(i) + 8 * (k % 2),
+                                           gd + 128 * k, idescDF, (kb | i | k) != 0);
+                    }
+                    umma_commit(bar_mma);
+                }
+                __syncwarp();
+            }
+            mbar_wait(bar_mma, ph_mma);
+            ph_mma ^= 1;
+            tc_fence_after_sync();
+            __syncthreads();
         }
-        mbar_wait(bar_mma, ph_mma);
-        ph_mma ^= 1;
-        tc_fence_after_sync();
-        __syncthreads();
+        if (pass == 0 && live) p.Dvec[grow] = Dv;
     }
 
     {
@@ -719,32 +745,29 @@ __global__ void attn_split_kernel(const T* __restrict__ x, int64_t ld, int64_t r
     }
 }
 
-// Backward preparation, one pass over dOut and o: do = gamma * dOut as np bf16 pieces, D_i = sum_c do_ic o_ic, and the
-// per-block partial sums of d(gamma)_c = sum_i dOut_ic o_ic (rows of a block in order; the caller adds the blocks up).
+// Backward preparation, one pass over dOut and o: do = gamma * dOut as np bf16 pieces and the per-block partial sums of
+// d(gamma)_c = sum_i dOut_ic o_ic (rows of a block in order; the caller adds the blocks up).  D_i is computed by the
+// query-major kernel itself.
 // Block = 256 threads = 8 warps over kPrepRows rows.
 constexpr int kPrepRows = 64;
 template <typename T>
 __global__ void __launch_bounds__(256)
 attn_bwd_prep_kernel(const T* __restrict__ dOut, const float* __restrict__ o, const float* __restrict__ gamma, int64_t rows,
-                     int H, int np, __nv_bfloat16* __restrict__ do_p, float* __restrict__ Dvec, float* __restrict__ part) {
+                     int H, int np, __nv_bfloat16* __restrict__ do_p, float* __restrict__ part) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kPrepRows;
     const int64_t total = rows * H;
     for (int rr = wib; rr < kPrepRows; rr += 8) {
         const int64_t r = r0 + rr;
         if (r >= rows) break;
-        float acc = 0.0f;
         for (int c = lane; c < H; c += 32) {
             float v = to_float(dOut[r * H + c]) * gamma[c];
-            acc = fmaf(v, o[r * H + c], acc);
             for (int pc = 0; pc < np; ++pc) {
                 const __nv_bfloat16 h = __float2bfloat16_rn(v);
                 do_p[pc * total + r * H + c] = h;
                 v -= __bfloat162float(h);
             }
         }
-        for (int s = 16; s >= 1; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
-        if (lane == 0) Dvec[r] = acc;
     }
     const int64_t r_end = r0 + kPrepRows < rows ? r0 + kPrepRows : rows;
     for (int c = threadIdx.x; c < H; c += 256) {
@@ -921,10 +944,10 @@ extern "C" int grl_selfatten_tc_bwd(const void* dOut, const float* o_save, const
     const int blocks = static_cast<int>((rows + kPrepRows - 1) / kPrepRows);
     if (io_dtype == GRL_BF16)
         attn_bwd_prep_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dOut), o_save, gamma, rows, H,
-                                                                    npb, static_cast<__nv_bfloat16*>(do_p), Dvec, part);
+                                                                    npb, static_cast<__nv_bfloat16*>(do_p), part);
     else
         attn_bwd_prep_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(dOut), o_save, gamma, rows, H, npb,
-                                                            static_cast<__nv_bfloat16*>(do_p), Dvec, part);
+                                                            static_cast<__nv_bfloat16*>(do_p), part);
     GRL_LAUNCH_CHECK("attn_bwd_prep_kernel");
     AttnTcParams p{};
     p.B = B; p.N = N; p.io_bf16 = io_dtype == GRL_BF16; p.gamma = gamma;

@@ -132,6 +132,13 @@ class GemmConfig:
     _modes = {"tf32x3": 2, "tf32bc": 3, "tf32": 1}
 
 
+def set_x3_promotion(k_blocks: int) -> None:
+    """K-blocks (of 32) the three-product forward kernels accumulate in TMEM before the partial sum is promoted to fp32
+    registers (grl_gemm_x3_set_promo; default 2).  TMEM accumulation truncates: fewer blocks = less rounding noise in
+    the pre-activations = fewer ReLU-derivative flips against an fp64 run, at the price of more accumulator drains."""
+    _lib.check(_lib.load().grl_gemm_x3_set_promo(int(k_blocks)), "grl_gemm_x3_set_promo")
+
+
 def _mode_for(dtype: torch.dtype, fp32_mode: Optional[str] = None) -> int:
     if dtype == torch.bfloat16:
         return _lib.GEMM_BF16

@@ -2,11 +2,15 @@
 """bench.py -- train graphs/s of the GraphCNNDropEdge hot path on N B200s (BASELINE.json metric).
 
   python bench.py --gpus 1 --steps K --warmup W              our arm (CUDA kernels behind the C ABI)
-  python bench.py --impl reference --gpus 1 --steps K ...    the reference's CPU implementation (oracle port)
+  python bench.py --impl reference --gpus 1 --steps K ...    the reference's own CPU implementation (oracle/_ref)
   torchrun --nproc-per-node N bench.py --gpus N ...          data parallel, one process per GPU (weak scaling)
 
 A "step" is one KVProcedure train step (kv_procedure.py:143-164: forward([V, A]) -> CE -> backward -> clip -> Adam)
 over one synthetic batch of the named workload.  One JSON line on stdout (rank 0).
+
+Line layout: the contract keys are about cfg2 (BASELINE.json configs[1]: 256 graphs x 500 nodes, S=256, fp32); the other
+BASELINE configurations ride in objects of the same line -- `cfg3` (S=512 bf16, 1000-node graphs: weak at 128 graphs / GPU
+and strong at a global batch of 1024), and at N = 1 `cfg4` (one 1M-node graph) and `cfg5` (eval latency sweep).
 """
 from __future__ import annotations
 
@@ -24,6 +28,7 @@ if ROOT not in sys.path:
 
 METRIC = "train graphs/sec (fwd+bwd)"
 UNIT = "graphs/s"
+NOMINAL_HBM_GBS = 8000.0          # the figure BASELINE.json's north_star quotes ("about 8 TB/s")
 
 
 def parse_args():
@@ -34,15 +39,18 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=["cfg1", "cfg2", "cfg3"])
     ap.add_argument("--batch", type=int, default=None, help="override graphs per GPU (debug)")
-    ap.add_argument("--cpu-batch", type=int, default=8, help="graphs per step of the bounded CPU sample")
+    ap.add_argument("--cpu-batch", type=int, default=16, help="graphs per step of the bounded CPU sample (SURVEY 8d: 16)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-bow", action="store_true", help="skip the bag-of-words feature variant (sparse emb1 path)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg3 / cfg4 / cfg5 objects")
     ap.add_argument("--x3-promo", type=int, default=None, help="K-blocks per TMEM accumulator promotion of the fp32 forward GEMMs (A/B)")
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket ONE extra train step (after the timed region) with cudaProfilerStart/Stop for "
                          "`ncu --profile-from-start off`; numbers printed by such a run are not bench values")
+    ap.add_argument("--profile-workload", default=None, choices=[None, "cfg3", "cfg4"],
+                    help="with --profile-step: profile one step of this configuration instead of the bench line's")
     return ap.parse_args()
 
 
@@ -76,7 +84,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append(parts)
             except Exception:
                 pass
-            self._halt.wait(0.2)
+            self._halt.wait(0.1)
 
     def finish(self):
         self._halt.set()
@@ -90,30 +98,78 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
-def cpu_reference_arm(wl, B, steps, warmup):
-    """The reference's CPU path (oracle port of drop_robust_gcn.py:61-103 + kv_procedure.py:143-164) on the host
-    cores, dense adjacency, nn.Dropout semantics.  Returns (graphs/s, ms/step, cores)."""
-    import torch
-    from graph_representation_learning_b200 import GraphCNNDropEdge, synthetic
-    from oracle import reference_port as rp
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    torch.manual_seed(0)
-    model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention)
-    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
-    V, A, y = synthetic.make_batch(wl, 1234, "cpu", B=B)
-    A = A.float()                                            # kv_procedure.py:118
-    state = {}
-    times = []
-    for it in range(warmup + steps):
-        t0 = time.perf_counter()
-        rp.train_step(sd, V, A, y, state, step=it + 1)
-        times.append(time.perf_counter() - t0)
-    t = sum(times[warmup:]) / steps
-    return B / t, t * 1e3, cores
+# ------------------------------------------------------------------------------------------------ CPU arm
+class CpuReference:
+    """The reference's CPU path on the host cores: the UNMODIFIED ``gnn.models.GraphCNNDropEdge`` staged under
+    oracle/_ref (oracle/ref_loader.py) inside a restated ``_run_train_step`` (kv_procedure.py:143-164), dense fp32
+    adjacency and nn.Dropout exactly like the reference.  Falls back to the port (oracle/reference_port.py) only when
+    the staged reference is absent, and says so in ``kind``."""
+
+    def __init__(self, wl, threads=None):
+        import torch
+        from oracle import ref_loader
+        self.torch, self.wl = torch, wl
+        self.cores = threads or os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        loaded = ref_loader.load_reference()
+        torch.manual_seed(0)
+        if loaded is not None:
+            self.kind = "reference"
+            self.model = loaded[0](wl.input_dim, wl.output_dim, wl.num_edges, net_size=wl.net_size,
+                                   use_attention=wl.use_attention)
+            self.opt = torch.optim.Adam([p for p in self.model.parameters() if p.requires_grad])
+            self._step = lambda V, A, y: ref_loader.reference_train_step(self.model, self.opt, V, A, y)
+        else:
+            from graph_representation_learning_b200 import GraphCNNDropEdge
+            from oracle import reference_port as rp
+            self.kind = "port"
+            self.model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention)
+            sd = {k: v.detach().clone() for k, v in self.model.state_dict().items()}
+            self._sd = sd
+            state, it = {}, [0]
+
+            def step(V, A, y):
+                it[0] += 1
+                return rp.train_step(sd, V, A, y, state, step=it[0])[1]
+            self._step = step
+
+    def batch(self, B):
+        from graph_representation_learning_b200 import synthetic
+        V, A, y = synthetic.make_batch(self.wl, 1234, "cpu", B=B)
+        return V.contiguous(), A.float(), y                  # kv_procedure.py:117-118: .float() of both inputs
+
+    def train(self, B, steps, warmup):
+        """(graphs/s, ms/step) of `steps` timed train steps after `warmup`"""
+        V, A, y = self.batch(B)
+        times = []
+        for _ in range(warmup + steps):
+            t0 = time.perf_counter()
+            self._step(V, A, y)
+            times.append(time.perf_counter() - t0)
+        t = sum(times[warmup:]) / max(steps, 1)
+        return B / t, t * 1e3
+
+    def eval_forward(self, B, N, reps=1):
+        """graphs/s of the eval forward at `N` nodes per graph (cfg5's CPU column)"""
+        torch = self.torch
+        from graph_representation_learning_b200 import synthetic
+        wl = synthetic.Workload("cfg5", B, N)
+        V, A, _ = synthetic.make_batch(wl, 77 + N, "cpu", B=B)
+        V, A = V.contiguous(), A.float()
+        if self.kind == "port":
+            from oracle import reference_port as rp
+            fwd = lambda: rp.forward(self._sd, V, A, training=False)  # noqa: E731
+        else:
+            self.model.eval()
+            fwd = lambda: self.model([V, A])  # noqa: E731
+        with torch.no_grad():
+            fwd()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                fwd()
+        return B * reps / (time.perf_counter() - t0)
 
 
-# ------------------------------------------------------------------------------------------------ reference arm
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -121,16 +177,36 @@ def run_reference(args):
     from graph_representation_learning_b200 import synthetic
     wl = synthetic.CONFIGS[args.workload]
     B = args.cpu_batch
-    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
-    val, ms, cores = cpu_reference_arm(wl, B, steps, warmup)
-    sample = f"{B} graphs x {wl.N} nodes per step ({warmup}+{steps} steps) of {wl.name}, dense fp32 adjacency"
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    ref = CpuReference(wl)
+    val, ms = ref.train(B, steps, warmup)
+    sample = (f"{B} graphs x {wl.N} nodes per step ({warmup}+{steps} steps) of {wl.name}, dense fp32 adjacency, "
+              f"{ref.cores} threads")
+    extra = {}
+    try:
+        import psutil
+        free_gb = psutil.virtual_memory().available / 1e9
+    except Exception:
+        free_gb = 0.0
+    if wl.name.startswith("cfg2"):
+        # a 1-thread run, and one step at the configuration's full batch when host RAM allows
+        one = CpuReference(wl, threads=1)
+        v1, ms1 = one.train(min(B, 4), 1, 1)
+        extra["single_thread"] = {"value": v1, "unit": UNIT, "ms_per_step": ms1, "graphs_per_step": min(B, 4), "cores": 1}
+        del one
+        ref = CpuReference(wl)
+        if free_gb > 64:
+            vf, msf = ref.train(wl.B, 1, 0)
+            extra["full_batch_step"] = {"value": vf, "unit": UNIT, "ms_per_step": msf, "graphs_per_step": wl.B,
+                                        "cores": ref.cores, "note": "one un-warmed step at the configuration's batch"}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam", "graphs_per_step": B},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        **extra,
     }))
 
 
@@ -156,32 +232,23 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     if _lib.load().grl_device_ok() != 1:
         raise SystemExit("bench.py needs a compute-capability 10.x GPU (B200); there is no fallback path")
-
-    wl = synthetic.CONFIGS[args.workload]
-    B = args.batch or wl.B
     if args.x3_promo:
         ops.set_x3_promotion(args.x3_promo)
-    torch.manual_seed(0)                                     # identical replicas
-    model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention).to(dev)
-    model.set_compute_dtype(wl.dtype)
-    model.rng_seed = 1000 + rank                             # independent DropEdge/dropout streams per rank
-    step = KVTrainStep(model)
-    feat_dtype = torch.float32 if wl.dtype == torch.float32 else torch.bfloat16
-    V, A, y = synthetic.make_batch(wl, 1234 + rank, dev, B=B, feature_dtype=feat_dtype)
-    batch_dev = {"textline_encoding": V, "adjacency_matrix": A, "node_label": y}
+    pk = peaks()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, sample_clocks=False):
+        """(ms per step as the max over ranks, our kernel launches in the timed region, clocks)"""
         for _ in range(warmup):
             fn()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         n0 = _lib.launches()
-        sampler = ClockSampler(local_rank) if rank == 0 else None
+        sampler = ClockSampler(local_rank) if (rank == 0 and sample_clocks) else None
         if sampler:
             sampler.start()
         e0.record()
@@ -196,11 +263,41 @@ def run_b200(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t) / steps, _lib.launches() - n0, clocks
 
-    # (1) device-resident inputs: the whole forward([V, A]) API call incl. the CSR/CSC pack of the dense fp16 A
-    ms_step, launches, clocks = timed(lambda: step.run_train_step(batch_dev), args.steps, args.warmup)
-    value = world * B / (ms_step * 1e-3)
+    def make_step(wl):
+        torch.manual_seed(0)                                     # identical replicas
+        model = GraphCNNDropEdge(wl.input_dim, wl.output_dim, wl.num_edges, wl.net_size, wl.use_attention).to(dev)
+        model.set_compute_dtype(wl.dtype)
+        model.rng_seed = 1000 + rank                             # independent DropEdge/dropout streams per rank
+        return model, KVTrainStep(model)
 
-    if args.profile_step:
+    def exposed_allreduce(step, fn, steps):
+        """ms per step with the gradient collective skipped (None on one GPU): step time minus this = what the all-reduce
+        costs on the critical path"""
+        if world == 1:
+            return None
+        bucket = step.bucket
+        bucket.all_reduce = lambda average=True: bucket.reattach()
+        bucket.arm_overlap = lambda: None
+        try:
+            ms_off, _, _ = timed(fn, steps, 1)
+        finally:
+            del bucket.all_reduce, bucket.arm_overlap
+        return ms_off
+
+    wl = synthetic.CONFIGS[args.workload]
+    B = args.batch or wl.B
+    model, step = make_step(wl)
+    grad_bytes = 4 * step.bucket.flat.numel()
+    feat_dtype = torch.float32 if wl.dtype == torch.float32 else torch.bfloat16
+    V, A, y = synthetic.make_batch(wl, 1234 + rank, dev, B=B, feature_dtype=feat_dtype)
+    batch_dev = {"textline_encoding": V, "adjacency_matrix": A, "node_label": y}
+
+    # (1) device-resident inputs: the whole forward([V, A]) API call incl. the CSR/CSC pack of the dense fp16 A
+    ms_step, launches, clocks = timed(lambda: step.run_train_step(batch_dev), args.steps, args.warmup, sample_clocks=True)
+    value = world * B / (ms_step * 1e-3)
+    ms_nocomm = exposed_allreduce(step, lambda: step.run_train_step(batch_dev), max(5, args.steps // 2))
+
+    if args.profile_step and not args.profile_workload:
         torch.cuda.synchronize()
         torch.cuda.profiler.start()
         step.run_train_step(batch_dev)
@@ -211,56 +308,81 @@ def run_b200(args):
     # the SAME batch: the EdgeListCollate format (features + (b, i, l, j) triples; the adjacency never exists densely,
     # SURVEY 8f N1) is the headline; the reference's dense fp16 [B, N, L, N] adjacency is reported beside it.
     e2e = None
-    if not args.no_e2e:
+
+    def pin(t):
+        return torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)
+
+    def nbytes(d, keys):
+        return sum(d[k].numel() * d[k].element_size() for k in keys)
+
+    pinned_loss = torch.zeros(64, dtype=torch.float32).pin_memory()
+
+    def e2e_run(host, steps, warmup):
+        """the public step API over a host loader: H2D of every step's inputs (pinned -> device, one batch ahead on
+        a copy stream) and a D2H read of every step's loss, all inside the timed region"""
         from graph_representation_learning_b200.trainer import DevicePrefetcher
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        seen = []
+        for i, dev_batch in enumerate(DevicePrefetcher((host for _ in range(warmup + steps)), dev)):
+            if i == warmup:
+                e0.record()
+            loss = step.run_train_step(dev_batch)
+            pinned_loss[i % 64].copy_(loss, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            if seen:                                   # read the previous step's loss on the host
+                pev, pi = seen[-1]
+                pev.synchronize()
+                float(pinned_loss[pi % 64])
+            seen.append((ev, i))
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t) / steps
 
-        def pin(t):
-            return torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)
+    def h2d_probe():
+        """plain pinned -> device cudaMemcpyAsync of 1 GiB, all ranks at once: the box's H2D ceiling per rank"""
+        src = torch.empty(1 << 30, dtype=torch.uint8, pin_memory=True)
+        dst = torch.empty(1 << 30, dtype=torch.uint8, device=dev)
+        dst.copy_(src, non_blocking=True)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(4):
+            dst.copy_(src, non_blocking=True)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gbs = 4 * (1 << 30) / (float(t) * 1e-3) / 1e9
+        del src, dst
+        return gbs
 
+    e_steps = max(3, min(args.steps, 10))
+    if not args.no_e2e:
         Vp = V._base if V._base is not None else V          # the padded storage (16-byte row pitch)
         host_dense = {k: pin(v) for k, v in batch_dev.items()}
         Vp_h = pin(Vp)
         host_edges = {"textline_encoding": Vp_h[..., :wl.input_dim], "features_padded": Vp_h,
                       "node_label": host_dense["node_label"], "edges": pin(A.nonzero().to(torch.int32)),
                       "edge_weights": None, "graph_shape": (B, wl.N, wl.num_edges)}
-        pinned_loss = torch.zeros(64, dtype=torch.float32).pin_memory()
-
-        def nbytes(d, keys):
-            return sum(d[k].numel() * d[k].element_size() for k in keys)
-
-        def e2e_run(host, steps, warmup):
-            """the public step API over a host loader: H2D of every step's inputs (pinned -> device, one batch ahead on
-            a copy stream) and a D2H read of every step's loss, all inside the timed region"""
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            seen = []
-            for i, dev_batch in enumerate(DevicePrefetcher((host for _ in range(warmup + steps)), dev)):
-                if i == warmup:
-                    e0.record()
-                loss = step.run_train_step(dev_batch)
-                pinned_loss[i % 64].copy_(loss, non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record()
-                if seen:                                   # read the previous step's loss on the host
-                    pev, pi = seen[-1]
-                    pev.synchronize()
-                    float(pinned_loss[pi % 64])
-                seen.append((ev, i))
-            e1.record()
-            barrier()
-            t = torch.tensor([e0.elapsed_time(e1)], device=dev)
-            if world > 1:
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t) / steps
-        e_steps = max(3, min(args.steps, 10))
         ms_edges = e2e_run(host_edges, e_steps, 2)
         ms_dense = e2e_run(host_dense, e_steps, 2)
-        e2e = {"value": world * B / (ms_edges * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": nbytes(host_edges, ["features_padded", "node_label", "edges"]),
+        h2d_bytes = nbytes(host_edges, ["features_padded", "node_label", "edges"])
+        probe = h2d_probe()
+        e2e = {"value": world * B / (ms_edges * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                "d2h_bytes_per_step": 4, "ms_per_step": ms_edges, "steps": e_steps,
                "how": "KVTrainStep.run_train_step over DevicePrefetcher(host loader of EdgeListCollate batches): pinned "
                       "host V (fp32, all columns) / y / int32 (b,i,l,j) edge triples -> device one batch ahead on a copy "
                       "stream, CSR/CSC packed on the device, loss read back every step",
+               "h2d_probe": {"per_rank_GBps": probe, "aggregate_GBps": probe * world,
+                             "loader_per_rank_GBps": h2d_bytes / (ms_edges * 1e-3) / 1e9,
+                             "how": "1 GiB pinned -> device cudaMemcpyAsync x4 on every rank at once (max over ranks): the "
+                                    "box's concurrent H2D ceiling, beside what the loader moves per rank and step time"},
                "dense_adjacency": {"value": world * B / (ms_dense * 1e-3), "ms_per_step": ms_dense,
                                    "h2d_bytes_per_step": nbytes(host_dense, list(host_dense)),
                                    "how": "same, host loader yields the reference's dense fp16 [B,N,L,N] adjacency "
@@ -273,7 +395,6 @@ def run_b200(args):
     bow = None
     if not args.no_bow and wl.dtype == torch.float32:
         from graph_representation_learning_b200 import SparseNodeFeatures
-        from graph_representation_learning_b200.trainer import DevicePrefetcher
         Vb, _, _ = synthetic.make_batch(wl, 1234 + rank, dev, B=B, features="bow")
         sf = SparseNodeFeatures.from_dense(Vb)
         del Vb
@@ -297,7 +418,57 @@ def run_b200(args):
         del sf
 
     # (3) roofline of the aggregation kernel (gcn1 SpMM, DropEdge weights applied), timed alone with CUDA events
-    pk = peaks()
+    roofline = None
+    if not args.no_roofline:
+        roofline = spmm_and_gemm_roofline(torch, ops, PackedGraphBatch, timed, pk, wl, B, A, dev)
+
+    # (4) CPU baseline: the reference itself on a bounded sample of the same workload (rank 0, N=1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ref = CpuReference(wl)
+        cb = args.cpu_batch
+        v, ms_cpu = ref.train(cb, 3, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "ms_per_step": ms_cpu,
+               "sample": f"{cb} graphs x {wl.N} nodes per step (1+3 steps) of the same workload, dense fp32 adjacency"}
+        del ref
+
+    # (5) the other BASELINE configurations
+    v_gb = V.numel() * V.element_size() / 1e9
+    del step, model, batch_dev, V, A, y
+    torch.cuda.empty_cache()
+    extra = {}
+    if not args.no_configs and args.workload == "cfg2" and args.batch is None:
+        extra["cfg3"] = run_cfg3(torch, synthetic, make_step, timed, exposed_allreduce, world, rank, dev, args)
+        torch.cuda.empty_cache()
+        if world == 1:
+            extra["cfg5"] = run_cfg5(torch, synthetic, GraphCNNDropEdge, PackedGraphBatch, dev,
+                                     rank == 0 and not args.no_cpu_baseline)
+            torch.cuda.empty_cache()
+            extra["cfg4"] = run_cfg4(torch, synthetic, PackedGraphBatch, ops, make_step, timed, pk, dev, args)
+            torch.cuda.empty_cache()
+
+    if rank == 0:
+        allreduce = None
+        if world > 1:
+            allreduce = {"bytes": grad_bytes, "ms_per_step_without": ms_nocomm, "exposed_ms": ms_step - ms_nocomm,
+                         "how": "two buckets: everything but emb1 is reduced on NCCL's stream while emb1's weight-gradient "
+                                "GEMM runs, then emb1; sum of gradients (the loss is normalised by the GLOBAL valid-node count)"}
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if wl.dtype == torch.float32 else "bf16", "data": "synthetic",
+            "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam (forward includes the CSR/CSC pack of dense A)",
+                       "graphs_per_gpu": B, "global_batch": world * B, "parallelism": f"dp{world}",
+                       "l2": "inputs (V %.2f GB) larger than L2" % v_gb, "features": "dense U[0,1)",
+                       "host_cpus_rank0": (f"{len(numa_cpus)} GPU-local cores" if numa_cpus else "unbound")},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "allreduce": allreduce, "bow_features": bow, **extra,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def spmm_and_gemm_roofline(torch, ops, PackedGraphBatch, timed, pk, wl, B, A, dev):
     g = PackedGraphBatch.from_dense(A)
     S = wl.net_size
     X = torch.randn(B * wl.N, S, device=dev, dtype=wl.dtype)
@@ -314,14 +485,16 @@ def run_b200(args):
         traffic, traffic_bwd = tj["fwd"]["dram_bytes_per_launch"], tj["bwd"]["dram_bytes_per_launch"]
     roofline = {"kernel": "spmm_slab2_kernel (gcn1 aggregation fwd over the DropEdge node streams)", "bound": "hbm",
                 "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                "traffic": traffic,
+                "frac_nominal": achieved / NOMINAL_HBM_GBS, "peak_nominal": NOMINAL_HBM_GBS, "traffic": traffic,
                 "peak_source": pk["source"], "ms_per_launch": ms_spmm, "algorithmic_bytes": alg_bytes}
     dYt = torch.randn(g.num_rows, S, device=dev, dtype=wl.dtype)
     dX = torch.empty(B * wl.N, S, device=dev, dtype=wl.dtype)
     ms_bwd, _, _ = timed(lambda: ops.spmm_bwd_(g, w, dYt, dX), 20, 5)
     alg_bwd = 4 * (g.num_nodes + 1) + 12 * g.nnz + dYt.numel() * es + dX.numel() * es
-    roofline["bwd"] = {"kernel": "spmm_rows_kernel<transposed>", "achieved": alg_bwd / (ms_bwd * 1e-3) / 1e9,
-                       "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"], "ms_per_launch": ms_bwd,
+    roofline["bwd"] = {"kernel": "transposed aggregation (autograd of robust_gcn.py:45-47)",
+                       "achieved": alg_bwd / (ms_bwd * 1e-3) / 1e9,
+                       "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"],
+                       "frac_nominal": alg_bwd / (ms_bwd * 1e-3) / 1e9 / NOMINAL_HBM_GBS, "ms_per_launch": ms_bwd,
                        "algorithmic_bytes": alg_bwd, "traffic": traffic_bwd}
     del X, Y, dYt, dX
     # GEMMs are the larger share of the step (about 60 %): the gcn3 projection forward [Nt x S, K = 7 * 2S] and its dX,
@@ -341,39 +514,140 @@ def run_b200(args):
     roofline["gemm"] = {
         "bound": "tensor", "unit": "TFLOP/s", "peak": peak_tf,
         "peak_how": "measured sustained cuBLAS bf16" + (" / 2 (tf32 operands)" if fp32 else ""),
-        "fwd": {"kernel": "gemm_x3_kernel (gcn3 projection, three tf32 products)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 projection)",
+        "fwd": {"kernel": "gemm_bc_kernel<NT, x3> (gcn3 projection, three tf32 products)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 projection)",
                 "shape_mnk": [B * wl.N, S, Kg], "ms_per_launch": ms_gf, "useful": useful / ms_gf / 1e9,
+                "frac_useful": useful / ms_gf / 1e9 / peak_tf,
                 "achieved": prod_f * useful / ms_gf / 1e9, "frac": prod_f * useful / ms_gf / 1e9 / peak_tf},
         "bwd_dx": {"kernel": "gemm_bc_kernel<NT> (gcn3 dX, tf32 + bf16 correction product)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 dX)",
                    "shape_mnk": [B * wl.N, Kg, S], "ms_per_launch": ms_gb, "useful": useful / ms_gb / 1e9,
+                   "frac_useful": useful / ms_gb / 1e9 / peak_tf,
                    "achieved": prod_b * useful / ms_gb / 1e9, "frac": prod_b * useful / ms_gb / 1e9 / peak_tf},
         "note": "all GEMMs of the step run under the board power cap (sw_power_cap, ~1000 W) and are L2->SM bound "
-                "(DESIGN.md 4.2); the fractions are against an un-capped cuBLAS figure"}
-    del Xg, Wg, dZg
+                "(DESIGN.md 4.2); the fractions are against an un-capped cuBLAS figure; frac counts executed tensor "
+                "work (3 / 2 products per fp32-grade product), frac_useful the fp32-grade product itself"}
+    return roofline
 
-    # (4) CPU baseline: the oracle port on a bounded sample of the same workload (rank 0, N=1 only)
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cb = args.cpu_batch
-        v, ms_cpu, cores = cpu_reference_arm(wl, cb, 3, 1)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms_cpu,
-               "sample": f"{cb} graphs x {wl.N} nodes per step (1+3 steps) of the same workload, dense fp32 adjacency"}
 
-    if rank == 0:
-        print(json.dumps({
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32" if wl.dtype == torch.float32 else "bf16", "data": "synthetic",
-            "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam (forward includes the CSR/CSC pack of dense A)",
-                       "graphs_per_gpu": B, "global_batch": world * B, "parallelism": f"dp{world}",
-                       "l2": "inputs (V %.2f GB) larger than L2" % (V.numel() * V.element_size() / 1e9),
-                       "features": "dense U[0,1)",
-                       "host_cpus_rank0": (f"{len(numa_cpus)} GPU-local cores" if numa_cpus else "unbound")},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "bow_features": bow,
-        }))
-    if world > 1:
-        dist.destroy_process_group()
+def run_cfg3(torch, synthetic, make_step, timed, exposed_allreduce, world, rank, dev, args):
+    """BASELINE configs[2]: S=512, bf16, 1000-node graphs, data parallel.  Weak: 128 graphs per GPU.  Strong: global
+    batch 1024 split over the ranks.  Each: ms/step (max over ranks), aggregate graphs/s, exposed all-reduce, peak memory."""
+    wl = synthetic.CONFIGS["cfg3"]
+    out = {"workload": "cfg3: S=512 bf16, 1000 nodes per graph, ~8 neighbours per edge type, dense features", "dtype": "bf16"}
+    for mode, Bg in (("weak", wl.B), ("strong", 1024 // world)):
+        torch.cuda.empty_cache()
+        torch.cuda.reset_peak_memory_stats()
+        model, step = make_step(wl)
+        out["allreduce_bytes"] = 4 * step.bucket.flat.numel()
+        V, A, y = synthetic.make_batch(wl, 4321 + rank, dev, B=Bg, feature_dtype=torch.bfloat16)
+        batch = {"textline_encoding": V, "adjacency_matrix": A, "node_label": y}
+        n = 5 if Bg <= 256 else 3
+        ms, launches, _ = timed(lambda: step.run_train_step(batch), n, 2)
+        ms_off = exposed_allreduce(step, lambda: step.run_train_step(batch), n)
+        out[mode] = {"graphs_per_gpu": Bg, "global_batch": Bg * world, "ms_per_step": ms,
+                     "graphs_per_s": world * Bg / (ms * 1e-3), "gpu_launches": launches,
+                     "exposed_allreduce_ms": None if ms_off is None else ms - ms_off,
+                     "peak_mem_GB": torch.cuda.max_memory_allocated() / 1e9, "scaling": mode}
+        if args.profile_step and args.profile_workload == "cfg3" and mode == "weak":
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
+            step.run_train_step(batch)
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
+        del model, step, V, A, y, batch
+    return out
+
+
+def run_cfg4(torch, synthetic, PackedGraphBatch, ops, make_step, timed, pk, dev, args):
+    """BASELINE configs[3]: ONE graph, 1M nodes, 6 edge types, degree 16 per type, fp32, no attention: full-batch
+    forward + backward.  The graph's feature slab does not fit in shared memory and the neighbours are uniform-random, so the
+    gather kernels run and the SpMM roofline is `bytes_gather`: every entry fetches its own F*s-byte row."""
+    wl = synthetic.CONFIGS["cfg4"]
+    torch.cuda.reset_peak_memory_stats()
+    model, step = make_step(wl)
+    V, edges, y = synthetic.make_edge_batch(wl, 1234, dev)
+    g = PackedGraphBatch.from_edges(edges, wl.B, wl.N, wl.num_edges)
+    del edges
+    batch = {"textline_encoding": V, "adjacency_matrix": g, "node_label": y}
+    ms, launches, _ = timed(lambda: step.run_train_step(batch), 3, 1)
+    if args.profile_step and args.profile_workload == "cfg4":
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step.run_train_step(batch)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+    out = {"workload": wl.name, "dtype": "f32", "ms_per_step": ms, "nodes_per_s": wl.N / (ms * 1e-3), "nnz": g.nnz,
+           "gpu_launches": launches, "peak_mem_GB": torch.cuda.max_memory_allocated() / 1e9,
+           "multi_gpu": "replicas only (one graph does not shard without a halo exchange)"}
+    del model, step, V, batch
+    torch.cuda.empty_cache()
+    S = wl.net_size
+    X = torch.randn(wl.N, S, device=dev)
+    Y = torch.empty(g.num_rows, S, device=dev)
+    w = g.edge_weights(0.3, seed=1, stream_id=1)
+    ms_f, _, _ = timed(lambda: ops.spmm_fwd_(g, w, X, Y), 5, 2)
+    dX = torch.empty(wl.N, S, device=dev)
+    ms_b, _, _ = timed(lambda: ops.spmm_bwd_(g, w, Y, dX), 5, 2)
+    kept = int((w != 0).sum())
+    idx = 4 * (g.num_rows + 1) + 8 * g.nnz
+    gather_f = idx + kept * S * 4 + Y.numel() * 4                 # every KEPT entry fetches one F*4-byte row of X
+    gather_b = 4 * (g.num_nodes + 1) + 12 * g.nnz + kept * S * 4 + dX.numel() * 4
+    tj = None
+    tpath = os.path.join(ROOT, "profiles", "spmm_traffic_cfg4.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+    out["spmm"] = {
+        "fwd": {"kernel": "spmm_nodes_kernel (L2 gather; the 1M x 1 KB slab does not fit shared memory)", "ms_per_launch": ms_f,
+                "bytes_gather": gather_f, "achieved": gather_f / (ms_f * 1e-3) / 1e9, "unit": "GB/s",
+                "frac": gather_f / (ms_f * 1e-3) / 1e9 / pk["hbm_gbs"], "frac_nominal": gather_f / (ms_f * 1e-3) / 1e9 / NOMINAL_HBM_GBS,
+                "traffic": tj["fwd"]["dram_bytes_per_launch"] if tj else None},
+        "bwd": {"kernel": "spmm_rows_kernel<transposed>", "ms_per_launch": ms_b, "bytes_gather": gather_b,
+                "achieved": gather_b / (ms_b * 1e-3) / 1e9, "unit": "GB/s", "frac": gather_b / (ms_b * 1e-3) / 1e9 / pk["hbm_gbs"],
+                "frac_nominal": gather_b / (ms_b * 1e-3) / 1e9 / NOMINAL_HBM_GBS,
+                "traffic": tj["bwd"]["dram_bytes_per_launch"] if tj else None},
+        "kept_entries": kept, "rule": "SURVEY 8d: cfg4 is judged on bytes_gather (no locality by construction); traffic = "
+                                      "ncu dram bytes of the same launch (profiles/), ~ bytes_gather x (1 - L2 hit)"}
+    return out
+
+
+def run_cfg5(torch, synthetic, GraphCNNDropEdge, PackedGraphBatch, dev, cpu_column):
+    """BASELINE configs[4]: eval forward at batch 64 over nodes per graph 100 -> 10k: latency p50 / p99 (one event pair per
+    call, a synchronize between calls as a serving loop would see) and graphs/s, edge-list pack included."""
+    wl0 = synthetic.Workload("cfg5", 64, 0)
+    torch.manual_seed(0)
+    model = GraphCNNDropEdge(wl0.input_dim, wl0.output_dim, wl0.num_edges, wl0.net_size, True).to(dev).eval()
+    ref = CpuReference(wl0) if cpu_column else None
+    rows = []
+    for N in (100, 200, 500, 1000, 2000, 5000, 10000):
+        torch.cuda.empty_cache()
+        V, edges, _ = synthetic.make_edge_batch(wl0, 77 + N, dev, B=64, N=N)
+
+        def fwd():
+            with torch.no_grad():
+                g = PackedGraphBatch.from_edges(edges, 64, N, wl0.num_edges, with_transpose=False)
+                return model([V, g])
+        for _ in range(2):
+            fwd()
+        lat = []
+        for _ in range(10 if N >= 5000 else 30):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fwd()
+            e1.record()
+            torch.cuda.synchronize()
+            lat.append(e0.elapsed_time(e1))
+        lat.sort()
+        row = {"N": N, "latency_p50_ms": lat[len(lat) // 2], "latency_p99_ms": lat[min(len(lat) - 1, int(0.99 * len(lat)))],
+               "graphs_per_s": 64 / (lat[len(lat) // 2] * 1e-3)}
+        if ref is not None and N <= 2000:
+            # SURVEY 8d: the reference's dense CPU forward at a batch the host can hold, normalised to graphs/s
+            Bc = 8 if N <= 500 else 2
+            row["cpu_graphs_per_s"] = ref.eval_forward(Bc, N)
+            row["cpu_batch"] = Bc
+        rows.append(row)
+        del V, edges
+    return {"workload": "cfg5: eval forward, batch 64, nodes per graph 100 -> 10 000 (edge-list pack + model)", "dtype": "f32",
+            "rows": rows, "cpu_kind": ref.kind if ref else None, "cpu_cores": ref.cores if ref else None}
 
 
 def main():

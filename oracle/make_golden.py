@@ -26,14 +26,9 @@ OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "g
 def import_reference():
     if not os.path.isdir(REF):
         raise SystemExit(f"{REF} not present: golden vectors can only be regenerated in the authoring container")
-    colorlog = types.ModuleType("colorlog")
-    colorlog.basicConfig = lambda **kw: None
-    sys.modules.setdefault("colorlog", colorlog)
-    decouple = types.ModuleType("decouple")
-    decouple.config = lambda key, default=None, **kw: default
-    sys.modules.setdefault("decouple", decouple)
-    if not hasattr(np, "float"):
-        np.float = float  # removed numpy alias used by textline_encoding.py:71
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    from oracle import ref_loader
+    ref_loader._shims()
     sys.path.insert(0, REF)
     from gnn.models import GraphCNNDropEdge  # noqa: E402
     from gnn.data_generator.data_collate.numpy_padding import NumpyPadding  # noqa: E402

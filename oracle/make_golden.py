@@ -331,6 +331,9 @@ def deep_rp_gcn_case(name, seed, B, N, in_dim, S, out_dim, L=6, deg=2.0):
     print(f"{name}: loss {float(loss):.6f}")
 
 
+REF32_THREADS = (16, 4, 1)      # OpenMP thread counts of the reference fp32 runs (summation orders)
+
+
 def production_case(GraphCNNDropEdge, name, seed, B, N, in_dim, S, out_dim, L=6, deg=8.0, w_rand_scale=None):
     """Production-shape vectors: the UNMODIFIED reference run in fp64 (the truth every tensor is judged
     against) and in fp32 (its own rounding noise, stored as one norm-wise number per tensor: SURVEY.md 8c's
@@ -371,18 +374,30 @@ def production_case(GraphCNNDropEdge, name, seed, B, N, in_dim, S, out_dim, L=6,
         return logits_eval, logits_train.detach(), loss.detach(), grads
 
     e64, t64, l64, g64 = run(torch.float64)
-    e32, t32, l32, g32 = run(torch.float32)
 
     def rel(a, b):
         return float((a.double() - b.double()).norm() / b.double().norm())
 
     out = {"meta": np.array(json.dumps(meta)), "logits_eval": e64.numpy(), "logits_train": t64.numpy(),
            "loss": l64.numpy()}
-    err32 = {"logits_eval": rel(e32, e64), "logits_train": rel(t32, t64), "loss": abs(float(l32) - float(l64)) / float(l64)}
     for k, g in g64.items():
-        idx = sample_index(k, g.numel(), seed)
-        out["grad/" + k] = g.reshape(-1)[idx].numpy()
-        err32["grad/" + k] = rel(g32[k].reshape(-1)[idx], g.reshape(-1)[idx])
+        out["grad/" + k] = g.reshape(-1)[sample_index(k, g.numel(), seed)].numpy()
+    # The reference's fp32 noise is ONE draw per summation order: the same unmodified fp32 run lands 1.1e-4 from fp64 with
+    # 16 OpenMP threads and 2.2-2.7e-4 with 1 / 4 (prod_s512_tame, gradients upstream of the attention).  The yardstick
+    # is therefore the per-tensor MAX over the thread counts below; every run is kept in err_ref32_runs.
+    runs32 = {}
+    threads0 = torch.get_num_threads()
+    for nt in REF32_THREADS:
+        torch.set_num_threads(nt)
+        e32, t32, l32, g32 = run(torch.float32)
+        r = {"logits_eval": rel(e32, e64), "logits_train": rel(t32, t64), "loss": abs(float(l32) - float(l64)) / float(l64)}
+        for k, g in g64.items():
+            idx = sample_index(k, g.numel(), seed)
+            r["grad/" + k] = rel(g32[k].reshape(-1)[idx], g.reshape(-1)[idx])
+        runs32[str(nt)] = r
+    torch.set_num_threads(threads0)
+    err32 = {k: max(r[k] for r in runs32.values()) for k in next(iter(runs32.values()))}
+    out["err_ref32_runs"] = np.array(json.dumps(runs32))
     # the reference's OWN bf16 run (torch.autocast on the CPU: nn.Linear / matmul / bmm in bf16), same masks: the
     # yardstick for our bf16 mode where 1e-2 is out of reach for any bf16 implementation (gradients upstream of the
     # unscaled softmax attention: dS = P (dP - D) cancels, a 4e-3 perturbation of its inputs moves them by O(1))

@@ -52,6 +52,10 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
     "grl_spmm_fwd_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,
                                     c_int, c_int, c_void_p]),
+    "grl_graphconv_fused_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_int,
+                                        c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+                                        c_int, c_uint32, c_float, c_void_p, c_uint64, c_uint64, c_void_p]),
+    "grl_graphconv_fused_set_mode": (c_int, [c_int]),
     "grl_spmm_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,
                              c_int, c_int, c_void_p]),
     "grl_spmm_set_tile_mode": (c_int, [c_int]),

@@ -278,6 +278,8 @@ static int g_x3_tmem_operand = 1; // 1 (-3, default): NT products run on the TME
                                   // arithmetic, half the shared-memory traffic: 5-9 % faster once the MMA issue loop stopped
                                   // being the bound (scripts/gemm_x3_ab.py); 0 (-4): the shared-memory-operand kernel here
 
+int gemm_x3_current_promo() { return g_x3_promo; }      // graphconv_fused.cu promotes its main product like the forward GEMMs
+
 template <bool kTN>
 static int ensure_smem_attr() {
     static bool attr_set = false;

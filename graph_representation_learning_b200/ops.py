@@ -537,8 +537,54 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
                seed: int = 0, stream_id: int = 0) -> torch.Tensor:
     """GraphConv over a virtual concat of node-feature tensors: aggregate over the (L+1) typed adjacencies,
     then one projection with K = (L+1)*F (reference robust_gcn.py:45-51), epilogue fused."""
+    if FusedGraphConv.enabled and not (torch.is_grad_enabled() and (h_weights.requires_grad or any(x.requires_grad for x in xs))):
+        out = graph_conv_fused(xs, g, w_edge, h_weights, bias, relu, p, mask, seed, stream_id)
+        if out is not None:
+            return out
     new_v = spmm_aggregate(g, w_edge, xs)
     return linear_act([new_v], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
+
+
+class FusedGraphConv:
+    """``enabled``: GraphConv layers that need no gradient (eval, ``KVInference``, cfg5) run ONE kernel
+    (csrc/graphconv_fused.cu): the aggregation of each (node tile, 32-column chunk, edge type) is produced straight into
+    the operand tile of the tcgen05 projection, so ``new_V`` ((L+1) x the layer input) is neither written nor re-read.
+    Training keeps the unfused pair: the weight gradient dW = new_V^T dZ needs ``new_V`` again."""
+    enabled = True
+
+
+def graph_conv_fused(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Tensor, h_weights: torch.Tensor,
+                     bias: Optional[torch.Tensor], relu=False, p: float = 0.0, mask: Optional[torch.Tensor] = None,
+                     seed: int = 0, stream_id: int = 0) -> Optional[torch.Tensor]:
+    """Forward-only fused GraphConv (grl_graphconv_fused_fwd).  Returns None for shapes / dtypes the kernel is not built
+    for (the caller then runs spmm_aggregate + linear_act): fp32 inputs under the "tf32x3" forward mode, one or two
+    inputs with widths that are multiples of 32, C <= 512."""
+    if not 1 <= len(xs) <= 2 or any(x.dtype != torch.float32 for x in xs) or GemmConfig.fp32_mode != "tf32x3":
+        return None
+    F_total = sum(x.shape[1] for x in xs)
+    K, C = h_weights.shape
+    if K != (g.L + 1) * F_total or any(x.shape[1] % 32 for x in xs) or C > 512 or g.L + 2 > 32 or g.num_nodes == 0:
+        return None
+    xs = [_tma_ready(x) for x in xs]
+    hi, lo = _prep_weight(h_weights.t(), torch.float32, _lib.GEMM_TF32X3)
+    if bias is not None and (bias.dtype != torch.float32 or not bias.is_contiguous()):
+        bias = bias.float().contiguous()
+    M = g.num_nodes
+    if mask is not None and (mask.dtype != torch.uint8 or mask.numel() != M * C or not mask.is_contiguous()):
+        raise _lib.GrlError("dropout mask must be contiguous uint8 [M, C]")
+    Y = torch.empty(M, C, dtype=torch.float32, device=xs[0].device)
+    flags = (_lib.EPI_BIAS if bias is not None else 0) | _act_flag(relu) | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+    x1 = xs[1] if len(xs) == 2 else None
+    rc = _lib.load().grl_graphconv_fused_fwd(
+        g.rowptr.data_ptr(), g.col.data_ptr(), w_edge.data_ptr(), xs[0].data_ptr(), xs[0].stride(0), xs[0].shape[1],
+        _lib.ptr(x1), x1.stride(0) if x1 is not None else 0, x1.shape[1] if x1 is not None else 0,
+        hi.data_ptr(), lo.data_ptr(), hi.stride(0), _lib.ptr(bias), Y.data_ptr(), Y.stride(0), g.B, g.N, g.L, C,
+        flags, float(p), _lib.ptr(mask), int(seed) & (2**64 - 1), int(stream_id), _lib.stream_ptr(Y.device))
+    if rc == _lib.GRL_E_UNSUP:
+        return None
+    _lib.check(rc, "grl_graphconv_fused_fwd")
+    _lib.count_launch(1)
+    return Y
 
 
 class AttentionConfig:

@@ -148,6 +148,31 @@ int grl_spmm_fwd_stream(const int32_t* nodeinfo, const void* ew, const void* X, 
                         int dtype, int B, int N, int L, int F, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Fused GraphConv forward (SURVEY.md K5 / 8b gcn_graphconv_fused_fwd): aggregation producer -> tcgen05 projection;
+ * new_V = matmul(A', V) never reaches HBM.  Replaces GraphConv.forward  gnn/models/networks/robust_gcn.py:45-51
+ * (aggregate, then ONE projection with K = (L+1)F) together with its bias / ReLU / dropout epilogue
+ * (drop_robust_gcn.py:76-77).  fp32 only; same arithmetic as grl_spmm_fwd + grl_gemm_nt(TF32X3) with the K-blocks
+ * visited in a different order (agrees to fp32 rounding, ~1e-7 norm-wise).
+ *   Y[n, 0:C] = epilogue( sum_t sum_f ( sum_{e in row (n, t)} w[e] X[base(n) + col[e], f] ) W[t*F + f, 0:C] + bias )
+ * X = the virtual concat [X0 | X1] of one or two [B*N, F_k] inputs (F = F0 + F1, F1 may be 0; multiples of 32).
+ * W_hi / W_lo: the K-major [C, (L+1)*F] split of h_weights^T written by grl_split_tf32 (pitch ldw).
+ * CTA clusters of ceil(C / 128) share a 128-row node tile (C <= 512); the aggregated operand tile is produced once per
+ * cluster and broadcast through distributed shared memory.  The graph's [N, 32-column] feature slab is staged in shared
+ * memory by TMA when it fits (N <~ 850), otherwise rows are gathered from global memory / L2.
+ * Returns GRL_E_UNSUP for shapes it is not built for -- the caller then runs the unfused pair.
+ * ------------------------------------------------------------------------------------------ */
+int grl_graphconv_fused_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
+                            const float* X0, int64_t ldx0, int F0, const float* X1, int64_t ldx1, int F1,
+                            const float* W_hi, const float* W_lo, int64_t ldw, const float* bias,
+                            float* Y, int64_t ldy, int B, int N, int L, int C,
+                            uint32_t flags, float p, const uint8_t* mask, uint64_t seed, uint64_t stream_id,
+                            void* stream);
+
+/* Producer selection of grl_graphconv_fused_fwd (host call, process-global; experiments and tests):
+ * 0 = auto, 1 = shared-memory slab (GRL_E_UNSUP when it does not fit), 2 = direct gather from global memory. */
+int grl_graphconv_fused_set_mode(int mode);
+
+/* ------------------------------------------------------------------------------------------
  * Segmented SpMM (aggregation).  Replaces torch.matmul(A, V.view(-1,N,F)).view(-1,N,(L+1)F)
  * gnn/models/networks/robust_gcn.py:45-47.
  *   Y[r, 0:F] = sum_{e in row r} w[e] * X[base(r) + col[e], 0:F]      r in [0, R)

@@ -20,7 +20,10 @@
 // fence.acq_rel.cluster + release-arrives spent its time in MEMBAR / CCTL.IVALL, which also flushed the cached edge
 // lists out of L1 every K-block).  An operand slot is reused when the splitters of ALL CTAs have read it (remote
 // arrives on `a_free`).
-// Register budget by role (setmaxnreg per warpgroup): TMA / MMA / slab warps 40, gather 48, splitter 88, drain 128.
+// Register budget by role (setmaxnreg per warpgroup, 640 threads launched at 96): TMA / MMA / slab warps 40, splitter 88,
+// drain 208 (FOUR warps holding 128 promoted columns each: at the pace the producer sets, half the drain warps of the
+// plain GEMM are enough, and their registers go to the producer), gather 72 (two rows in flight per lane group: the
+// gather warps were stalled on dependency latency 85 % of the time with one).
 //
 // Arithmetic = the unfused path's (CSR-order fp32 aggregation, three-product tf32 GEMM with promotion), but the K-blocks
 // are visited in (kc, t) instead of (t, kc) order: results agree to fp32 rounding (~1e-7), not bit for bit.
@@ -36,12 +39,13 @@ struct FusedCfg {
     static constexpr int B_STAGE_BYTES = 2 * TILE_BYTES;            // B_hi | B_lo
     static constexpr int MAX_A = 3, MAX_B = 4;
     static constexpr int TA_STAGES = 2, TA_COL0 = 384, TA_COLS = 64;
-    static constexpr int EPI_BYTES = X3Cfg::EPI_BYTES;
+    static constexpr int EPI_BYTES = 4 * 32 * X3Cfg::EPI_PITCH * 4;   // one 32 x 16 transposition buffer per drain warp
     static constexpr int BAR_BYTES = 256;
     static constexpr int GATHER_WARPS = 8;
-    static constexpr int THREADS = 768;                             // 6 warpgroups: control | splitter | drain x2 | gather x2
+    static constexpr int THREADS = 640;                             // 5 warpgroups: control | splitter | drain | gather x2
     static constexpr int TMEM_COLS = 512;
-    static constexpr int DRAIN_WARPS = X3Cfg::DRAIN_WARPS;
+    static constexpr int DRAIN_WARPS = 4;                           // one per TMEM lane quarter, all 128 columns
+    static constexpr int GATHER_WARP0 = 12;
 };
 
 struct FusedParams {
@@ -230,7 +234,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
         }
     } else if (warp < 8) {
         // ===================================================================== operand splitter (warps 4..7)
-        setmaxnreg_inc<88>();
+        setmaxnreg_dec<88>();
         const int quarter = warp & 3, row = quarter * 32 + lane;
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + Cfg::TA_COL0;
         Ring ra(p.n_a);
@@ -267,60 +271,85 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
                 ra.next();
             }
         }
-    } else if (warp < 16) {
-        // ===================================================================== drain + epilogue (warps 8..15)
-        setmaxnreg_inc<128>();
-        const int quarter = warp & 3, half = (warp - 8) >> 2;
-        const int colbase = half * X3Cfg::DRAIN_COLS;
-        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + colbase;
+    } else if (warp < 12) {
+        // ===================================================================== drain + epilogue (warps 8..11)
+        setmaxnreg_inc<208>();
+        const int quarter = warp & 3;
+        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
         float* my_buf = epi_buf + (warp - 8) * 32 * X3Cfg::EPI_PITCH;
         int cg = 0;
         for (int t = t_first; t < p.n_mtiles; t += t_step) {
             const int b = t / p.tiles_per_graph, q = t - b * p.tiles_per_graph;
             const int m0 = b * p.N + q * Cfg::BLOCK_M;
-            float acc[X3Cfg::DRAIN_COLS];
+            float acc0[64], acc1[64];               // columns [0, 64) and [64, 128) of this lane's row
 #pragma unroll
-            for (int x = 0; x < X3Cfg::DRAIN_COLS; ++x) acc[x] = 0.0f;
+            for (int x = 0; x < 64; ++x) { acc0[x] = 0.0f; acc1[x] = 0.0f; }
+            auto add_from = [&](uint32_t col0, bool last_of_buffer, uint64_t* release) {
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + col0, r0);
+                tmem_ld_32x32(lane_base + col0 + 32, r1);
+                tmem_ld_wait();
+#pragma unroll
+                for (int x = 0; x < 32; ++x) acc0[x] += __uint_as_float(r0[x]);
+#pragma unroll
+                for (int x = 0; x < 32; ++x) acc0[32 + x] += __uint_as_float(r1[x]);
+                tmem_ld_32x32(lane_base + col0 + 64, r0);
+                tmem_ld_32x32(lane_base + col0 + 96, r1);
+                tmem_ld_wait();
+                if (last_of_buffer) {
+                    tc_fence_before_sync();
+                    mbar_arrive(release);
+                }
+#pragma unroll
+                for (int x = 0; x < 32; ++x) acc1[x] += __uint_as_float(r0[x]);
+#pragma unroll
+                for (int x = 0; x < 32; ++x) acc1[32 + x] += __uint_as_float(r1[x]);
+            };
             for (int c = 0; c < n_chunks; ++c, ++cg) {
                 const int buf = cg & 1;
                 mbar_wait(&acc_full[buf], (cg >> 1) & 1);
                 tc_fence_after_sync();
-                uint32_t r0[32], r1[32];
-                tmem_ld_32x32(lane_base + buf * 128, r0);
-                tmem_ld_32x32(lane_base + buf * 128 + 32, r1);
-                tmem_ld_wait();
-                tc_fence_before_sync();
-                mbar_arrive(&acc_empty[buf]);
-#pragma unroll
-                for (int x = 0; x < 32; ++x) acc[x] += __uint_as_float(r0[x]);
-#pragma unroll
-                for (int x = 0; x < 32; ++x) acc[32 + x] += __uint_as_float(r1[x]);
+                add_from(buf * 128, true, &acc_empty[buf]);
             }
-            {
-                uint32_t r0[32], r1[32];
-                tmem_ld_32x32(lane_base + 256, r0);
-                tmem_ld_32x32(lane_base + 256 + 32, r1);
-                tmem_ld_wait();
-                tc_fence_before_sync();
-                mbar_arrive(small_empty);
-#pragma unroll
-                for (int x = 0; x < 32; ++x) acc[x] += __uint_as_float(r0[x]);
-#pragma unroll
-                for (int x = 0; x < 32; ++x) acc[32 + x] += __uint_as_float(r1[x]);
-            }
+            add_from(256, true, small_empty);
             GemmParams gq = p.g;
             gq.M = b * p.N + min(p.N, (q + 1) * Cfg::BLOCK_M);       // rows of THIS graph only
-            if (m0 + quarter * 32 < gq.M && n0 + colbase < gq.N)
-                epilogue_from_regs(gq, acc, my_buf, m0 + quarter * 32, n0 + colbase, lane);
+            if (m0 + quarter * 32 < gq.M) {
+                if (n0 < gq.N) epilogue_from_regs(gq, acc0, my_buf, m0 + quarter * 32, n0, lane);
+                if (n0 + 64 < gq.N) epilogue_from_regs(gq, acc1, my_buf, m0 + quarter * 32, n0 + 64, lane);
+            }
         }
     } else {
-        // ===================================================================== aggregation producer (warps 16..23)
-        setmaxnreg_dec<48>();
-        const int gw = warp - 16, grp = lane >> 3, l8 = lane & 7;
-        const int gtid = static_cast<int>(threadIdx.x) - 16 * 32;
+        // ===================================================================== aggregation producer (warps 12..19)
+        setmaxnreg_dec<72>();
+        const int gw = warp - Cfg::GATHER_WARP0, grp = lane >> 3, l8 = lane & 7;
+        const int gtid = static_cast<int>(threadIdx.x) - Cfg::GATHER_WARP0 * 32;
         const uint32_t slab_lane = base_u32 + p.off_slab + l8 * 16;
         Ring ra(p.n_a);
         uint32_t slab_ph = 0;
+        uint32_t peer_base[4];              // shared::cluster address of `tiles` in every CTA of the cluster (cs is 1, 2 or 4)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) peer_base[r] = mapa_cluster(base_u32, static_cast<uint32_t>(r < cs ? r : 0));
+        // Work units of one (input, 32-column chunk): (edge type ty, pass) -- a lane group of 8 aggregates row
+        // lr = gw*4 + grp + 32*pass of my share for type ty; a K-block is n_pass consecutive units.  Units are processed
+        // in PAIRS (two independent rows per lane group in flight).  The edge list of a unit (<= 16 entries: lane l8
+        // holds entries l8 and l8 + 8) is fetched one pair ahead and broadcast inside the group with shuffles, so the
+        // latency of col / w never sits in front of the gather; longer typed rows finish in a plain loop.
+        const int n_pass = rows_share / 32, pass_shift = n_pass == 4 ? 2 : (n_pass == 2 ? 1 : 0), units = Lp1 * n_pass;
+        struct Pre { int cnt, c0, c1; float w0, w1; };
+        auto unit_e0 = [&](int u) { return rp_s[(gw * 4 + grp + 32 * (u & (n_pass - 1))) * rp_pitch + (u >> pass_shift)]; };
+        auto prefetch = [&](int u) -> Pre {
+            Pre x;
+            x.cnt = 0; x.c0 = 0; x.c1 = 0; x.w0 = 0.0f; x.w1 = 0.0f;
+            if (u < units) {
+                const int ty = u >> pass_shift, lr = gw * 4 + grp + 32 * (u & (n_pass - 1));
+                const int e0 = rp_s[lr * rp_pitch + ty];
+                x.cnt = rp_s[lr * rp_pitch + ty + 1] - e0;
+                if (l8 < x.cnt) { x.c0 = __ldg(p.col + e0 + l8); x.w0 = __ldg(p.w + e0 + l8); }
+                if (l8 + 8 < x.cnt) { x.c1 = __ldg(p.col + e0 + l8 + 8); x.w1 = __ldg(p.w + e0 + l8 + 8); }
+            }
+            return x;
+        };
         for (int t = t_first; t < p.n_mtiles; t += t_step) {
             const int b = t / p.tiles_per_graph, q = t - b * p.tiles_per_graph;
             const int n_valid = min(Cfg::BLOCK_M, p.N - q * Cfg::BLOCK_M);
@@ -333,6 +362,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
                 rp_s[idx] = row < n_valid ? __ldg(p.rowptr + (node0 + row) * Lp1 + k) : 0;
             }
             named_bar_sync(1, Cfg::GATHER_WARPS * 32);
+            Pre nxa = prefetch(0), nxb = prefetch(1);
             for (int seg = 0; seg < 2; ++seg) {
                 const int Fk = seg ? p.F1 : p.F0;
                 const float* Xg = (seg ? p.X1 : p.X0) + static_cast<int64_t>(b) * p.N * (seg ? p.ldx1 : p.ldx0) + l8 * 4;
@@ -342,45 +372,83 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
                         mbar_wait(slab_full, slab_ph);
                         slab_ph ^= 1u;
                     }
-                    for (int ty = 0; ty < Lp1; ++ty) {
-                        mbar_wait(&a_free[ra.s], ra.ph ^ 1u);
-                        if (gw == 0 && lane == 0) mbar_expect_tx(&agg_bar[ra.s], Cfg::TILE_BYTES);
-                        const uint32_t ta = smem_u32(tile_a(ra.s)), ab = smem_u32(&agg_bar[ra.s]);
-                        for (int lr = gw * 4 + grp; lr < rows_share; lr += Cfg::GATHER_WARPS * 4) {
-                            const int e0 = rp_s[lr * rp_pitch + ty], e1 = rp_s[lr * rp_pitch + ty + 1];
-                            float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                            auto fetch = [&](int c) -> float4 {
-                                if (kSlab) {
-                                    float4 v;
-                                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                                                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                                                 : "r"(slab_lane + static_cast<uint32_t>(c) * 128u));
-                                    return v;
-                                }
-                                return __ldg(reinterpret_cast<const float4*>(Xg + static_cast<int64_t>(c) * ldx + kc * Cfg::BLOCK_K));
-                            };
-                            int e = e0;
-                            for (; e + 4 <= e1; e += 4) {
-                                const int c0 = __ldg(p.col + e), c1 = __ldg(p.col + e + 1), c2 = __ldg(p.col + e + 2), c3 = __ldg(p.col + e + 3);
-                                const float w0 = __ldg(p.w + e), w1 = __ldg(p.w + e + 1), w2 = __ldg(p.w + e + 2), w3 = __ldg(p.w + e + 3);
-                                const float4 v0 = fetch(c0), v1 = fetch(c1), v2 = fetch(c2), v3 = fetch(c3);
-                                acc.x = fmaf(w0, v0.x, acc.x); acc.y = fmaf(w0, v0.y, acc.y); acc.z = fmaf(w0, v0.z, acc.z); acc.w = fmaf(w0, v0.w, acc.w);
-                                acc.x = fmaf(w1, v1.x, acc.x); acc.y = fmaf(w1, v1.y, acc.y); acc.z = fmaf(w1, v1.z, acc.z); acc.w = fmaf(w1, v1.w, acc.w);
-                                acc.x = fmaf(w2, v2.x, acc.x); acc.y = fmaf(w2, v2.y, acc.y); acc.z = fmaf(w2, v2.z, acc.z); acc.w = fmaf(w2, v2.w, acc.w);
-                                acc.x = fmaf(w3, v3.x, acc.x); acc.y = fmaf(w3, v3.y, acc.y); acc.z = fmaf(w3, v3.z, acc.z); acc.w = fmaf(w3, v3.w, acc.w);
-                            }
-                            for (; e < e1; ++e) {
-                                const int c0 = __ldg(p.col + e);
-                                const float w0 = __ldg(p.w + e);
-                                const float4 v0 = fetch(c0);
-                                acc.x = fmaf(w0, v0.x, acc.x); acc.y = fmaf(w0, v0.y, acc.y); acc.z = fmaf(w0, v0.z, acc.z); acc.w = fmaf(w0, v0.w, acc.w);
-                            }
-                            // K-major SWIZZLE_128B tile: 16-byte chunk c of row r sits at c ^ (r & 7)
-                            const int row = rank * rows_share + lr;
-                            const uint32_t dst = ta + row * 128 + ((l8 ^ (row & 7)) << 4);
-                            for (int r = 0; r < cs; ++r) st_async_v4(mapa_cluster(dst, r), acc, mapa_cluster(ab, r));
+                    auto fetch = [&](int c) -> float4 {
+                        if (kSlab) {
+                            float4 v;
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                                         : "r"(slab_lane + static_cast<uint32_t>(c) * 128u));
+                            return v;
                         }
-                        ra.next();
+                        return __ldg(reinterpret_cast<const float4*>(Xg + static_cast<int64_t>(c) * ldx + kc * Cfg::BLOCK_K));
+                    };
+                    auto fma4 = [](float4& a, float w, const float4& v) {
+                        a.x = fmaf(w, v.x, a.x); a.y = fmaf(w, v.y, a.y); a.z = fmaf(w, v.z, a.z); a.w = fmaf(w, v.w, a.w);
+                    };
+                    auto begin_kblock = [&](const Ring& r) {
+                        mbar_wait(&a_free[r.s], r.ph ^ 1u);
+                        if (gw == 0 && lane == 0) mbar_expect_tx(&agg_bar[r.s], Cfg::TILE_BYTES);
+                    };
+                    auto store_row = [&](const Ring& r, int pass, const float4& acc) {
+                        // K-major SWIZZLE_128B tile: 16-byte chunk c of row r sits at c ^ (r & 7)
+                        const int row = rank * rows_share + gw * 4 + grp + 32 * pass;
+                        const uint32_t dst = r.s * Cfg::TILE_BYTES + row * 128 + ((l8 ^ (row & 7)) << 4);
+                        const uint32_t ab = p.off_bars + (8 + r.s) * 8;                 // agg_bar[r.s]
+                        st_async_v4(peer_base[0] + dst, acc, peer_base[0] + ab);
+                        if (cs > 1) st_async_v4(peer_base[1] + dst, acc, peer_base[1] + ab);
+                        if (cs > 2) {
+                            st_async_v4(peer_base[2] + dst, acc, peer_base[2] + ab);
+                            st_async_v4(peer_base[3] + dst, acc, peer_base[3] + ab);
+                        }
+                    };
+                    for (int u = 0; u < units; u += 2) {
+                        const Pre ca = nxa, cb = nxb;
+                        const int un = u + 2 < units ? u + 2 : 0;             // wraps to the next chunk's first pair (same rows)
+                        nxa = prefetch(un);
+                        nxb = prefetch(un + 1);
+                        const bool has_b = u + 1 < units;
+                        const int pass_a = u & (n_pass - 1), pass_b = (u + 1) & (n_pass - 1);
+                        Ring rb = ra;                                        // unit b: the same K-block, or (n_pass == 1) the next
+                        if (n_pass == 1) rb.next();
+                        if (pass_a == 0) begin_kblock(ra);
+                        if (has_b && pass_b == 0) begin_kblock(rb);
+                        float4 acc_a = make_float4(0.0f, 0.0f, 0.0f, 0.0f), acc_b = acc_a;
+                        const int kmax = __reduce_max_sync(0xffffffffu, min(max(ca.cnt, cb.cnt), 16));
+                        const int src0 = lane & 24;
+#pragma unroll 1
+                        for (int k = 0; k < kmax; k += 2) {       // entries past a row's end carry w = 0 (col = 0: a valid row)
+                            const int s0 = src0 | (k & 7), s1 = s0 + 1;
+                            const bool lo = k < 8;
+                            const int ca0 = __shfl_sync(0xffffffffu, lo ? ca.c0 : ca.c1, s0);
+                            const int cb0 = __shfl_sync(0xffffffffu, lo ? cb.c0 : cb.c1, s0);
+                            const int ca1 = __shfl_sync(0xffffffffu, lo ? ca.c0 : ca.c1, s1);
+                            const int cb1 = __shfl_sync(0xffffffffu, lo ? cb.c0 : cb.c1, s1);
+                            const float4 va0 = fetch(ca0), vb0 = fetch(cb0), va1 = fetch(ca1), vb1 = fetch(cb1);
+                            const float wa0 = __shfl_sync(0xffffffffu, lo ? ca.w0 : ca.w1, s0);
+                            const float wb0 = __shfl_sync(0xffffffffu, lo ? cb.w0 : cb.w1, s0);
+                            const float wa1 = __shfl_sync(0xffffffffu, lo ? ca.w0 : ca.w1, s1);
+                            const float wb1 = __shfl_sync(0xffffffffu, lo ? cb.w0 : cb.w1, s1);
+                            fma4(acc_a, wa0, va0);
+                            fma4(acc_b, wb0, vb0);
+                            fma4(acc_a, wa1, va1);
+                            fma4(acc_b, wb1, vb1);
+                        }
+                        if (ca.cnt > 16) {                                    // typed rows longer than 16 entries
+                            const int e0 = unit_e0(u);
+                            for (int e = e0 + 16; e < e0 + ca.cnt; ++e) fma4(acc_a, __ldg(p.w + e), fetch(__ldg(p.col + e)));
+                        }
+                        if (cb.cnt > 16) {
+                            const int e0 = unit_e0(u + 1);
+                            for (int e = e0 + 16; e < e0 + cb.cnt; ++e) fma4(acc_b, __ldg(p.w + e), fetch(__ldg(p.col + e)));
+                        }
+                        store_row(ra, pass_a, acc_a);
+                        if (has_b) store_row(rb, pass_b, acc_b);
+                        if (n_pass == 1) {
+                            ra.next();
+                            if (has_b) ra.next();
+                        } else if (pass_b == n_pass - 1) {
+                            ra.next();
+                        }
                     }
                     if (kSlab) {
                         __syncwarp();                           // every lane's slab reads of this chunk are in registers

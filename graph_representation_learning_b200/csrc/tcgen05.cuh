@@ -46,6 +46,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// The same with a sleep between polls: for roles that wait LONG next to warps that need the issue slots (a spinning
+// try_wait loop is ~10 instructions every ~50 cycles per waiting warp).
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(ns);
+        if (clock64() - t0 > 4000000000LL) __trap();
+    }
+}
+
 // ------------------------------------------------------------------------------------------ fences
 __device__ __forceinline__ void fence_proxy_async_smem() {  // generic-proxy smem writes -> visible to TMA / tcgen05
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -537,7 +537,7 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
                seed: int = 0, stream_id: int = 0) -> torch.Tensor:
     """GraphConv over a virtual concat of node-feature tensors: aggregate over the (L+1) typed adjacencies,
     then one projection with K = (L+1)*F (reference robust_gcn.py:45-51), epilogue fused."""
-    if FusedGraphConv.enabled and not (torch.is_grad_enabled() and (h_weights.requires_grad or any(x.requires_grad for x in xs))):
+    if FusedGraphConv.wants(g, h_weights.shape[1]) and not (torch.is_grad_enabled() and (h_weights.requires_grad or any(x.requires_grad for x in xs))):
         out = graph_conv_fused(xs, g, w_edge, h_weights, bias, relu, p, mask, seed, stream_id)
         if out is not None:
             return out
@@ -546,11 +546,25 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
 
 
 class FusedGraphConv:
-    """``enabled``: GraphConv layers that need no gradient (eval, ``KVInference``, cfg5) run ONE kernel
+    """GraphConv layers that need no gradient (eval, ``KVInference``, cfg5) can run as ONE kernel
     (csrc/graphconv_fused.cu): the aggregation of each (node tile, 32-column chunk, edge type) is produced straight into
-    the operand tile of the tcgen05 projection, so ``new_V`` ((L+1) x the layer input) is neither written nor re-read.
-    Training keeps the unfused pair: the weight gradient dW = new_V^T dZ needs ``new_V`` again."""
-    enabled = True
+    the operand tile of the tcgen05 projection, so ``new_V`` ((L+1) x the layer input) is neither written nor re-read
+    (1.84 GB of HBM traffic per cfg2 layer).  Training keeps the unfused pair: dW = new_V^T dZ needs ``new_V`` again.
+
+    ``enabled``: True = every supported layer, False = never, "auto" (default) = when the layer is at most ``max_waves``
+    waves of CTA clusters.  Measured (profiles/r02_s29_fused_*.jsonl): the aggregation producer has 8 of the SM's warps and is
+    bound by its own dependent instruction stream, so a full-machine layer runs 1.33x the unfused pair's time (1.23 vs
+    0.92 ms at cfg2's gcn1) while small batches, which are launch-bound, gain (whole eval forward 64 x 100 nodes:
+    0.99 -> 0.81 ms; 8 x 200: 0.92 -> 0.81 ms)."""
+    enabled = "auto"
+    max_waves = 1.0
+
+    @classmethod
+    def wants(cls, g: PackedGraphBatch, C: int) -> bool:
+        if cls.enabled is True or cls.enabled is False:
+            return cls.enabled
+        ctas = g.B * ((g.N + 127) // 128) * (1 if C <= 128 else (2 if C <= 256 else 4))
+        return ctas <= cls.max_waves * 148
 
 
 def graph_conv_fused(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Tensor, h_weights: torch.Tensor,

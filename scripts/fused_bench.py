@@ -31,9 +31,32 @@ def main():
     ap.add_argument("--shapes", default="256x500x256x256,256x500x512x256,64x500x256x256,64x1000x256x256,64x2000x256x256")
     ap.add_argument("--degree", type=float, default=8.0)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--model", default="", help="comma list of BxN: time the whole eval forward (S=256, in_dim 4369) fused vs unfused")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     lib = _lib.load()
+    if args.model:
+        from graph_representation_learning_b200 import GraphCNNDropEdge
+        torch.manual_seed(0)
+        model = GraphCNNDropEdge(4369, 53, 6, net_size=256).to(dev).eval()
+        for shp in args.model.split(","):
+            B, N = (int(v) for v in shp.split("x"))
+            wl = synthetic.Workload("bench", B, N, input_dim=4369, degree=args.degree)
+            V, edges, _ = synthetic.make_edge_batch(wl, 7, dev)
+            res = {"model_eval": {"B": B, "N": N}}
+            outs = {}
+            for on in (False, True):
+                ops.FusedGraphConv.enabled = on
+
+                def fwd():
+                    with torch.no_grad():
+                        return model([V, PackedGraphBatch.from_edges(edges, B, N, 6, with_transpose=False)])
+                outs[on] = fwd()
+                res["fused_ms" if on else "unfused_ms"] = round(timed(fwd, args.iters), 4)
+            ops.FusedGraphConv.enabled = "auto"
+            res["logits_rel_diff"] = float((outs[True].double() - outs[False].double()).norm() / outs[False].double().norm())
+            print(json.dumps(res), flush=True)
+        return
     for shp in args.shapes.split(","):
         B, N, F, C = (int(v) for v in shp.split("x"))
         wl = synthetic.Workload("bench", B, N, input_dim=8, degree=args.degree)

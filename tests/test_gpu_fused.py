@@ -120,7 +120,7 @@ def test_eval_forward_fused_equals_unfused_and_reference(dev, name):
                 outs[on] = model([V, A])
             outs[("launches", on)] = _lib.launches() - n0
         finally:
-            ops.FusedGraphConv.enabled = True
+            ops.FusedGraphConv.enabled = "auto"
     assert outs[("launches", True)] < outs[("launches", False)], "the fused path did not run"
     assert rel_err(outs[True], outs[False]) < 1e-5
     assert rel_err(outs[True].cpu(), c["logits_eval"]) < 1e-5

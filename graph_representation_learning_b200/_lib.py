@@ -50,6 +50,10 @@ SIGNATURES = {
     "grl_dropedge_weights": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_uint64, c_uint64, c_void_p, c_void_p]),
     "grl_dropedge_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float, c_uint64, c_uint64,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    "grl_stream_from_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p,
+                                        c_void_p]),
+    "grl_csc_typed_regroup": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                      c_void_p]),
     "grl_spmm_fwd_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,
                                     c_int, c_int, c_void_p]),
     "grl_graphconv_fused_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_int,

@@ -341,6 +341,60 @@ __global__ void __launch_bounds__(256) csc_rank_kernel(const int32_t* __restrict
     }
 }
 
+// Typed transpose: regroup every CSC column (entries sorted by CSR row r = (i, t)) by edge type, keeping the i order
+// inside a type -- the CSR of the transposed typed adjacency A_t^T, rows (j, t), over the same node numbering.  One
+// warp per column, two passes over its entries in chunks of 32: per-type totals (lane t keeps the count of type t; an
+// exclusive warp scan gives the typed row pointers), then a stable placement by ballot ranks.  (A first version ranked
+// every entry against all others of the column, O(d^2) with a modulo each: 0.45 ms at cfg2 against 0.03 ms.)
+__global__ void __launch_bounds__(256) csc_typed_kernel(const int32_t* __restrict__ colptr, int64_t n_cols,
+                                                        const int32_t* __restrict__ rowidx, const int32_t* __restrict__ perm,
+                                                        int Lp1, int N, int32_t* __restrict__ t_rowptr,
+                                                        int32_t* __restrict__ t_col, int32_t* __restrict__ t_perm) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t c = warp; c < n_cols; c += n_warps) {
+        const int32_t s = colptr[c], d = colptr[c + 1] - s;
+        int32_t total = 0;                                  // lane t: entries of type t in this column
+        for (int32_t a0 = 0; a0 < d; a0 += 32) {
+            const int32_t a = a0 + lane;
+            const int ta = a < d ? rowidx[s + a] % Lp1 : -1;
+            for (int t = 0; t < Lp1; ++t) {
+                const uint32_t m = __ballot_sync(0xffffffffu, ta == t);
+                if (lane == t) total += __popc(m);
+            }
+        }
+        int32_t off = total;                                // inclusive scan over the types, then made exclusive
+#pragma unroll
+        for (int k = 1; k < 32; k <<= 1) {
+            const int32_t v = __shfl_up_sync(0xffffffffu, off, k);
+            if (lane >= k) off += v;
+        }
+        off -= total;
+        if (lane < Lp1) t_rowptr[c * Lp1 + lane] = s + off;
+        if (c == n_cols - 1 && lane == 0) t_rowptr[n_cols * Lp1] = s + d;
+        const int32_t node_base = static_cast<int32_t>((c / N) * N);
+        int32_t placed = 0;                                 // lane t: entries of type t already placed
+        for (int32_t a0 = 0; a0 < d; a0 += 32) {
+            const int32_t a = a0 + lane;
+            const int32_t r = a < d ? rowidx[s + a] : 0;
+            const int ta = a < d ? r % Lp1 : -1;
+            int32_t pos = 0;
+            for (int t = 0; t < Lp1; ++t) {
+                const uint32_t m = __ballot_sync(0xffffffffu, ta == t);
+                const int32_t base = __shfl_sync(0xffffffffu, off + placed, t);
+                if (ta == t) pos = s + base + __popc(m & lt);
+                if (lane == t) placed += __popc(m);
+            }
+            if (a < d) {
+                t_col[pos] = r / Lp1 - node_base;
+                t_perm[pos] = perm[s + a];
+            }
+        }
+    }
+}
+
 static inline int grid_for(int64_t work_items, int threads, int items_per_thread = 1) {
     int64_t blocks = (work_items + static_cast<int64_t>(threads) * items_per_thread - 1) /
                      (static_cast<int64_t>(threads) * items_per_thread);
@@ -567,6 +621,18 @@ static int csr_transpose_impl(const int32_t* rowptr, const int32_t* col, int64_t
     GRL_LAUNCH_CHECK("csc_scatter_kernel");
     csc_rank_kernel<<<grid_for(n_cols * 32, 256), 256, 0, st>>>(colptr, n_cols, tmp_e, tmp_r, rowidx, perm);
     GRL_LAUNCH_CHECK("csc_rank_kernel");
+    return 0;
+}
+
+extern "C" int grl_csc_typed_regroup(const int32_t* colptr, const int32_t* rowidx, const int32_t* perm, int B, int N, int L,
+                                    int32_t* t_rowptr, int32_t* t_col, int32_t* t_perm, void* stream) {
+    GRL_CHECK_ARG(colptr && rowidx && perm && t_rowptr && t_col && t_perm, GRL_E_BADARG, "grl_csc_typed_regroup: null pointer");
+    GRL_CHECK_ARG(B > 0 && N > 0 && L > 0 && L + 1 <= 31, GRL_E_BADARG, "grl_csc_typed_regroup: bad shape (L + 1 must be <= 31)");
+    const int64_t n_cols = static_cast<int64_t>(B) * N;
+    GRL_CHECK_ARG(n_cols * (L + 1) < (1LL << 31), GRL_E_BADARG, "grl_csc_typed_regroup: row count overflows int32");
+    csc_typed_kernel<<<grid_for(n_cols * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(colptr, n_cols, rowidx, perm, L + 1,
+                                                                                              N, t_rowptr, t_col, t_perm);
+    GRL_LAUNCH_CHECK("csc_typed_kernel");
     return 0;
 }
 

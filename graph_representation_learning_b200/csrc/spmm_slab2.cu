@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(256)
 dropedge_stream_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val,
                        const uint8_t* __restrict__ mask, int64_t n_nodes, int Lp1, float scale, uint32_t thresh,
                        uint64_t seed, uint64_t stream_id, float* __restrict__ w, uint2* __restrict__ ew,
-                       int2* __restrict__ nodeinfo) {
+                       int2* __restrict__ nodeinfo, const int32_t* __restrict__ perm = nullptr) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
@@ -154,7 +154,7 @@ dropedge_stream_kernel(const int32_t* __restrict__ rowptr, const int32_t* __rest
                 bool keep = true;
                 if (mask) keep = mask[e] != 0;
                 else if (thresh) keep = Philox::word(seed, stream_id, static_cast<uint64_t>(e)) >= thresh;
-                wv = keep ? __ldg(val + e) * scale : 0.0f;
+                wv = keep ? __ldg(val + (perm ? perm[e] : e)) * scale : 0.0f;    // perm: weights of another entry order
                 w[e] = wv;
             }
             uint32_t t = 0;
@@ -444,6 +444,20 @@ extern "C" int grl_dropedge_stream(const int32_t* rowptr, const int32_t* col, co
         rowptr, col, val, mask, n_nodes, L + 1, 1.0f / (1.0f - p), p > 0.0f ? keep_threshold(p) : 0u, seed, stream_id, w,
         static_cast<uint2*>(ew), reinterpret_cast<int2*>(nodeinfo));
     GRL_LAUNCH_CHECK("dropedge_stream_kernel");
+    return 0;
+}
+
+extern "C" int grl_stream_from_weights(const int32_t* rowptr, const int32_t* col, const int32_t* perm, const float* w_src,
+                                      int64_t n_nodes, int L, float* w, void* ew, int32_t* nodeinfo, void* stream) {
+    GRL_CHECK_ARG(rowptr && col && perm && w_src && w && ew && nodeinfo, GRL_E_BADARG, "grl_stream_from_weights: null pointer");
+    GRL_CHECK_ARG(n_nodes > 0 && L > 0 && L + 1 <= 31, GRL_E_BADARG, "grl_stream_from_weights: bad shape (L + 1 must be <= 31)");
+    GRL_CHECK_ARG(aligned_to(ew, 8) && aligned_to(nodeinfo, 8), GRL_E_ALIGN, "grl_stream_from_weights: ew / nodeinfo need 8-byte alignment");
+    int64_t blocks = (n_nodes + 7) / 8;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    dropedge_stream_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        rowptr, col, w_src, nullptr, n_nodes, L + 1, 1.0f, 0u, 0ull, 0ull, w, static_cast<uint2*>(ew),
+        reinterpret_cast<int2*>(nodeinfo), perm);
+    GRL_LAUNCH_CHECK("dropedge_stream_kernel<perm>");
     return 0;
 }
 

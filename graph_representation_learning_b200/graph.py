@@ -65,6 +65,8 @@ class PackedGraphBatch:
     rowidx: Optional[torch.Tensor] = None   # int32 [nnz]   global CSR row of each CSC entry
     perm: Optional[torch.Tensor] = None     # int32 [nnz]   CSR position of each CSC entry
     _eval_weights: Optional[torch.Tensor] = None   # cached edge_weights(p=0) (val + its node streams)
+    _typed_T: Optional["PackedGraphBatch"] = None  # typed_transpose()
+    t_perm: Optional[torch.Tensor] = None          # (on a typed transpose) int32 [nnz] CSR position in the forward packing
 
     @property
     def num_nodes(self) -> int:
@@ -205,6 +207,45 @@ class PackedGraphBatch:
                                          self.perm.data_ptr(), ws.data_ptr(), ws_bytes, _lib.stream_ptr(dev)),
                    "grl_csr_transpose")
         _lib.count_launch(4)
+
+    def typed_transpose(self) -> "PackedGraphBatch":
+        """The batch with every typed adjacency transposed, A_t^T: rows (j, t) list the source nodes i of the entries
+        (i, t) -> j.  Built once per batch from the CSC (csrc/csr_pack.cu csc_typed_kernel); ``t_perm`` maps its
+        entries to CSR positions of this packing.  The backward aggregation U = A_t^T dZ is a FORWARD aggregation over
+        it (ops._GraphConv: dX = sum_t (A_t^T dZ) W_t^T, autograd of robust_gcn.py:45-50)."""
+        if self._typed_T is not None:
+            return self._typed_T
+        self.build_transpose()
+        dev = self.device
+        t_rowptr = torch.empty(self.num_rows + 1, dtype=torch.int32, device=dev)
+        t_col = torch.empty(self.nnz, dtype=torch.int32, device=dev)
+        t_perm = torch.empty(self.nnz, dtype=torch.int32, device=dev)
+        _lib.check(_lib.load().grl_csc_typed_regroup(self.colptr.data_ptr(), self.rowidx.data_ptr(), self.perm.data_ptr(),
+                                                     self.B, self.N, self.L, t_rowptr.data_ptr(), t_col.data_ptr(),
+                                                     t_perm.data_ptr(), _lib.stream_ptr(dev)), "grl_csc_typed_regroup")
+        _lib.count_launch(1)
+        gT = PackedGraphBatch(self.B, self.N, self.L, self.nnz, t_rowptr, t_col, self.val)
+        gT.t_perm = t_perm
+        self._typed_T = gT
+        return gT
+
+    def transposed_weights(self, w: torch.Tensor) -> torch.Tensor:
+        """per-entry weights ``w`` of this packing (one GraphConv layer's DropEdge weights) in the entry order of
+        ``typed_transpose()``, with the node streams of the forward slab kernel attached (grl_stream_from_weights)"""
+        gT = self.typed_transpose()
+        wT = torch.empty_like(w)
+        if self.L + 1 <= 31 and self.N < (1 << 24) - 2:
+            ew = torch.empty(max(self.nnz, 1), 2, dtype=torch.int32, device=self.device)
+            nodeinfo = torch.empty(self.num_nodes, 2, dtype=torch.int32, device=self.device)
+            _lib.check(_lib.load().grl_stream_from_weights(gT.rowptr.data_ptr(), gT.col.data_ptr(), gT.t_perm.data_ptr(),
+                                                           w.data_ptr(), self.num_nodes, self.L, wT.data_ptr(),
+                                                           ew.data_ptr(), nodeinfo.data_ptr(), _lib.stream_ptr(self.device)),
+                       "grl_stream_from_weights")
+            _lib.count_launch(1)
+            wT._grl_stream = (nodeinfo, ew)
+        else:
+            torch.index_select(w, 0, gT.t_perm.long(), out=wT)
+        return wT
 
     # ------------------------------------------------------------------ DropEdge
     def edge_weights(self, p: float, seed: int = 0, stream_id: int = 0,

@@ -349,43 +349,8 @@ class _LinearAct(torch.autograd.Function):
     def backward(ctx, dY):
         weight, y, *xs = ctx.saved_tensors
         relu, p, weight_is_kn, has_bias = ctx.cfg
-        dY = dY.contiguous()
-        d_weight = d_bias = None
-        bwd, cache = GemmConfig.fp32_mode_bwd, {}
-        want_w = ctx.needs_input_grad[0]
-        want_b = has_bias and ctx.needs_input_grad[1]
-        M, C = dY.shape
-        fused = (relu is True and dY.dtype == torch.float32 and bwd == "tf32bc" and C % 8 == 0 and C <= 2048 and
-                 256 % (C // 8) == 0 and M > 0 and y.stride(0) % 4 == 0)
-        if fused:
-            # one pass: dZ, its split for the weight-gradient kernel (when dZ is the narrow operand) and the bias gradient
-            lib = _lib.load()
-            dZ = torch.empty_like(dY)
-            # gemm_tn takes dZ as the narrow (pre-split) operand when it is narrower than x (ties: its second argument)
-            split = want_w and all((x.shape[1] >= C) if weight_is_kn else (x.shape[1] > C) for x in xs)
-            hi = torch.empty(M, C, dtype=torch.float32, device=dY.device) if split else None
-            packed = torch.empty((M + 31) // 32 * 64, C, dtype=torch.bfloat16, device=dY.device) if split else None
-            d_bias = torch.empty(C, dtype=torch.float32, device=dY.device) if want_b else None
-            ws = torch.empty(lib.grl_dz_split_workspace_bytes(M, C) if want_b else 0, dtype=torch.uint8, device=dY.device)
-            flags = _lib.EPI_RELU | (_lib.EPI_DROPOUT if p > 0.0 else 0)
-            _lib.check(lib.grl_dz_split(dY.data_ptr(), dY.stride(0), y.data_ptr(), y.stride(0), dZ.data_ptr(), dZ.stride(0),
-                                        _lib.ptr(hi), _lib.ptr(packed), C, M, C, flags, float(p), _lib.ptr(d_bias),
-                                        _lib.ptr(ws) if want_b else 0, ws.numel(), _lib.stream_ptr(dY.device)),
-                       "grl_dz_split")
-            _lib.count_launch(2 if want_b else 1)
-            if split:
-                cache[(dZ.data_ptr(), dZ.stride(0), M, C)] = (hi, packed, dZ)
-        elif relu or p > 0.0:
-            dZ = torch.empty_like(dY)
-            epilogue_bwd_(dY, y, dZ, relu, p)
-        else:
-            dZ = dY
-        if want_w:
-            # fp32 master gradient whatever the compute dtype; [K, N] for h_weights, [N, K] for nn.Linear
-            parts = [gemm_tn(x, dZ, bwd, cache) if weight_is_kn else gemm_tn(dZ, x, bwd, cache) for x in xs]
-            d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
-        if want_b and d_bias is None:
-            d_bias = colsum(dZ)
+        dZ, d_weight, d_bias = _linear_grads(dY, y, xs, relu, p, weight_is_kn, ctx.needs_input_grad[0],
+                                             has_bias and ctx.needs_input_grad[1])
         dxs = []
         off = 0
         for k, x in enumerate(xs):
@@ -398,6 +363,48 @@ class _LinearAct(torch.autograd.Function):
                 dxs.append(None)
             off += K
         return (d_weight, d_bias, None, None, None, None, None, None, *dxs)
+
+
+def _linear_grads(dY: torch.Tensor, y: Optional[torch.Tensor], xs: Sequence[torch.Tensor], relu, p: float,
+                  weight_is_kn: bool, want_w: bool, want_b: bool):
+    """Shared backward of y = dropout(act(sum_k x_k W_k + b)): returns (dZ, dW or None, db or None).  dZ is the gradient
+    at the pre-activation (autograd of F.relu + nn.Dropout, drop_robust_gcn.py:64-100); dW is the fp32 master gradient,
+    [K, N] for h_weights (``weight_is_kn``), [N, K] for nn.Linear."""
+    dY = dY.contiguous()
+    d_weight = d_bias = None
+    bwd, cache = GemmConfig.fp32_mode_bwd, {}
+    M, C = dY.shape
+    fused = (relu is True and dY.dtype == torch.float32 and bwd == "tf32bc" and C % 8 == 0 and C <= 2048 and
+             256 % (C // 8) == 0 and M > 0 and y.stride(0) % 4 == 0)
+    if fused:
+        # one pass: dZ, its split for the weight-gradient kernel (when dZ is the narrow operand) and the bias gradient
+        lib = _lib.load()
+        dZ = torch.empty_like(dY)
+        # gemm_tn takes dZ as the narrow (pre-split) operand when it is narrower than x (ties: its second argument)
+        split = want_w and all((x.shape[1] >= C) if weight_is_kn else (x.shape[1] > C) for x in xs)
+        hi = torch.empty(M, C, dtype=torch.float32, device=dY.device) if split else None
+        packed = torch.empty((M + 31) // 32 * 64, C, dtype=torch.bfloat16, device=dY.device) if split else None
+        d_bias = torch.empty(C, dtype=torch.float32, device=dY.device) if want_b else None
+        ws = torch.empty(lib.grl_dz_split_workspace_bytes(M, C) if want_b else 0, dtype=torch.uint8, device=dY.device)
+        flags = _lib.EPI_RELU | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+        _lib.check(lib.grl_dz_split(dY.data_ptr(), dY.stride(0), y.data_ptr(), y.stride(0), dZ.data_ptr(), dZ.stride(0),
+                                    _lib.ptr(hi), _lib.ptr(packed), C, M, C, flags, float(p), _lib.ptr(d_bias),
+                                    _lib.ptr(ws) if want_b else 0, ws.numel(), _lib.stream_ptr(dY.device)),
+                   "grl_dz_split")
+        _lib.count_launch(2 if want_b else 1)
+        if split:
+            cache[(dZ.data_ptr(), dZ.stride(0), M, C)] = (hi, packed, dZ)
+    elif relu or p > 0.0:
+        dZ = torch.empty_like(dY)
+        epilogue_bwd_(dY, y, dZ, relu, p)
+    else:
+        dZ = dY
+    if want_w:
+        parts = [gemm_tn(x, dZ, bwd, cache) if weight_is_kn else gemm_tn(dZ, x, bwd, cache) for x in xs]
+        d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)
+    if want_b and d_bias is None:
+        d_bias = colsum(dZ)
+    return dZ, d_weight, d_bias
 
 
 def linear_act(xs: Sequence[torch.Tensor], weight: torch.Tensor, bias: Optional[torch.Tensor], relu: bool = False,
@@ -541,8 +548,68 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
         out = graph_conv_fused(xs, g, w_edge, h_weights, bias, relu, p, mask, seed, stream_id)
         if out is not None:
             return out
+    if GraphConvBackward.aggregate_first and h_weights.shape[1] <= sum(x.shape[1] for x in xs) and torch.is_grad_enabled() \
+            and any(x.requires_grad for x in xs):
+        return _GraphConv.apply(g, w_edge, h_weights, bias, relu, float(p), mask, seed, stream_id, *xs)
     new_v = spmm_aggregate(g, w_edge, xs)
     return linear_act([new_v], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
+
+
+class GraphConvBackward:
+    """``aggregate_first``: the input gradient of GraphConv as aggregate-then-project on the TRANSPOSED typed graph,
+        dX_k = sum_t (A_t^T dZ) W_{t,k}^T
+    (ops._GraphConv) instead of autograd's project-then-aggregate dX_k = sum_t A_t^T (dZ W_{t,k}^T): the aggregation
+    runs the forward slab kernel over [B*N, C] instead of the L2-gather transposed kernel over [B*N*(L+1), F], the
+    projection becomes a long-K product (K = (L+1) C) instead of a short-K, epilogue-bound one, and the intermediate is
+    [R, C] instead of [R, F].  Same mathematics in a different association: gradients agree to fp32 rounding."""
+    aggregate_first = True
+
+
+class _GraphConv(torch.autograd.Function):
+    """GraphConv (robust_gcn.py:45-51) with its ReLU / dropout epilogue as ONE autograd node: forward = aggregation +
+    projection exactly as ``spmm_aggregate`` + ``linear_act``; backward = dZ / dW / db as ``_LinearAct`` and the input
+    gradients through the typed transpose of the batch (``GraphConvBackward``)."""
+
+    @staticmethod
+    def forward(ctx, g, w_edge, h_weights, bias, relu, p, mask, seed, stream_id, *xs):
+        F_total = sum(x.shape[1] for x in xs)
+        new_v = torch.empty(g.num_nodes, (g.L + 1) * F_total, dtype=xs[0].dtype, device=xs[0].device)
+        nv = new_v.view(g.num_rows, F_total)
+        off = 0
+        for x in xs:
+            spmm_fwd_(g, w_edge, x, nv[:, off:off + x.shape[1]])
+            off += x.shape[1]
+        z = gemm_nt([new_v], [h_weights.t()], None, bias, relu, p, mask, seed, stream_id)
+        ctx.save_for_backward(h_weights, z if relu else None, new_v)
+        ctx.g, ctx.w = g, w_edge
+        ctx.widths = [x.shape[1] for x in xs]
+        ctx.cfg = (relu, p, bias is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dY):
+        h_weights, y, new_v = ctx.saved_tensors
+        relu, p, has_bias = ctx.cfg
+        g, w = ctx.g, ctx.w
+        dZ, d_weight, d_bias = _linear_grads(dY, y, [new_v], relu, p, True, ctx.needs_input_grad[2],
+                                             has_bias and ctx.needs_input_grad[3])
+        grads: List[Optional[torch.Tensor]] = [None] * len(ctx.widths)
+        if any(ctx.needs_input_grad[9:]):
+            C = dZ.shape[1]
+            gT = g.typed_transpose()
+            wT = g.transposed_weights(w)
+            U = torch.empty(g.num_nodes, (g.L + 1) * C, dtype=dZ.dtype, device=dZ.device)       # rows (j, t) of A_t^T dZ
+            spmm_fwd_(gT, wT, dZ, U.view(g.num_rows, C))
+            F_total = sum(ctx.widths)
+            w3 = h_weights.detach().view(g.L + 1, F_total, C)
+            off = 0
+            for k, Fk in enumerate(ctx.widths):
+                if ctx.needs_input_grad[9 + k]:
+                    # B[f, t*C + c] = h_weights[t*F + off + f, c]: the NT "B" operand [F_k, (L+1) C] of dX_k = U B^T
+                    bk = w3[:, off:off + Fk, :].permute(1, 0, 2).reshape(Fk, (g.L + 1) * C)
+                    grads[k] = gemm_nt([U], [bk], fp32_mode=GemmConfig.fp32_mode_bwd)
+                off += Fk
+        return (None, None, d_weight, d_bias, None, None, None, None, None, *grads)
 
 
 class FusedGraphConv:

@@ -139,6 +139,13 @@ int grl_dropedge_stream(const int32_t* rowptr, const int32_t* col, const float* 
                         int64_t n_nodes, int L, float p, uint64_t seed, uint64_t stream_id,
                         float* w, void* ew, int32_t* nodeinfo, void* stream);
 
+/* Node streams of a graph whose per-entry weights already exist in ANOTHER entry order: w[e] = w_src[perm[e]] (also
+ * written out), then the same compaction / row tagging as grl_dropedge_stream.  Used for the typed transpose of the
+ * batch (grl_csc_typed_regroup): the backward aggregation U = A_t^T dZ runs the forward slab kernel over it with the
+ * layer's DropEdge weights (autograd of robust_gcn.py:45-50 as aggregate-then-project). */
+int grl_stream_from_weights(const int32_t* rowptr, const int32_t* col, const int32_t* perm, const float* w_src,
+                            int64_t n_nodes, int L, float* w, void* ew, int32_t* nodeinfo, void* stream);
+
 /* Aggregation over the node streams of grl_dropedge_stream (same result as grl_spmm_fwd, bit for bit):
  * one CTA stages the [N, chunk] feature slab of a graph in shared memory with TMA (double-buffered when two fit) and
  * walks the streams of its nodes.  Returns GRL_E_UNSUP when one graph's slab does not fit in shared memory or the
@@ -189,6 +196,15 @@ int grl_spmm_fwd(const int32_t* rowptr, const int32_t* col, const float* w,
  *   108 / 116 / 132 = force 8 / 16 / 32 lanes (of 16 bytes) per node group in grl_spmm_fwd_stream, 208 / 216 = two 16-byte
  *   words per lane (grl_spmm_fwd stays on auto). */
 int grl_spmm_set_tile_mode(int mode);
+
+/* Typed transpose of the packed batch: the CSC of grl_csr_transpose (columns = global nodes, entries sorted by CSR row
+ * (i, t)) regrouped by edge type inside every column.  Result = CSR of A_t^T with rows (j, t):
+ *   t_rowptr int32 [B*N*(L+1) + 1], t_col int32 [nnz] = local source node i, ascending inside a typed row,
+ *   t_perm int32 [nnz] = CSR position of the entry in the forward packing (to fetch per-layer DropEdge weights).
+ * Replaces the transposed bmm operand of autograd for the aggregate-then-project form of dX
+ * (dX = sum_t (A_t^T dZ) W_t^T,  robust_gcn.py:45-50). */
+int grl_csc_typed_regroup(const int32_t* colptr, const int32_t* rowidx, const int32_t* perm, int B, int N, int L,
+                          int32_t* t_rowptr, int32_t* t_col, int32_t* t_perm, void* stream);
 
 /* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.
  *   dX[b*N+j, 0:F] = sum_{k in column (b*N+j)} w[perm[k]] * dY[rowidx[k], 0:F]

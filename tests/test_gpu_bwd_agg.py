@@ -1,0 +1,90 @@
+"""Backward of GraphConv as aggregate-then-project on the typed transpose of the batch (ops._GraphConv,
+csrc/csr_pack.cu csc_typed_kernel, grl_stream_from_weights): the autograd of
+gnn/models/networks/robust_gcn.py:45-51 in the association dX = sum_t (A_t^T dZ) W_t^T.
+Index structures bit-exact against a dense transpose; gradients against fp64 autograd of the dense formula (2e-6, the
+fp32-grade GEMMs' bar) and against the project-then-aggregate path (same mathematics, other association)."""
+import pytest
+import torch
+
+from _golden import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from graph_representation_learning_b200 import _lib
+    assert _lib.load().grl_device_ok() == 1
+    return torch.device("cuda:0")
+
+
+@pytest.mark.parametrize("B,N,density,weighted", [(3, 37, 0.12, False), (2, 260, 0.03, True), (1, 8, 0.0, False)])
+def test_typed_transpose_is_the_dense_transpose(dev, B, N, density, weighted):
+    from graph_representation_learning_b200 import PackedGraphBatch
+    gen = torch.Generator().manual_seed(N)
+    L = 6
+    A = (torch.rand(B, N, L, N, generator=gen) < density).float()
+    if weighted:
+        A = A * (torch.randint(1, 200, (B, N, L, N), generator=gen).float() / 64)     # exact in fp16
+    g = PackedGraphBatch.from_dense(A.half().to(dev))
+    w = g.edge_weights(0.3, seed=11, stream_id=2)
+    gT = g.typed_transpose()
+    wT = g.transposed_weights(w)
+    nnz = int(g.rowptr[-1])
+    assert int(gT.rowptr[-1]) == nnz and int(gT.rowptr[0]) == 0
+    dense = g.to_dense(w).view(B, N, L + 1, N)                      # [b, i, t, j]
+    denseT = gT.to_dense(wT).view(B, N, L + 1, N)                   # [b, j, t, i]
+    assert torch.equal(denseT, dense.permute(0, 3, 2, 1))
+    # source nodes ascend inside every typed row (deterministic summation order), weights are a permutation of w
+    rp, col = gT.rowptr.cpu().long(), gT.col.cpu()[:nnz]
+    rows = torch.repeat_interleave(torch.arange(rp.numel() - 1), rp[1:] - rp[:-1])
+    same_row = rows[1:] == rows[:-1]
+    assert bool((col[1:][same_row] > col[:-1][same_row]).all())
+    assert torch.equal(wT[:nnz], w[gT.t_perm.long()[:nnz]])
+    assert getattr(wT, "_grl_stream", None) is not None
+
+
+@pytest.mark.parametrize("dtype,widths,C,N", [(torch.float32, (64,), 64, 130), (torch.float32, (128, 128), 128, 300),
+                                              (torch.bfloat16, (128,), 128, 257)])
+def test_graphconv_gradients_aggregate_first(dev, dtype, widths, C, N):
+    from graph_representation_learning_b200 import PackedGraphBatch, ops
+    gen = torch.Generator().manual_seed(C + N)
+    B, L = 2, 6
+    A = (torch.rand(B, N, L, N, generator=gen) < 0.04).half()
+    g = PackedGraphBatch.from_dense(A.to(dev))
+    K = (L + 1) * sum(widths)
+    xs0 = [torch.randn(B * N, f, generator=gen).to(dev) for f in widths]
+    h0 = (torch.randn(K, C, generator=gen) / K ** 0.5).to(dev)
+    b0 = torch.randn(C, generator=gen).to(dev)
+    dOut = torch.randn(B * N, C, generator=gen).to(dev)
+    w = g.edge_weights(0.3, seed=4, stream_id=9)
+
+    def run(agg_first):
+        ops.GraphConvBackward.aggregate_first = agg_first
+        try:
+            xs = [x.detach().clone().to(dtype).requires_grad_(True) for x in xs0]
+            h, b = h0.clone().requires_grad_(True), b0.clone().requires_grad_(True)
+            out = ops.graph_conv(xs, g, w, h, b, relu=True, p=0.5, seed=21, stream_id=3)
+            out.backward(dOut.to(dtype))
+            return out.detach(), [x.grad for x in xs], h.grad, b.grad
+        finally:
+            ops.GraphConvBackward.aggregate_first = True
+
+    out1, dx1, dh1, db1 = run(True)
+    out0, dx0, dh0, db0 = run(False)
+    assert torch.equal(out1, out0)                                 # same forward kernels
+    assert torch.equal(dh1, dh0) and torch.equal(db1, db0)         # same dZ / dW / db kernels
+    # fp64 autograd of the dense formula with the SAME dropout pattern (read off the output zeros is not enough: use the mask)
+    Ad = g.to_dense(w).double()
+    xs64 = [x.detach().clone().to(dtype).double().requires_grad_(True) for x in xs0]
+    h64 = h0.double().requires_grad_(True)
+    X = torch.cat(xs64, 1).view(B, N, -1)
+    pre = torch.bmm(Ad, X).view(B, N, L + 1, -1).reshape(B * N, -1) @ h64 + b0.double()
+    # the activation / dropout pattern is the kernel's (read off its output: kept and positive, scale 1 / (1 - 0.5)): a
+    # pre-activation whose sign differs between bf16 and fp64 must not count as a gradient error of the backward kernels
+    keep = (out1 != 0).double() * 2.0
+    (pre * keep).backward(dOut.to(dtype).double())
+    tol, tol_paths = (2e-6, 2e-6) if dtype == torch.float32 else (1e-2, 1e-2)
+    for k in range(len(widths)):
+        assert rel_err(dx1[k], xs64[k].grad) < tol, (k, rel_err(dx1[k], xs64[k].grad))
+        assert rel_err(dx1[k], dx0[k]) < tol_paths

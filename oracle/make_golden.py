@@ -428,6 +428,17 @@ def production_case(GraphCNNDropEdge, name, seed, B, N, in_dim, S, out_dim, L=6,
           ", ".join(f"{k.split('/')[-1]} {v:.1e}" for k, v in err32.items()))
 
 
+def output_schema_case():
+    """The reference's JSON schema of KVInference's output (tests/assets/schemas/output_schema.json, a data asset of its
+    test-suite) as a fixture: tests/test_gpu_procedures.py validates what our KVInference writes back against it."""
+    src = os.path.join(REF, "tests", "assets", "schemas", "output_schema.json")
+    with open(src) as f:
+        schema = json.load(f)
+    with open(os.path.join(OUT, "output_schema.json"), "w") as f:
+        json.dump(schema, f, indent=1, sort_keys=True)
+    print("output_schema.json: required =", schema["items"]["required"])
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     GraphCNNDropEdge, NumpyPadding = import_reference()
@@ -438,6 +449,9 @@ def main():
                         w_rand_scale=0.005)
         production_case(GraphCNNDropEdge, "prod_s512_tame", seed=44, B=2, N=300, in_dim=600, S=512, out_dim=53,
                         w_rand_scale=0.005)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "output_schema":
+        output_schema_case()
         return
     if len(sys.argv) > 1 and sys.argv[1] == "robust_gcn":       # add the sibling-model vectors without touching the rest
         robust_gcn_case("robustgcn_small", seed=21, B=3, N=10, in_dim=24, S=32, out_dim=7)
@@ -463,6 +477,7 @@ def main():
     rp_dropedge_case("rpdropedge_small", seed=22, B=3, N=10, in_dim=24, S=32, out_dim=7, rp_size=48)
     deep_rp_case("deeprp_small", seed=23, B=3, N=10, in_dim=24, S=32, out_dim=7)
     deep_rp_gcn_case("deeprpgcn_small", seed=24, B=2, N=9, in_dim=16, S=16, out_dim=5)
+    output_schema_case()
 
 
 if __name__ == "__main__":

@@ -122,6 +122,55 @@ def test_kv_inference_batched_equals_per_document_on_the_cuda_model(tmp_path):
             assert abs(x["confidence"] - y["confidence"]) < 1e-5
 
 
+def test_kv_inference_output_matches_the_oracle_and_the_reference_schema(tmp_path):
+    """predict() (kv_inference.py:57-75): the annotated boxes validate against the reference's own output schema
+    (tests/golden/output_schema.json, a copy of its tests/assets/schemas/output_schema.json made by oracle/make_golden.py)
+    and carry the classes / confidences of the ORACLE's forward (oracle/reference_port.py) on the same documents."""
+    import json
+    import jsonschema
+    from _golden import GOLDEN
+    from graph_representation_learning_b200 import GNNLearningWarper, GraphCNNDropEdge
+    from oracle import reference_port as rp     # checker only
+    feats = {}
+
+    def featurizer(doc):
+        n = len(doc)
+        r = np.random.default_rng(n * 11 + int(doc[0]["text"][1:]))
+        f = {"textline_encoding": r.random((n, 24), dtype=np.float32)}
+        A = (r.random((n, 6, n)) < 0.2).astype(np.float16)
+        if n % 2:
+            f["adjacency_matrix"] = A
+        else:
+            s_, l_, e_ = np.nonzero(A)
+            f["edges"] = np.stack([s_, l_, e_], 1).astype(np.int32)
+        feats[doc[0]["text"]] = (f["textline_encoding"], A)
+        return f
+
+    docs = [[{"text": f"t{k}", "location": [[0, 0], [4, 0], [4, 2], [0, 2]], "type": "textline"} for _ in range(n)]
+            for k, n in enumerate((12, 15, 12, 9, 15, 40))]
+    torch.manual_seed(3)
+    model = GraphCNNDropEdge(24, 5, 6, net_size=64)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    cfg = _cfg(tmp_path, is_train=False, procedure={"type": "KVInference", "args": {}})
+    ids = {i: (f"field{i}", "key" if i % 2 else "value") for i in range(1, 5)}
+    out = GNNLearningWarper(model, config=cfg, featurizer=featurizer, id_to_class=ids).predict(docs)
+    schema = json.load(open(os.path.join(GOLDEN, "output_schema.json")))
+    ids[0] = ("other", "other")
+    assert len(out) == len(docs)
+    for doc_out, doc in zip(out, docs):
+        jsonschema.validate(doc_out, schema)                         # the reference's output contract
+        V, A = feats[doc[0]["text"]]
+        logits = rp.forward(sd, torch.from_numpy(V)[None], torch.from_numpy(A.astype(np.float32))[None], training=False)
+        prob = torch.softmax(logits, dim=2)[0]
+        top2 = prob.topk(2, dim=1).values
+        score, cls = prob.max(dim=1)
+        assert len(doc_out) == len(doc)
+        for i, box in enumerate(doc_out):
+            assert abs(box["confidence"] - float(score[i])) < 1e-5
+            if float(top2[i, 0] - top2[i, 1]) > 1e-4:                # away from ties the class is the oracle's
+                assert (box["formal_key"], box["key_type"]) == ids[int(cls[i])]
+
+
 def test_graphed_eval_forward_matches_eager():
     """CUDA-graph replay of pack + eval forward == the eager path, bit for bit, on fresh batches after capture"""
     from graph_representation_learning_b200 import GraphCNNDropEdge

@@ -491,12 +491,22 @@ def spmm_and_gemm_roofline(torch, ops, PackedGraphBatch, timed, pk, wl, B, A, de
     dX = torch.empty(B * wl.N, S, device=dev, dtype=wl.dtype)
     ms_bwd, _, _ = timed(lambda: ops.spmm_bwd_(g, w, dYt, dX), 20, 5)
     alg_bwd = 4 * (g.num_nodes + 1) + 12 * g.nnz + dYt.numel() * es + dX.numel() * es
-    roofline["bwd"] = {"kernel": "transposed aggregation (autograd of robust_gcn.py:45-47)",
-                       "achieved": alg_bwd / (ms_bwd * 1e-3) / 1e9,
-                       "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"],
-                       "frac_nominal": alg_bwd / (ms_bwd * 1e-3) / 1e9 / NOMINAL_HBM_GBS, "ms_per_launch": ms_bwd,
-                       "algorithmic_bytes": alg_bwd, "traffic": traffic_bwd}
-    del X, Y, dYt, dX
+    # what the backward of the train step runs since r02 (ops._GraphConv): U = A_t^T dZ, the forward slab kernel over the
+    # typed transpose of the batch with the layer's DropEdge weights; same algorithmic bytes as the forward aggregation
+    gT, wT = g.typed_transpose(), g.transposed_weights(w)
+    ms_agg_t, _, _ = timed(lambda: ops.spmm_fwd_(gT, wT, X, Y), 20, 5)
+    roofline["bwd"] = {"kernel": "spmm_slab2_kernel over the typed transpose (U = A_t^T dZ; autograd of robust_gcn.py:45-47 "
+                                 "as aggregate-then-project)",
+                       "achieved": alg_bytes / (ms_agg_t * 1e-3) / 1e9,
+                       "frac": alg_bytes / (ms_agg_t * 1e-3) / 1e9 / pk["hbm_gbs"],
+                       "frac_nominal": alg_bytes / (ms_agg_t * 1e-3) / 1e9 / NOMINAL_HBM_GBS, "ms_per_launch": ms_agg_t,
+                       "algorithmic_bytes": alg_bytes, "traffic": traffic}
+    roofline["bwd_legacy"] = {"kernel": "spmm_rows_kernel<transposed> (project-then-aggregate; still serves layers with C > F)",
+                              "achieved": alg_bwd / (ms_bwd * 1e-3) / 1e9,
+                              "frac": alg_bwd / (ms_bwd * 1e-3) / 1e9 / pk["hbm_gbs"],
+                              "frac_nominal": alg_bwd / (ms_bwd * 1e-3) / 1e9 / NOMINAL_HBM_GBS, "ms_per_launch": ms_bwd,
+                              "algorithmic_bytes": alg_bwd, "traffic": traffic_bwd}
+    del X, Y, dYt, dX, gT, wT
     # GEMMs are the larger share of the step (about 60 %): the gcn3 projection forward [Nt x S, K = 7 * 2S] and its dX,
     # timed alone.  Tensor-bound figure = EXECUTED tensor flops (fp32: three tf32 products forward, tf32 + double-K bf16
     # backward = 2 tf32-product equivalents; bf16: one product) against the dense peak of that operand type
@@ -506,8 +516,12 @@ def spmm_and_gemm_roofline(torch, ops, PackedGraphBatch, timed, pk, wl, B, A, de
     Wg = torch.randn(S, Kg, device=dev) / Kg ** 0.5
     dZg = torch.randn(B * wl.N, S, device=dev, dtype=wl.dtype)
     ms_gf, _, _ = timed(lambda: ops.gemm_nt([Xg], [Wg]), 10, 3)
-    ms_gb, _, _ = timed(lambda: ops.gemm_nt([dZg], [Wg.t()], fp32_mode=ops.GemmConfig.fp32_mode_bwd), 10, 3)
+    # dX of gcn3 since r02: per input, U [Nt, 7 S] against the regrouped weights [S, 7 S] (long-K; two such launches)
+    Ug = torch.randn(B * wl.N, 7 * S, device=dev, dtype=wl.dtype)
+    Wb = torch.randn(S, 7 * S, device=dev) / (7 * S) ** 0.5
+    ms_gb, _, _ = timed(lambda: ops.gemm_nt([Ug], [Wb], fp32_mode=ops.GemmConfig.fp32_mode_bwd), 10, 3)
     useful = 2.0 * B * wl.N * S * Kg
+    useful_b = 2.0 * B * wl.N * S * 7 * S
     fp32 = wl.dtype == torch.float32
     peak_tf = pk["bf16_tflops_sustained"] / 2 if fp32 else pk["bf16_tflops_sustained"]
     prod_f, prod_b = (3.0, 2.0) if fp32 else (1.0, 1.0)
@@ -518,10 +532,10 @@ def spmm_and_gemm_roofline(torch, ops, PackedGraphBatch, timed, pk, wl, B, A, de
                 "shape_mnk": [B * wl.N, S, Kg], "ms_per_launch": ms_gf, "useful": useful / ms_gf / 1e9,
                 "frac_useful": useful / ms_gf / 1e9 / peak_tf,
                 "achieved": prod_f * useful / ms_gf / 1e9, "frac": prod_f * useful / ms_gf / 1e9 / peak_tf},
-        "bwd_dx": {"kernel": "gemm_bc_kernel<NT> (gcn3 dX, tf32 + bf16 correction product)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 dX)",
-                   "shape_mnk": [B * wl.N, Kg, S], "ms_per_launch": ms_gb, "useful": useful / ms_gb / 1e9,
-                   "frac_useful": useful / ms_gb / 1e9 / peak_tf,
-                   "achieved": prod_b * useful / ms_gb / 1e9, "frac": prod_b * useful / ms_gb / 1e9 / peak_tf},
+        "bwd_dx": {"kernel": "gemm_bc_kernel<NT> (gcn3 dX per input from U = A_t^T dZ, tf32 + bf16 correction product)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 dX per input)",
+                   "shape_mnk": [B * wl.N, S, 7 * S], "ms_per_launch": ms_gb, "useful": useful_b / ms_gb / 1e9,
+                   "frac_useful": useful_b / ms_gb / 1e9 / peak_tf,
+                   "achieved": prod_b * useful_b / ms_gb / 1e9, "frac": prod_b * useful_b / ms_gb / 1e9 / peak_tf},
         "note": "all GEMMs of the step run under the board power cap (sw_power_cap, ~1000 W) and are L2->SM bound "
                 "(DESIGN.md 4.2); the fractions are against an un-capped cuBLAS figure; frac counts executed tensor "
                 "work (3 / 2 products per fp32-grade product), frac_useful the fp32-grade product itself"}
@@ -585,12 +599,13 @@ def run_cfg4(torch, synthetic, PackedGraphBatch, ops, make_step, timed, pk, dev,
     Y = torch.empty(g.num_rows, S, device=dev)
     w = g.edge_weights(0.3, seed=1, stream_id=1)
     ms_f, _, _ = timed(lambda: ops.spmm_fwd_(g, w, X, Y), 5, 2)
-    dX = torch.empty(wl.N, S, device=dev)
-    ms_b, _, _ = timed(lambda: ops.spmm_bwd_(g, w, Y, dX), 5, 2)
+    # backward aggregation since r02: U = A_t^T dZ, the SAME kernel over the typed transpose of the graph (ops._GraphConv)
+    gT, wT = g.typed_transpose(), g.transposed_weights(w)
+    ms_b, _, _ = timed(lambda: ops.spmm_fwd_(gT, wT, X, Y), 5, 2)
     kept = int((w != 0).sum())
     idx = 4 * (g.num_rows + 1) + 8 * g.nnz
     gather_f = idx + kept * S * 4 + Y.numel() * 4                 # every KEPT entry fetches one F*4-byte row of X
-    gather_b = 4 * (g.num_nodes + 1) + 12 * g.nnz + kept * S * 4 + dX.numel() * 4
+    gather_b = gather_f
     tj = None
     tpath = os.path.join(ROOT, "profiles", "spmm_traffic_cfg4.json")
     if os.path.exists(tpath):
@@ -600,7 +615,7 @@ def run_cfg4(torch, synthetic, PackedGraphBatch, ops, make_step, timed, pk, dev,
                 "bytes_gather": gather_f, "achieved": gather_f / (ms_f * 1e-3) / 1e9, "unit": "GB/s",
                 "frac": gather_f / (ms_f * 1e-3) / 1e9 / pk["hbm_gbs"], "frac_nominal": gather_f / (ms_f * 1e-3) / 1e9 / NOMINAL_HBM_GBS,
                 "traffic": tj["fwd"]["dram_bytes_per_launch"] if tj else None},
-        "bwd": {"kernel": "spmm_rows_kernel<transposed>", "ms_per_launch": ms_b, "bytes_gather": gather_b,
+        "bwd": {"kernel": "spmm_nodes_kernel over the typed transpose (U = A_t^T dZ, aggregate-then-project backward)", "ms_per_launch": ms_b, "bytes_gather": gather_b,
                 "achieved": gather_b / (ms_b * 1e-3) / 1e9, "unit": "GB/s", "frac": gather_b / (ms_b * 1e-3) / 1e9 / pk["hbm_gbs"],
                 "frac_nominal": gather_b / (ms_b * 1e-3) / 1e9 / NOMINAL_HBM_GBS,
                 "traffic": tj["bwd"]["dram_bytes_per_launch"] if tj else None},

@@ -1,0 +1,341 @@
+// fp32-grade NT GEMMs on CTA PAIRS (tcgen05 cta_group::2): the arithmetic and the warp roles of gemm_bc_kernel<NT>
+// (gemm_bc_tcgen05.cu: activation operand split in registers and fed from TMEM, weights from shared memory, promoted fp32
+// accumulation, register epilogue), with two CTAs of a cluster on adjacent row tiles of the SAME column tile running ONE
+// MMA of M = 256.
+//
+// Why: the single-CTA kernel moves, per 128x128x32 K-block, 16 KB (TMA, A) + 16 KB (splitter read) + 32 KB (TMA, weight
+// tiles hi / lo-or-packed) + 32-48 KB (MMA reads of the weight tiles) through the SM's 128 B/clk shared-memory port --
+// ~900 of the 960-1180 cycles a K-block takes.  Multicast (gemm_bc_kernel<NT, -, kMC>) halves only where the weight bytes
+// COME FROM, and measured nothing.  In a pair each CTA holds HALF of every weight tile (64 of its 128 rows): the TMA
+// writes and the MMA reads of the weight tiles halve per SM.
+//
+// Protocol (rank 0 = leader issues every MMA and commit):
+//   a_full[s]    local   TMA bytes of my raw activation tile           -> my splitter warps
+//   b_full[s]    leader  TMA bytes of BOTH CTAs' weight halves (cp.async.bulk.tensor .cta_group::2 signals the leader's
+//                        barrier from the peer)                         -> the MMA warp
+//   split[j]     leader  128 local + 128 remote arrivals: both CTAs' splitters have written their A rows to their TMEM
+//   empty[s], ta_empty[j], acc_full[b]   both   tcgen05.commit.cta_group::2 ... multicast::cluster
+//   acc_empty[b], small_empty            leader 256 local + 256 remote arrivals from the drain warps
+#include "gemm_x3_parts.cuh"
+
+namespace grl {
+
+int gemm_x3_current_promo();    // gemm_x3_tcgen05.cu
+
+struct Bc2Cfg {
+    static constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 32;
+    static constexpr int TILE_A = 128 * 128, HALF_B = 64 * 128;
+    static constexpr int STAGE_BYTES = TILE_A + 2 * HALF_B;         // A raw | B_hi half | B_lo / packed half
+    static constexpr int STAGES = 5;
+    static constexpr int TA_STAGES = 2, TA_COL0 = 384, TA_COLS = 64;
+    static constexpr int EPI_BYTES = X3Cfg::EPI_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int THREADS = X3Cfg::THREADS;
+};
+static_assert(Bc2Cfg::SMEM_BYTES <= 227 * 1024, "shared memory budget");
+
+__device__ __forceinline__ uint32_t pack_bf16x2_2sm(float first, float second) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(first, second);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+template <bool kX3>
+__global__ void __launch_bounds__(Bc2Cfg::THREADS, 1)
+gemm_bc_2sm_kernel(const GemmParams p, const int promo, const int n_pairs, const __grid_constant__ CUtensorMap tmA0,
+                   const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmBp0,
+                   const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                   const __grid_constant__ CUtensorMap tmBp1) {
+    using Cfg = Bc2Cfg;
+    constexpr int STAGES = Cfg::STAGES, TA = Cfg::TA_STAGES, DRAIN_WARPS = X3Cfg::DRAIN_WARPS;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
+    float* epi_buf = reinterpret_cast<float*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
+    uint64_t* a_full = bars;                            // [STAGES]
+    uint64_t* b_full = bars + STAGES;                   // [STAGES] (used in the leader)
+    uint64_t* empty_bar = bars + 2 * STAGES;            // [STAGES]
+    uint64_t* split_bar = bars + 3 * STAGES;            // [TA]     (leader)
+    uint64_t* ta_empty = split_bar + TA;                // [TA]
+    uint64_t* acc_full = ta_empty + TA;                 // [2]
+    uint64_t* acc_empty = acc_full + 2;                 // [2]      (leader)
+    uint64_t* small_empty = acc_empty + 2;              //          (leader)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(small_empty + 1);
+
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    const int rank = static_cast<int>(cluster_ctarank());
+    const bool leader = rank == 0;
+    const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int total_kb = p.kblocks0 + p.kblocks1;
+    const int n_chunks = (total_kb + promo - 1) / promo;
+    const int t_first = static_cast<int>(blockIdx.x >> 1), t_step = static_cast<int>(gridDim.x >> 1);
+    auto tile_m0 = [&](int t) { return (2 * (t / tiles_n) + rank) * Cfg::BLOCK_M; };
+    auto tile_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
+    auto tile_b = [&](int s, int which) { return tiles + s * Cfg::STAGE_BYTES + Cfg::TILE_A + which * Cfg::HALF_B; };
+    // barriers the leader owns, as shared::cluster addresses valid from either CTA
+    auto leader_addr = [&](uint64_t* bar) { return mapa_cluster(smem_u32(bar), 0u); };
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA0);
+        tma_prefetch_desc(&tmB0);
+        tma_prefetch_desc(&tmBp0);
+        if (p.kblocks1) {
+            tma_prefetch_desc(&tmA1);
+            tma_prefetch_desc(&tmB1);
+            tma_prefetch_desc(&tmBp1);
+        }
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&a_full[s], 1);
+            mbar_init(&b_full[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int j = 0; j < TA; ++j) {
+            mbar_init(&split_bar[j], 256);
+            mbar_init(&ta_empty[j], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 2 * 32 * DRAIN_WARPS);
+        }
+        mbar_init(small_empty, 2 * 32 * DRAIN_WARPS);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc_2sm<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================================================================== TMA producer (one lane, both CTAs)
+        if (lane == 0) {
+            int it = 0;
+            for (int t = t_first; t < n_pairs; t += t_step) {
+                const int m0 = tile_m0(t), nh = (t % tiles_n) * Cfg::BLOCK_N + rank * 64;
+                for (int kb = 0; kb < total_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    const bool seg1 = kb >= p.kblocks0;
+                    const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
+                    mbar_expect_tx(&a_full[s], Cfg::TILE_A);
+                    tma_load_2d(tile_a(s), seg1 ? &tmA1 : &tmA0, &a_full[s], k_elem, m0);
+                    if (leader) mbar_expect_tx(&b_full[s], 4 * Cfg::HALF_B);          // two halves from each CTA
+                    const uint32_t bf = leader_addr(&b_full[s]);
+                    tma_load_2d_2sm(tile_b(s, 0), seg1 ? &tmB1 : &tmB0, bf, k_elem, nh);
+                    tma_load_2d_2sm(tile_b(s, 1), seg1 ? &tmBp1 : &tmBp0, bf, kX3 ? k_elem : 2 * k_elem, nh);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================================== MMA issuer (leader only; warp-wide loop)
+        if (leader) {
+            constexpr uint32_t idesc = umma_idesc(2, 2 * Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 0);      // tf32, M = 256 over the pair
+            constexpr uint32_t idesc_c = umma_idesc(1, 2 * Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 0);    // bf16
+            const uint32_t d_small = tmem_base + 256;
+            int it = 0, cg = 0, tl = 0;
+            for (int t = t_first; t < n_pairs; t += t_step, ++tl) {
+                mbar_wait(small_empty, (tl & 1) ^ 1);
+                tc_fence_after_sync();
+                int kk = 0;
+                for (int c = 0; c < n_chunks; ++c, ++cg) {
+                    const int buf = cg & 1;
+                    mbar_wait(&acc_empty[buf], ((cg >> 1) & 1) ^ 1);
+                    tc_fence_after_sync();
+                    const uint32_t d_main = tmem_base + buf * 128;
+                    for (int i = 0; i < promo && kk < total_kb; ++i, ++kk, ++it) {
+                        const int s = it % STAGES, j = it % TA;
+                        mbar_wait(&b_full[s], (it / STAGES) & 1);
+                        mbar_wait(&split_bar[j], (it / TA) & 1);
+                        tc_fence_after_sync();
+                        const uint32_t ta_hi = tmem_base + Cfg::TA_COL0 + j * Cfg::TA_COLS, ta_pk = ta_hi + 32;
+                        const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(tile_b(s, 0)));
+                        const uint64_t bp_desc = umma_desc_kmajor_sw128(smem_u32(tile_b(s, 1)));
+                        if (elect_one_sync()) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const uint64_t koff = static_cast<uint64_t>(k * 2);
+                                umma_ts_2sm<true>(d_main, ta_hi + 8 * k, b_desc + koff, idesc, (i | k) != 0);
+                                if constexpr (kX3) {
+                                    umma_ts_2sm<true>(d_small, ta_pk + 8 * k, b_desc + koff, idesc, (kk | k) != 0);   // a_lo * b_hi
+                                    umma_ts_2sm<true>(d_small, ta_hi + 8 * k, bp_desc + koff, idesc, 1u);             // a_hi * b_lo
+                                } else {
+                                    umma_ts_2sm<false>(d_small, ta_pk + 8 * k, bp_desc + koff, idesc_c, (kk | k) != 0);
+                                }
+                            }
+                            umma_commit_2sm_multicast(&empty_bar[s], 3);
+                            umma_commit_2sm_multicast(&ta_empty[j], 3);
+                        }
+                        __syncwarp();
+                    }
+                    if (elect_one_sync()) umma_commit_2sm_multicast(&acc_full[buf], 3);
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp < 6) {
+        // ===================================================================== operand splitter (warps 2..5, both CTAs)
+        const int quarter = warp & 3, row = quarter * 32 + lane;
+        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + Cfg::TA_COL0;
+        const uint32_t split_remote0 = leader_addr(&split_bar[0]), split_remote1 = leader_addr(&split_bar[1]);
+        int it = 0;
+        for (int t = t_first; t < n_pairs; t += t_step) {
+            for (int kk = 0; kk < total_kb; ++kk, ++it) {
+                const int s = it % STAGES, j = it % TA;
+                mbar_wait(&a_full[s], (it / STAGES) & 1);
+                uint32_t hi[32], pk[32];
+                const uint8_t* rowp = tile_a(s) + row * 128;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const uint4 v = *reinterpret_cast<const uint4*>(rowp + ((c ^ (row & 7)) << 4));
+                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                    float lo[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        hi[4 * c + e] = tf32_rn_bits(w[e]);
+                        lo[e] = __uint_as_float(w[e]) - __uint_as_float(hi[4 * c + e]);
+                    }
+                    if constexpr (kX3) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) pk[4 * c + e] = tf32_rn_bits(__float_as_uint(lo[e]));
+                        continue;
+                    }
+                    pk[4 * c + 0] = pack_bf16x2_2sm(lo[0], lo[1]);
+                    pk[4 * c + 1] = pack_bf16x2_2sm(lo[2], lo[3]);
+                    pk[4 * c + 2] = pack_bf16x2_2sm(__uint_as_float(hi[4 * c]), __uint_as_float(hi[4 * c + 1]));
+                    pk[4 * c + 3] = pack_bf16x2_2sm(__uint_as_float(hi[4 * c + 2]), __uint_as_float(hi[4 * c + 3]));
+                }
+                mbar_wait(&ta_empty[j], ((it / TA) & 1) ^ 1);
+                tc_fence_after_sync();
+                tmem_st_32x32(lane_addr + j * Cfg::TA_COLS, hi);
+                tmem_st_32x32(lane_addr + j * Cfg::TA_COLS + 32, pk);
+                tmem_st_wait();
+                tc_fence_before_sync();
+                mbar_arrive_cluster_relaxed(j ? split_remote1 : split_remote0);
+            }
+        }
+    } else {
+        // ===================================================================== drain + epilogue (warps 6..13, both CTAs)
+        const int quarter = warp & 3, half = (warp - 6) >> 2;
+        const int colbase = half * X3Cfg::DRAIN_COLS;
+        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + colbase;
+        float* my_buf = epi_buf + (warp - 6) * 32 * X3Cfg::EPI_PITCH;
+        const uint32_t acc_empty_remote0 = leader_addr(&acc_empty[0]), acc_empty_remote1 = leader_addr(&acc_empty[1]);
+        const uint32_t small_empty_remote = leader_addr(small_empty);
+        int cg = 0;
+        for (int t = t_first; t < n_pairs; t += t_step) {
+            const int m0 = tile_m0(t), n0 = (t % tiles_n) * Cfg::BLOCK_N;
+            float acc[X3Cfg::DRAIN_COLS];
+#pragma unroll
+            for (int q = 0; q < X3Cfg::DRAIN_COLS; ++q) acc[q] = 0.0f;
+            for (int c = 0; c < n_chunks; ++c, ++cg) {
+                const int buf = cg & 1;
+                mbar_wait(&acc_full[buf], (cg >> 1) & 1);
+                tc_fence_after_sync();
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + buf * 128, r0);
+                tmem_ld_32x32(lane_base + buf * 128 + 32, r1);
+                tmem_ld_wait();
+                tc_fence_before_sync();
+                mbar_arrive_cluster_relaxed(buf ? acc_empty_remote1 : acc_empty_remote0);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
+            }
+            {
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + 256, r0);
+                tmem_ld_32x32(lane_base + 256 + 32, r1);
+                tmem_ld_wait();
+                tc_fence_before_sync();
+                mbar_arrive_cluster_relaxed(small_empty_remote);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
+            }
+            if (m0 + quarter * 32 < p.M) epilogue_from_regs(p, acc, my_buf, m0 + quarter * 32, n0 + colbase, lane);
+        }
+    }
+    tc_fence_before_sync();
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
+}
+
+static int g_bc_pairs = 1;      // grl_gemm_bc_set_pairs(0 / 1): NT fp32-grade products on CTA pairs (cta_group::2); measured
+                                // 1.07-1.20x the single-CTA kernel at identical bits (profiles/r02_s52_gemm_2sm_ab.jsonl)
+
+template <bool kX3>
+static int launch_2sm(const GemmParams& p, int promo, int n_pairs, const CUtensorMap& tA0, const CUtensorMap& tB0,
+                      const CUtensorMap& tBp0, const CUtensorMap& tA1, const CUtensorMap& tB1, const CUtensorMap& tBp1,
+                      cudaStream_t st) {
+    auto kern = gemm_bc_2sm_kernel<kX3>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Bc2Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm_bc_2sm_kernel)");
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(Bc2Cfg::THREADS);
+    cfg.dynamicSmemBytes = Bc2Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    static int max_clusters = 0;
+    if (max_clusters == 0) {
+        int n = 0;
+        cfg.gridDim = dim3(kNumSMs);
+        cudaError_t eo = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+        if (eo != cudaSuccess) return cuda_fail(eo, "cudaOccupancyMaxActiveClusters(gemm_bc_2sm_kernel)");
+        max_clusters = n < 1 ? 1 : (n > kNumSMs / 2 ? kNumSMs / 2 : n);
+    }
+    cfg.gridDim = dim3(2 * (n_pairs < max_clusters ? n_pairs : max_clusters));
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_bc_2sm_kernel)");
+    return 0;
+}
+
+// returns 1 when the pair kernel is switched off or the product is too small for it (the caller runs gemm_bc_kernel)
+int try_launch_gemm_bc_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo) {
+    using Cfg = Bc2Cfg;
+    if (!g_bc_pairs) return 1;
+    const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int n_pairs = (tiles_m + 1) / 2 * tiles_n;
+    if (n_pairs < kNumSMs / 2) return 1;
+    CUtensorMap tA0, tB0, tBp0, tA1, tB1, tBp1;
+    int rc;
+    auto lo_map = [&](CUtensorMap* out, const void* ptr, int K, int64_t ldb) {
+        return x3 ? make_tmap_sw128(out, ptr, 4, p.N, K, ldb, 64) : make_tmap_sw128(out, ptr, 2, p.N, 2 * ((K + 3) / 4 * 4), 2 * ldb, 64);
+    };
+    if ((rc = make_tmap_sw128(&tA0, a.A0, 4, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;
+    if ((rc = make_tmap_sw128(&tB0, a.B0, 4, p.N, a.K0, a.ldb0, 64))) return rc;
+    if ((rc = lo_map(&tBp0, a.B0lo, a.K0, a.ldb0))) return rc;
+    tA1 = tA0; tB1 = tB0; tBp1 = tBp0;
+    if (a.K1 > 0) {
+        if ((rc = make_tmap_sw128(&tA1, a.A1, 4, p.M, a.K1, a.lda1, Cfg::BLOCK_M))) return rc;
+        if ((rc = make_tmap_sw128(&tB1, a.B1, 4, p.N, a.K1, a.ldb1, 64))) return rc;
+        if ((rc = lo_map(&tBp1, a.B1lo, a.K1, a.ldb1))) return rc;
+    }
+    p.kblocks0 = (a.K0 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K;
+    p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
+    return x3 ? launch_2sm<true>(p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1, st)
+              : launch_2sm<false>(p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1, st);
+}
+
+}  // namespace grl
+
+using namespace grl;
+
+extern "C" int grl_gemm_bc_set_pairs(int on) {
+    g_bc_pairs = on != 0;
+    return 0;
+}

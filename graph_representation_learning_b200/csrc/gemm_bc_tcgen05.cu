@@ -373,6 +373,10 @@ static int ensure_bc_smem_attr() {
 // 2 * ldb.  x3 = true: B*lo = the fp32 low parts of grl_split_tf32 (pitch ldb), three-product arithmetic.
 int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo_x3) {
     using Cfg = BcCfg;
+    {
+        const int rc2 = try_launch_gemm_bc_2sm(a, p, st, x3, x3 ? promo_x3 : g_bc_promo);
+        if (rc2 != 1) return rc2;
+    }
     CUtensorMap tA0, tB0, tBp0, tA1, tB1, tBp1;
     int rc;
     auto lo_map = [&](CUtensorMap* out, const void* ptr, int K, int64_t ldb) {

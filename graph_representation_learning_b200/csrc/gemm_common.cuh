@@ -198,5 +198,7 @@ struct GemmArgs {
 
 int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_x3_tcgen05.cu
 int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo_x3);   // gemm_bc_tcgen05.cu
+// CTA-pair (cta_group::2) variant of the NT product; returns 1 when it is switched off / the product is too small for it
+int try_launch_gemm_bc_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo);   // gemm_bc_2sm.cu
 
 }  // namespace grl

@@ -264,6 +264,12 @@ int grl_gemm_nt_bf16_set_persistent(int on);
  * multicast (32 KB instead of 48 KB of L2 -> SM traffic per K-block and CTA).  Identical results and, measured, identical
  * time (the kernel is not bound by L2 reads of the weights), so the default is 0 = single-CTA loads. */
 int grl_gemm_bc_set_multicast(int on);
+
+/* Experiment / tuning knob (host call, process-global): on != 0 runs the fp32-grade NT products (GRL_GEMM_TF32X3 on the
+ * TMEM-operand path and GRL_GEMM_TF32_BF16C) on CTA PAIRS -- tcgen05 cta_group::2, one MMA of M = 256 over two CTAs on
+ * adjacent row tiles, each CTA holding half of every weight tile -- when the product has at least 74 tile pairs.
+ * Same arithmetic per output element as the single-CTA kernel. */
+int grl_gemm_bc_set_pairs(int on);
 int grl_gemm_bc_set_promo(int promo);   /* the same knob of the GRL_GEMM_TF32_BF16C kernels; default 4 */
 /* Weight-gradient GEMM ("TN", reduction over the node dimension R, both operands MN-major fp32 activations):
  *   C[Ma, Nb] = A[R, Ma]^T * B[R, Nb]        fp32-grade TF32X3 on tcgen05, split-K over R, deterministic reduce.

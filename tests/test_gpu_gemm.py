@@ -181,15 +181,49 @@ def test_tf32bc_weight_multicast_clusters_identical(M, N, K):
     bias = torch.randn(N, generator=gen).to(dev)
     outs = []
     try:
+        lib.grl_gemm_bc_set_pairs(0)                 # the cta_group::2 kernel (default) would take both runs
         for on in (0, 1):
             lib.grl_gemm_bc_set_multicast(on)
             outs.append(ops.gemm_nt([a], [b], bias=bias, relu=True, fp32_mode="tf32bc"))
             torch.cuda.synchronize()
     finally:
         lib.grl_gemm_bc_set_multicast(0)
+        lib.grl_gemm_bc_set_pairs(1)
     assert torch.equal(outs[0], outs[1])
     ref = torch.relu(a.double() @ b.double().t() + bias.double())
     assert float((outs[1].double() - ref).norm() / ref.norm()) < 2e-6
+
+
+@pytest.mark.parametrize("M,N,K,mode,two,p_drop", [(19000, 300, 100, "tf32bc", False, 0.0), (19100, 128, 64, "tf32x3", False, 0.5),
+                                                   (40000, 53, 1280, "tf32x3", False, 0.0), (9577, 256, 160, "tf32x3", True, 0.0),
+                                                   (19001, 200, 4369, "tf32bc", False, 0.3)])
+def test_cta_pair_kernel_identical_to_single_cta(M, N, K, mode, two, p_drop):
+    """grl_gemm_bc_set_pairs(1) (default): the fp32-grade NT products on CTA pairs -- tcgen05 cta_group::2, one MMA of
+    M = 256 over two CTAs that each hold half of every weight tile -- must reproduce the single-CTA kernel bit for bit:
+    odd row-tile counts (the pair's second tile past M), N tails inside / past the second weight half, K tails, two K
+    segments (virtual concat), bias + ReLU + Philox dropout epilogue."""
+    from graph_representation_learning_b200 import _lib, ops
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(M + N + K)
+    Kp = (K + 3) // 4 * 4
+    a = torch.randn(M, Kp, generator=gen).to(dev)[:, :K]
+    b = (torch.randn(N, K, generator=gen) / K ** 0.5).to(dev)
+    bias = torch.randn(N, generator=gen).to(dev)
+    a_list, b_list = ([a[:, :K // 8 * 4], a[:, K // 8 * 4:]], [b[:, :K // 8 * 4], b[:, K // 8 * 4:]]) if two else ([a], [b])
+    outs = []
+    try:
+        for on in (0, 1):
+            lib.grl_gemm_bc_set_pairs(on)
+            n0 = _lib.launches()
+            outs.append(ops.gemm_nt(a_list, b_list, bias=bias, relu=True, p=p_drop, seed=5, stream_id=2, fp32_mode=mode))
+            torch.cuda.synchronize()
+    finally:
+        lib.grl_gemm_bc_set_pairs(1)
+    assert torch.equal(outs[0], outs[1])
+    if p_drop == 0.0:
+        ref = torch.relu(a.double() @ b.double().t() + bias.double())
+        assert float((outs[1].double() - ref).norm() / ref.norm()) < 2e-6
 
 
 @pytest.mark.parametrize("M,N,K,two", [(1000, 256, 512, False), (777, 53, 100, False), (4096, 300, 37, False),

@@ -265,6 +265,209 @@ gemm_bc_2sm_kernel(const GemmParams p, const int promo, const int n_pairs, const
     if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
 }
 
+// Weight gradients C[Ma, Nb] = A[R, Ma]^T B[R, Nb] on CTA pairs: gemm_bc_kernel<TN> (wide operand A transposed by the
+// splitter's shared-memory reads into TMEM, narrow operand B = dZ pre-split in HBM and read MN-major, split-K over R with
+// a deterministic reduce) with two CTAs on adjacent Ma tiles of the same Nb tile and the same K split; each CTA holds 64 of
+// the 128 B columns.  One tile per CTA (grid = pairs x splits).
+__global__ void __launch_bounds__(Bc2Cfg::THREADS, 1)
+gemm_bc_tn_2sm_kernel(const GemmParams p, const int promo, const int kb_per_split, const int transpose_out,
+                      const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ CUtensorMap tmBp) {
+    using Cfg = Bc2Cfg;
+    constexpr int STAGES = Cfg::STAGES, TA = Cfg::TA_STAGES, DRAIN_WARPS = X3Cfg::DRAIN_WARPS;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
+    float* epi_buf = reinterpret_cast<float*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
+    uint64_t* a_full = bars;
+    uint64_t* b_full = bars + STAGES;
+    uint64_t* empty_bar = bars + 2 * STAGES;
+    uint64_t* split_bar = bars + 3 * STAGES;
+    uint64_t* ta_empty = split_bar + TA;
+    uint64_t* acc_full = ta_empty + TA;
+    uint64_t* acc_empty = acc_full + 2;
+    uint64_t* small_empty = acc_empty + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(small_empty + 1);
+
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    const int rank = static_cast<int>(cluster_ctarank());
+    const bool leader = rank == 0;
+    const int tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int pair = static_cast<int>(blockIdx.x >> 1);
+    const int m0 = (2 * (pair / tiles_n) + rank) * Cfg::BLOCK_M, n0 = (pair % tiles_n) * Cfg::BLOCK_N;
+    const int kb_begin = static_cast<int>(blockIdx.y) * kb_per_split;
+    const int total_kb = max(min(p.kblocks0, kb_begin + kb_per_split) - kb_begin, 0);
+    const int n_chunks = (total_kb + promo - 1) / promo;
+    auto tile_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
+    auto tile_b = [&](int s, int which) { return tiles + s * Cfg::STAGE_BYTES + Cfg::TILE_A + which * Cfg::HALF_B; };
+    auto leader_addr = [&](uint64_t* bar) { return mapa_cluster(smem_u32(bar), 0u); };
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmBp);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&a_full[s], 1);
+            mbar_init(&b_full[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int j = 0; j < TA; ++j) {
+            mbar_init(&split_bar[j], 256);
+            mbar_init(&ta_empty[j], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 2 * 32 * DRAIN_WARPS);
+        }
+        mbar_init(small_empty, 2 * 32 * DRAIN_WARPS);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc_2sm<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int it = 0; it < total_kb; ++it) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                const int r0 = (kb_begin + it) * Cfg::BLOCK_K;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                mbar_expect_tx(&a_full[s], Cfg::TILE_A);
+                tma_load_2d(tile_a(s), &tmA, &a_full[s], m0, r0);                      // plain box {128 columns, 32 reduction rows}
+                if (leader) mbar_expect_tx(&b_full[s], 4 * Cfg::HALF_B);
+                const uint32_t bf = leader_addr(&b_full[s]);
+                const int nh = n0 + rank * 64;
+                tma_load_2d_2sm(tile_b(s, 0), &tmB, bf, nh, r0);                       // B_hi: my two {32 columns, 32 rows} atoms
+                tma_load_2d_2sm(tile_b(s, 0) + 4096, &tmB, bf, nh + 32, r0);
+                tma_load_2d_2sm(tile_b(s, 1), &tmBp, bf, nh, 2 * r0);                  // packed bf16: my {64 columns, 64 rows} atom
+            }
+        }
+    } else if (warp == 1) {
+        if (leader) {
+            constexpr uint32_t idesc = umma_idesc(2, 2 * Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 1);      // tf32, B MN-major
+            constexpr uint32_t idesc_c = umma_idesc(1, 2 * Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 1);    // bf16
+            const uint32_t d_small = tmem_base + 256;
+            int it = 0, kk = 0;
+            for (int c = 0; c < n_chunks; ++c) {
+                const int buf = c & 1;
+                mbar_wait(&acc_empty[buf], ((c >> 1) & 1) ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d_main = tmem_base + buf * 128;
+                for (int i = 0; i < promo && kk < total_kb; ++i, ++kk, ++it) {
+                    const int s = it % STAGES, j = it % TA;
+                    mbar_wait(&b_full[s], (it / STAGES) & 1);
+                    mbar_wait(&split_bar[j], (it / TA) & 1);
+                    tc_fence_after_sync();
+                    const uint32_t ta_hi = tmem_base + Cfg::TA_COL0 + j * Cfg::TA_COLS, ta_pk = ta_hi + 32;
+                    const uint64_t b_desc = umma_desc_mnmajor_sw128(smem_u32(tile_b(s, 0)), 4096, 512, 1);
+                    const uint64_t bp_desc = umma_desc_mnmajor_sw128(smem_u32(tile_b(s, 1)), 8192, 1024, 2);
+                    if (elect_one_sync()) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            umma_ts_2sm<true>(d_main, ta_hi + 8 * k, b_desc + static_cast<uint64_t>(k * 64), idesc, (i | k) != 0);
+                            umma_ts_2sm<false>(d_small, ta_pk + 8 * k, bp_desc + static_cast<uint64_t>(k * 128), idesc_c, (kk | k) != 0);
+                        }
+                        umma_commit_2sm_multicast(&empty_bar[s], 3);
+                        umma_commit_2sm_multicast(&ta_empty[j], 3);
+                    }
+                    __syncwarp();
+                }
+                if (elect_one_sync()) umma_commit_2sm_multicast(&acc_full[buf], 3);
+                __syncwarp();
+            }
+        }
+    } else if (warp < 6) {
+        const int quarter = warp & 3, row = quarter * 32 + lane;
+        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + Cfg::TA_COL0;
+        const uint32_t split_remote0 = leader_addr(&split_bar[0]), split_remote1 = leader_addr(&split_bar[1]);
+        for (int it = 0; it < total_kb; ++it) {
+            const int s = it % STAGES, j = it % TA;
+            mbar_wait(&a_full[s], (it / STAGES) & 1);
+            uint32_t hi[32], pk[32];
+            // [32 reduction rows][128 columns] plain: lane m reads column m (conflict-free LDS.32)
+            const uint32_t* colp = reinterpret_cast<const uint32_t*>(tile_a(s)) + row;
+            float lo[32];
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                const uint32_t v = colp[r * 128];
+                hi[r] = tf32_rn_bits(v);
+                lo[r] = __uint_as_float(v) - __uint_as_float(hi[r]);
+            }
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                pk[q] = pack_bf16x2_2sm(lo[2 * q], lo[2 * q + 1]);
+                pk[16 + q] = pack_bf16x2_2sm(__uint_as_float(hi[2 * q]), __uint_as_float(hi[2 * q + 1]));
+            }
+            mbar_wait(&ta_empty[j], ((it / TA) & 1) ^ 1);
+            tc_fence_after_sync();
+            tmem_st_32x32(lane_addr + j * Cfg::TA_COLS, hi);
+            tmem_st_32x32(lane_addr + j * Cfg::TA_COLS + 32, pk);
+            tmem_st_wait();
+            tc_fence_before_sync();
+            mbar_arrive_cluster_relaxed(j ? split_remote1 : split_remote0);
+        }
+    } else {
+        const int quarter = warp & 3, half = (warp - 6) >> 2;
+        const int colbase = half * X3Cfg::DRAIN_COLS;
+        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + colbase;
+        float* my_buf = epi_buf + (warp - 6) * 32 * X3Cfg::EPI_PITCH;
+        const uint32_t acc_empty_remote0 = leader_addr(&acc_empty[0]), acc_empty_remote1 = leader_addr(&acc_empty[1]);
+        float acc[X3Cfg::DRAIN_COLS];
+#pragma unroll
+        for (int q = 0; q < X3Cfg::DRAIN_COLS; ++q) acc[q] = 0.0f;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int buf = c & 1;
+            mbar_wait(&acc_full[buf], (c >> 1) & 1);
+            tc_fence_after_sync();
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32(lane_base + buf * 128, r0);
+            tmem_ld_32x32(lane_base + buf * 128 + 32, r1);
+            tmem_ld_wait();
+            tc_fence_before_sync();
+            mbar_arrive_cluster_relaxed(buf ? acc_empty_remote1 : acc_empty_remote0);
+#pragma unroll
+            for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
+#pragma unroll
+            for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
+        }
+        if (n_chunks > 0) {
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32(lane_base + 256, r0);
+            tmem_ld_32x32(lane_base + 256 + 32, r1);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 32; ++q) acc[q] += __uint_as_float(r0[q]);
+#pragma unroll
+            for (int q = 0; q < 32; ++q) acc[32 + q] += __uint_as_float(r1[q]);
+        }
+        // partial tile of split blockIdx.y -> its slab of the workspace (transposed: slab is [N, M], a warp store writes 32
+        // consecutive m of one column n)
+        float* slab = static_cast<float*>(p.C) + static_cast<int64_t>(blockIdx.y) * p.M * p.N;
+        const int m = m0 + quarter * 32 + lane;
+        if (transpose_out) {
+            if (m < p.M) {
+#pragma unroll
+                for (int q = 0; q < X3Cfg::DRAIN_COLS; ++q) {
+                    const int n = n0 + colbase + q;
+                    if (n < p.N) slab[static_cast<int64_t>(n) * p.M + m] = acc[q];
+                }
+            }
+        } else {
+            GemmParams q = p;
+            q.C = slab;
+            if (m0 + quarter * 32 < p.M) epilogue_from_regs(q, acc, my_buf, m0 + quarter * 32, n0 + colbase, lane);
+        }
+    }
+    tc_fence_before_sync();
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
+}
+
 static int g_bc_pairs = 1;      // grl_gemm_bc_set_pairs(0 / 1): NT fp32-grade products on CTA pairs (cta_group::2); measured
                                 // 1.07-1.20x the single-CTA kernel at identical bits (profiles/r02_s52_gemm_2sm_ab.jsonl)
 
@@ -329,6 +532,43 @@ int try_launch_gemm_bc_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st, boo
     p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
     return x3 ? launch_2sm<true>(p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1, st)
               : launch_2sm<false>(p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1, st);
+}
+
+// returns 1 when the pair kernel is switched off (the caller launches gemm_bc_kernel<TN>); otherwise launches the split-K
+// partial products into `p.C` (the workspace) and reports the split count it used
+int try_launch_gemm_bc_tn_2sm(GemmParams p, int promo, int transpose_out, const CUtensorMap& tA, const CUtensorMap& tB,
+                              const CUtensorMap& tBp, int* splits_out, size_t workspace_bytes, cudaStream_t st) {
+    using Cfg = Bc2Cfg;
+    if (!g_bc_pairs) return 1;
+    const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int n_pairs = (tiles_m + 1) / 2 * tiles_n;
+    int splits = tn_plan_splits(2 * n_pairs, p.kblocks0);
+    const int kb_per_split = (p.kblocks0 + splits - 1) / splits;
+    splits = (p.kblocks0 + kb_per_split - 1) / kb_per_split;
+    const size_t need = sizeof(float) * static_cast<size_t>(p.M) * p.N * splits;
+    GRL_CHECK_ARG(workspace_bytes >= need, GRL_E_WORKSPACE, "grl_gemm_tn_bc: workspace %zu < %zu", workspace_bytes, need);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_bc_tn_2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm_bc_tn_2sm_kernel)");
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * n_pairs, splits);
+    cfg.blockDim = dim3(Cfg::THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_bc_tn_2sm_kernel, p, promo, kb_per_split, transpose_out, tA, tB, tBp);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_bc_tn_2sm_kernel)");
+    *splits_out = splits;
+    return 0;
 }
 
 }  // namespace grl

@@ -659,6 +659,12 @@ extern "C" int grl_gemm_tn_bc(const float* A, int64_t lda, int Ma, const float* 
     p.M = Ma; p.N = Nb; p.ldc = Nb; p.C = workspace;
     p.kblocks0 = static_cast<int>(kblocks);
     p.kblocks1 = 0;
+    {
+        int sp = 0;
+        const int rc2 = try_launch_gemm_bc_tn_2sm(p, g_bc_promo, transpose_out, tA, tB, tBp, &sp, workspace_bytes, st);
+        if (rc2 == 0) return launch_reduce_splits(static_cast<const float*>(workspace), C, static_cast<int64_t>(Ma) * Nb, sp, st);
+        if (rc2 != 1) return rc2;
+    }
     const int tiles = ((Ma + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M) * ((Nb + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N);
     int splits = tn_plan_splits(tiles, p.kblocks0);
     const int kb_per_split = (p.kblocks0 + splits - 1) / splits;

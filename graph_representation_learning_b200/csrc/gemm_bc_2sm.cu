@@ -468,6 +468,154 @@ gemm_bc_tn_2sm_kernel(const GemmParams p, const int promo, const int kb_per_spli
     if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
 }
 
+// bf16 NT products with wide outputs (N > 128) on CTA pairs: gemm_nt_bf16_persistent_kernel (gemm_tcgen05.cu) with one
+// MMA of 256 x 256 x 16 over two CTAs.  Each CTA loads ITS 128 rows of A and HALF (128 rows) of the B tile: 32 KB instead
+// of 48 KB per K-block through the shared-memory port, and the tensor core reads 32 instead of 48 KB -- the single-CTA
+// kernel needs 768 port cycles per K-block for 512 cycles of MMA.  Two 256-column accumulators per CTA as before.
+struct NtP2Cfg {
+    static constexpr int BLOCK_M = 128, BLOCK_N = 256, BLOCK_K = 64, UMMA_K = 16;
+    static constexpr int A_BYTES = 128 * 128, BH_BYTES = 128 * 128, STAGE_BYTES = A_BYTES + BH_BYTES;
+    static constexpr int STAGES = 6;
+    static constexpr int DRAIN_WARPS = 8;
+    static constexpr int EPI_BYTES = DRAIN_WARPS * 32 * X3Cfg::EPI_PITCH * 4;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int THREADS = 64 + 32 * DRAIN_WARPS;
+};
+static_assert(NtP2Cfg::SMEM_BYTES <= 227 * 1024, "bf16 NT pair kernel: shared memory budget");
+
+__global__ void __launch_bounds__(NtP2Cfg::THREADS, 1)
+gemm_nt_bf16_2sm_kernel(const GemmParams p, int n_pairs, int tiles_n, const __grid_constant__ CUtensorMap tmA0,
+                        const __grid_constant__ CUtensorMap tmB0, const __grid_constant__ CUtensorMap tmA1,
+                        const __grid_constant__ CUtensorMap tmB1) {
+    using Cfg = NtP2Cfg;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* tiles = smem_raw + (base_u32 - smem_u32(smem_raw));
+    float* epi_buf = reinterpret_cast<float*>(tiles + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);
+    uint64_t* full_bar = bars;                     // [STAGES] (leader) TMA bytes of both CTAs landed
+    uint64_t* empty_bar = bars + STAGES;           // [STAGES] (both, multicast commit)
+    uint64_t* acc_full = bars + 2 * STAGES;        // [2] (both, multicast commit)
+    uint64_t* acc_empty = acc_full + 2;            // [2] (leader) 256 local + 256 remote arrivals
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
+
+    const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    const int rank = static_cast<int>(cluster_ctarank());
+    const bool leader = rank == 0;
+    const int total_kb = p.kblocks0 + p.kblocks1;
+    const int t_first = static_cast<int>(blockIdx.x >> 1), t_step = static_cast<int>(gridDim.x >> 1);
+    auto stage_a = [&](int s) { return tiles + s * Cfg::STAGE_BYTES; };
+    auto stage_b = [&](int s) { return tiles + s * Cfg::STAGE_BYTES + Cfg::A_BYTES; };
+    auto leader_addr = [&](uint64_t* bar) { return mapa_cluster(smem_u32(bar), 0u); };
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA0);
+        tma_prefetch_desc(&tmB0);
+        if (p.kblocks1) {
+            tma_prefetch_desc(&tmA1);
+            tma_prefetch_desc(&tmB1);
+        }
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 2 * 32 * Cfg::DRAIN_WARPS);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc_2sm<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int it = 0;
+            for (int t = t_first; t < n_pairs; t += t_step) {
+                const int m0 = (2 * (t / tiles_n) + rank) * Cfg::BLOCK_M, nh = (t % tiles_n) * Cfg::BLOCK_N + rank * 128;
+                for (int kb = 0; kb < total_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    if (leader) mbar_expect_tx(&full_bar[s], 2 * Cfg::STAGE_BYTES);      // A rows + B half of each CTA
+                    const uint32_t fb = leader_addr(&full_bar[s]);
+                    const bool seg1 = kb >= p.kblocks0;
+                    const int k_elem = (seg1 ? kb - p.kblocks0 : kb) * Cfg::BLOCK_K;
+                    tma_load_2d_2sm(stage_a(s), seg1 ? &tmA1 : &tmA0, fb, k_elem, m0);
+                    tma_load_2d_2sm(stage_b(s), seg1 ? &tmB1 : &tmB0, fb, k_elem, nh);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (leader) {
+            constexpr uint32_t idesc = umma_idesc(1, 2 * Cfg::BLOCK_M, Cfg::BLOCK_N, 0, 0);
+            int it = 0, ct = 0;
+            for (int t = t_first; t < n_pairs; t += t_step, ++ct) {
+                const int buf = ct & 1;
+                mbar_wait(&acc_empty[buf], ((ct >> 1) & 1) ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d = tmem_base + buf * Cfg::BLOCK_N;
+                for (int kb = 0; kb < total_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                    tc_fence_after_sync();
+                    const uint64_t a_desc = umma_desc_kmajor_sw128(smem_u32(stage_a(s)));
+                    const uint64_t b_desc = umma_desc_kmajor_sw128(smem_u32(stage_b(s)));
+                    if (elect_one_sync()) {
+#pragma unroll
+                        for (int k = 0; k < Cfg::BLOCK_K / Cfg::UMMA_K; ++k) {
+                            const uint64_t koff = static_cast<uint64_t>(k * 2);
+                            umma_2sm<false>(d, a_desc + koff, b_desc + koff, idesc, (kb | k) != 0);
+                        }
+                        umma_commit_2sm_multicast(&empty_bar[s], 3);
+                    }
+                    __syncwarp();
+                }
+                if (elect_one_sync()) umma_commit_2sm_multicast(&acc_full[buf], 3);
+                __syncwarp();
+            }
+        }
+    } else {
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + half * 128;
+        float* my_buf = epi_buf + (warp - 2) * 32 * X3Cfg::EPI_PITCH;
+        const uint32_t acc_empty_remote0 = leader_addr(&acc_empty[0]), acc_empty_remote1 = leader_addr(&acc_empty[1]);
+        int ct = 0;
+        for (int t = t_first; t < n_pairs; t += t_step, ++ct) {
+            const int m0 = (2 * (t / tiles_n) + rank) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
+            const int buf = ct & 1;
+            mbar_wait(&acc_full[buf], (ct >> 1) & 1);
+            tc_fence_after_sync();
+#pragma unroll 1
+            for (int pass = 0; pass < 2; ++pass) {
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32(lane_base + buf * Cfg::BLOCK_N + pass * 64, r0);
+                tmem_ld_32x32(lane_base + buf * Cfg::BLOCK_N + pass * 64 + 32, r1);
+                tmem_ld_wait();
+                if (pass == 1) {
+                    tc_fence_before_sync();
+                    mbar_arrive_cluster_relaxed(buf ? acc_empty_remote1 : acc_empty_remote0);
+                }
+                float acc[X3Cfg::DRAIN_COLS];
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[q] = __uint_as_float(r0[q]);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[32 + q] = __uint_as_float(r1[q]);
+                if (m0 + quarter * 32 < p.M)
+                    epilogue_from_regs(p, acc, my_buf, m0 + quarter * 32, n0 + half * 128 + pass * 64, lane);
+            }
+        }
+    }
+    tc_fence_before_sync();
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
+}
+
 static int g_bc_pairs = 1;      // grl_gemm_bc_set_pairs(0 / 1): NT fp32-grade products on CTA pairs (cta_group::2); measured
                                 // 1.07-1.20x the single-CTA kernel at identical bits (profiles/r02_s52_gemm_2sm_ab.jsonl)
 
@@ -532,6 +680,56 @@ int try_launch_gemm_bc_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st, boo
     p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
     return x3 ? launch_2sm<true>(p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1, st)
               : launch_2sm<false>(p, promo, n_pairs, tA0, tB0, tBp0, tA1, tB1, tBp1, st);
+}
+
+// returns 1 when the pair kernel is switched off or the product is too small (the caller runs the single-CTA kernel)
+int try_launch_gemm_nt_bf16_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st) {
+    using Cfg = NtP2Cfg;
+    if (!g_bc_pairs) return 1;
+    const int tiles_m = (p.M + Cfg::BLOCK_M - 1) / Cfg::BLOCK_M, tiles_n = (p.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N;
+    const int n_pairs = (tiles_m + 1) / 2 * tiles_n;
+    if (n_pairs < kNumSMs / 2) return 1;
+    CUtensorMap tA0, tB0, tA1, tB1;
+    int rc;
+    if ((rc = make_tmap_sw128(&tA0, a.A0, 2, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;
+    if ((rc = make_tmap_sw128(&tB0, a.B0, 2, p.N, a.K0, a.ldb0, 128))) return rc;
+    tA1 = tA0;
+    tB1 = tB0;
+    if (a.K1 > 0) {
+        if ((rc = make_tmap_sw128(&tA1, a.A1, 2, p.M, a.K1, a.lda1, Cfg::BLOCK_M))) return rc;
+        if ((rc = make_tmap_sw128(&tB1, a.B1, 2, p.N, a.K1, a.ldb1, 128))) return rc;
+    }
+    p.kblocks0 = (a.K0 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K;
+    p.kblocks1 = a.K1 > 0 ? (a.K1 + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K : 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_nt_bf16_2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm_nt_bf16_2sm_kernel)");
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(Cfg::THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    static int max_clusters = 0;
+    if (max_clusters == 0) {
+        int n = 0;
+        cfg.gridDim = dim3(kNumSMs);
+        cudaError_t eo = cudaOccupancyMaxActiveClusters(&n, gemm_nt_bf16_2sm_kernel, &cfg);
+        if (eo != cudaSuccess) return cuda_fail(eo, "cudaOccupancyMaxActiveClusters(gemm_nt_bf16_2sm_kernel)");
+        max_clusters = n < 1 ? 1 : (n > kNumSMs / 2 ? kNumSMs / 2 : n);
+    }
+    cfg.gridDim = dim3(2 * (n_pairs < max_clusters ? n_pairs : max_clusters));
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_nt_bf16_2sm_kernel, p, n_pairs, tiles_n, tA0, tB0, tA1, tB1);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_nt_bf16_2sm_kernel)");
+    return 0;
 }
 
 // returns 1 when the pair kernel is switched off (the caller launches gemm_bc_kernel<TN>); otherwise launches the split-K

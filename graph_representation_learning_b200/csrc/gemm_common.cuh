@@ -200,6 +200,7 @@ int launch_gemm_x3(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_
 int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo_x3);   // gemm_bc_tcgen05.cu
 // CTA-pair (cta_group::2) variant of the NT product; returns 1 when it is switched off / the product is too small for it
 int try_launch_gemm_bc_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, int promo);   // gemm_bc_2sm.cu
+int try_launch_gemm_nt_bf16_2sm(const GemmArgs& a, GemmParams p, cudaStream_t st);   // gemm_bc_2sm.cu
 int try_launch_gemm_bc_tn_2sm(GemmParams p, int promo, int transpose_out, const CUtensorMap& tA, const CUtensorMap& tB,
                               const CUtensorMap& tBp, int* splits_out, size_t workspace_bytes, cudaStream_t st);   // gemm_bc_2sm.cu
 

@@ -326,6 +326,10 @@ static bool g_nt_bf16_persistent = true;      // grl_gemm_nt_bf16_set_persistent
 
 static int launch_gemm_bf16_persistent(const GemmArgs& a, GemmParams p, cudaStream_t st) {
     using Cfg = NtPCfg;
+    {
+        const int rc2 = try_launch_gemm_nt_bf16_2sm(a, p, st);      // CTA pairs (cta_group::2) when switched on and large enough
+        if (rc2 != 1) return rc2;
+    }
     CUtensorMap tA0, tB0, tA1, tB1;
     int rc;
     if ((rc = make_tmap_sw128(&tA0, a.A0, 2, p.M, a.K0, a.lda0, Cfg::BLOCK_M))) return rc;

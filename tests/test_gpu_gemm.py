@@ -226,6 +226,33 @@ def test_cta_pair_kernel_identical_to_single_cta(M, N, K, mode, two, p_drop):
         assert float((outs[1].double() - ref).norm() / ref.norm()) < 2e-6
 
 
+@pytest.mark.parametrize("M,N,K,two", [(19001, 300, 100, False), (19001, 515, 1000, False), (38000, 256, 192, True)])
+def test_bf16_cta_pair_kernel_identical_to_single_cta(M, N, K, two):
+    """bf16 NT products with N > 128 run on CTA pairs by default (gemm_nt_bf16_2sm_kernel: one 256 x 256 MMA over two CTAs,
+    each loading its rows of A and half of the weight tile); same bits as the single-CTA persistent kernel, with odd
+    row-tile counts, N tails inside either weight half and two K segments; bias + ReLU + Philox dropout epilogue."""
+    from graph_representation_learning_b200 import _lib, ops
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=gen).to(dev).bfloat16()
+    b = (torch.randn(N, K, generator=gen) / K ** 0.5).to(dev)
+    bias = torch.randn(N, generator=gen).to(dev)
+    a_list, b_list = ([a[:, :K // 16 * 8], a[:, K // 16 * 8:]], [b[:, :K // 16 * 8], b[:, K // 16 * 8:]]) if two else ([a], [b])
+    outs = []
+    try:
+        for on in (0, 1):
+            lib.grl_gemm_bc_set_pairs(on)
+            outs.append(ops.gemm_nt(a_list, b_list, bias=bias, relu=True, p=0.5, seed=9, stream_id=1))
+            torch.cuda.synchronize()
+    finally:
+        lib.grl_gemm_bc_set_pairs(1)
+    assert torch.equal(outs[0], outs[1])
+    plain = ops.gemm_nt(a_list, b_list, out_dtype=torch.float32)
+    ref = a.double() @ b.bfloat16().double().t()
+    assert float((plain.double() - ref).norm() / ref.norm()) < 1e-5
+
+
 @pytest.mark.parametrize("M,N,K,two", [(1000, 256, 512, False), (777, 53, 100, False), (4096, 300, 37, False),
                                        (2000, 128, 256, True)])
 def test_tf32x3_tmem_and_smem_operand_kernels_identical(M, N, K, two):

@@ -523,22 +523,25 @@ def spmm_and_gemm_roofline(torch, ops, PackedGraphBatch, timed, pk, wl, B, A, de
     useful = 2.0 * B * wl.N * S * Kg
     useful_b = 2.0 * B * wl.N * S * 7 * S
     fp32 = wl.dtype == torch.float32
-    peak_tf = pk["bf16_tflops_sustained"] / 2 if fp32 else pk["bf16_tflops_sustained"]
+    # these GEMMs are timed ALONE (a few ms of back-to-back launches): the burst figure of MEASURED_PEAKS.json applies, the
+    # sustained one (a 4 s cuBLAS run at the power cap) is reported beside it
+    peak_tf = pk["bf16_tflops"] / 2 if fp32 else pk["bf16_tflops"]
+    peak_tf_sustained = pk["bf16_tflops_sustained"] / 2 if fp32 else pk["bf16_tflops_sustained"]
     prod_f, prod_b = (3.0, 2.0) if fp32 else (1.0, 1.0)
     roofline["gemm"] = {
         "bound": "tensor", "unit": "TFLOP/s", "peak": peak_tf,
-        "peak_how": "measured sustained cuBLAS bf16" + (" / 2 (tf32 operands)" if fp32 else ""),
-        "fwd": {"kernel": "gemm_bc_kernel<NT, x3> (gcn3 projection, three tf32 products)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 projection)",
+        "peak_how": "measured burst cuBLAS bf16 (kernels timed alone)" + (" / 2 (tf32 operands)" if fp32 else ""),
+        "peak_sustained": peak_tf_sustained,
+        "fwd": {"kernel": "gemm_bc_2sm_kernel<x3> (gcn3 projection, three tf32 products, CTA pairs)" if fp32 else "gemm_nt_bf16_2sm_kernel (gcn3 projection, CTA pairs)",
                 "shape_mnk": [B * wl.N, S, Kg], "ms_per_launch": ms_gf, "useful": useful / ms_gf / 1e9,
                 "frac_useful": useful / ms_gf / 1e9 / peak_tf,
                 "achieved": prod_f * useful / ms_gf / 1e9, "frac": prod_f * useful / ms_gf / 1e9 / peak_tf},
-        "bwd_dx": {"kernel": "gemm_bc_kernel<NT> (gcn3 dX per input from U = A_t^T dZ, tf32 + bf16 correction product)" if fp32 else "gemm_nt_bf16_persistent_kernel (gcn3 dX per input)",
+        "bwd_dx": {"kernel": "gemm_bc_2sm_kernel (gcn3 dX per input from U = A_t^T dZ, tf32 + bf16 correction product, CTA pairs)" if fp32 else "gemm_nt_bf16_2sm_kernel (gcn3 dX per input)",
                    "shape_mnk": [B * wl.N, S, 7 * S], "ms_per_launch": ms_gb, "useful": useful_b / ms_gb / 1e9,
                    "frac_useful": useful_b / ms_gb / 1e9 / peak_tf,
                    "achieved": prod_b * useful_b / ms_gb / 1e9, "frac": prod_b * useful_b / ms_gb / 1e9 / peak_tf},
-        "note": "all GEMMs of the step run under the board power cap (sw_power_cap, ~1000 W) and are L2->SM bound "
-                "(DESIGN.md 4.2); the fractions are against an un-capped cuBLAS figure; frac counts executed tensor "
-                "work (3 / 2 products per fp32-grade product), frac_useful the fp32-grade product itself"}
+        "note": "inside the step every GEMM runs at the board power cap (sw_power_cap, ~1000 W; DESIGN.md 4.2); frac counts "
+                "executed tensor work (3 / 2 products per fp32-grade product), frac_useful the fp32-grade product itself"}
     return roofline
 
 

@@ -26,7 +26,7 @@ struct Bc2Cfg {
     static constexpr int BLOCK_M = 128, BLOCK_N = 128, BLOCK_K = 32;
     static constexpr int TILE_A = 128 * 128, HALF_B = 64 * 128;
     static constexpr int STAGE_BYTES = TILE_A + 2 * HALF_B;         // A raw | B_hi half | B_lo / packed half
-    static constexpr int STAGES = 5;
+    static constexpr int STAGES = 6;
     static constexpr int TA_STAGES = 2, TA_COL0 = 384, TA_COLS = 64;
     static constexpr int EPI_BYTES = X3Cfg::EPI_BYTES;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;

@@ -20,10 +20,11 @@
 // fence.acq_rel.cluster + release-arrives spent its time in MEMBAR / CCTL.IVALL, which also flushed the cached edge
 // lists out of L1 every K-block).  An operand slot is reused when the splitters of ALL CTAs have read it (remote
 // arrives on `a_free`).
-// Register budget by role (setmaxnreg per warpgroup, 640 threads launched at 96): TMA / MMA / slab warps 40, splitter 88,
-// drain 208 (FOUR warps holding 128 promoted columns each: at the pace the producer sets, half the drain warps of the
-// plain GEMM are enough, and their registers go to the producer), gather 72 (two rows in flight per lane group: the
-// gather warps were stalled on dependency latency 85 % of the time with one).
+// Register budget by role (setmaxnreg per warpgroup, 896 threads launched at 72): TMA / MMA / slab warps 24, splitter 88,
+// drain 200 (FOUR warps holding 128 promoted columns each: at the pace the producer sets, half the drain warps of the
+// plain GEMM are enough, and their registers go to the producer), SIXTEEN gather warps at 48.  Measured steps of the
+// producer (cfg2 gcn1 layer): 8 warps, one row per lane group 1.27 ms -> two rows in flight (72 registers) 1.23 ms ->
+// 16 warps, one row 1.15 ms (direct producer 2.58 -> 1.91 -> 1.47 ms).
 //
 // Arithmetic = the unfused path's (CSR-order fp32 aggregation, three-product tf32 GEMM with promotion), but the K-blocks
 // are visited in (kc, t) instead of (t, kc) order: results agree to fp32 rounding (~1e-7), not bit for bit.
@@ -41,8 +42,8 @@ struct FusedCfg {
     static constexpr int TA_STAGES = 2, TA_COL0 = 384, TA_COLS = 64;
     static constexpr int EPI_BYTES = 4 * 32 * X3Cfg::EPI_PITCH * 4;   // one 32 x 16 transposition buffer per drain warp
     static constexpr int BAR_BYTES = 256;
-    static constexpr int GATHER_WARPS = 8;
-    static constexpr int THREADS = 640;                             // 5 warpgroups: control | splitter | drain | gather x2
+    static constexpr int GATHER_WARPS = 16;
+    static constexpr int THREADS = 896;                             // 7 warpgroups: control | splitter | drain | gather x4
     static constexpr int TMEM_COLS = 512;
     static constexpr int DRAIN_WARPS = 4;                           // one per TMEM lane quarter, all 128 columns
     static constexpr int GATHER_WARP0 = 12;
@@ -149,7 +150,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp < 4) {
-        setmaxnreg_dec<40>();
+        setmaxnreg_dec<24>();
         if (warp == 0) {
             // ================================================================= weight tiles (one lane)
             if (lane == 0) {
@@ -234,7 +235,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
         }
     } else if (warp < 8) {
         // ===================================================================== operand splitter (warps 4..7)
-        setmaxnreg_dec<88>();
+        setmaxnreg_inc<88>();
         const int quarter = warp & 3, row = quarter * 32 + lane;
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + Cfg::TA_COL0;
         Ring ra(p.n_a);
@@ -273,7 +274,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
         }
     } else if (warp < 12) {
         // ===================================================================== drain + epilogue (warps 8..11)
-        setmaxnreg_inc<208>();
+        setmaxnreg_inc<200>();
         const int quarter = warp & 3;
         const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
         float* my_buf = epi_buf + (warp - 8) * 32 * X3Cfg::EPI_PITCH;
@@ -321,7 +322,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
         }
     } else {
         // ===================================================================== aggregation producer (warps 12..19)
-        setmaxnreg_dec<72>();
+        setmaxnreg_dec<48>();
         const int gw = warp - Cfg::GATHER_WARP0, grp = lane >> 3, l8 = lane & 7;
         const int gtid = static_cast<int>(threadIdx.x) - Cfg::GATHER_WARP0 * 32;
         const uint32_t slab_lane = base_u32 + p.off_slab + l8 * 16;
@@ -331,22 +332,23 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
 #pragma unroll
         for (int r = 0; r < 4; ++r) peer_base[r] = mapa_cluster(base_u32, static_cast<uint32_t>(r < cs ? r : 0));
         // Work units of one (input, 32-column chunk): (edge type ty, pass) -- a lane group of 8 aggregates row
-        // lr = gw*4 + grp + 32*pass of my share for type ty; a K-block is n_pass consecutive units.  Units are processed
-        // in PAIRS (two independent rows per lane group in flight).  The edge list of a unit (<= 16 entries: lane l8
-        // holds entries l8 and l8 + 8) is fetched one pair ahead and broadcast inside the group with shuffles, so the
-        // latency of col / w never sits in front of the gather; longer typed rows finish in a plain loop.
-        const int n_pass = rows_share / 32, pass_shift = n_pass == 4 ? 2 : (n_pass == 2 ? 1 : 0), units = Lp1 * n_pass;
-        struct Pre { int cnt, c0, c1; float w0, w1; };
-        auto unit_e0 = [&](int u) { return rp_s[(gw * 4 + grp + 32 * (u & (n_pass - 1))) * rp_pitch + (u >> pass_shift)]; };
+        // lr = gw*4 + grp + 64*pass of my share for type ty; a K-block is n_pass consecutive units (cs = 4: half of the
+        // gather warps have no row).  The edge list of a unit (<= 16 entries: lane l8 holds entries l8 and l8 + 8) is
+        // fetched ONE UNIT AHEAD and broadcast inside the group with shuffles, so the latency of col / w never sits in
+        // front of the gather; longer typed rows finish in a plain loop.
+        constexpr int ROWS_PER_PASS = Cfg::GATHER_WARPS * 4;
+        const int n_pass = rows_share > ROWS_PER_PASS ? rows_share / ROWS_PER_PASS : 1, pass_shift = n_pass == 2 ? 1 : 0;
+        const int units = Lp1 * n_pass;
+        struct Pre { int e0, cnt, c0, c1; float w0, w1; };
         auto prefetch = [&](int u) -> Pre {
+            const int ty = u >> pass_shift, lr = gw * 4 + grp + ROWS_PER_PASS * (u & (n_pass - 1));
             Pre x;
-            x.cnt = 0; x.c0 = 0; x.c1 = 0; x.w0 = 0.0f; x.w1 = 0.0f;
-            if (u < units) {
-                const int ty = u >> pass_shift, lr = gw * 4 + grp + 32 * (u & (n_pass - 1));
-                const int e0 = rp_s[lr * rp_pitch + ty];
-                x.cnt = rp_s[lr * rp_pitch + ty + 1] - e0;
-                if (l8 < x.cnt) { x.c0 = __ldg(p.col + e0 + l8); x.w0 = __ldg(p.w + e0 + l8); }
-                if (l8 + 8 < x.cnt) { x.c1 = __ldg(p.col + e0 + l8 + 8); x.w1 = __ldg(p.w + e0 + l8 + 8); }
+            x.e0 = 0; x.cnt = 0; x.c0 = 0; x.c1 = 0; x.w0 = 0.0f; x.w1 = 0.0f;
+            if (lr < rows_share) {
+                x.e0 = rp_s[lr * rp_pitch + ty];
+                x.cnt = rp_s[lr * rp_pitch + ty + 1] - x.e0;
+                if (l8 < x.cnt) { x.c0 = __ldg(p.col + x.e0 + l8); x.w0 = __ldg(p.w + x.e0 + l8); }
+                if (l8 + 8 < x.cnt) { x.c1 = __ldg(p.col + x.e0 + l8 + 8); x.w1 = __ldg(p.w + x.e0 + l8 + 8); }
             }
             return x;
         };
@@ -362,7 +364,7 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
                 rp_s[idx] = row < n_valid ? __ldg(p.rowptr + (node0 + row) * Lp1 + k) : 0;
             }
             named_bar_sync(1, Cfg::GATHER_WARPS * 32);
-            Pre nxa = prefetch(0), nxb = prefetch(1);
+            Pre nxt = prefetch(0);
             for (int seg = 0; seg < 2; ++seg) {
                 const int Fk = seg ? p.F1 : p.F0;
                 const float* Xg = (seg ? p.X1 : p.X0) + static_cast<int64_t>(b) * p.N * (seg ? p.ldx1 : p.ldx0) + l8 * 4;
@@ -385,70 +387,49 @@ graphconv_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap 
                     auto fma4 = [](float4& a, float w, const float4& v) {
                         a.x = fmaf(w, v.x, a.x); a.y = fmaf(w, v.y, a.y); a.z = fmaf(w, v.z, a.z); a.w = fmaf(w, v.w, a.w);
                     };
-                    auto begin_kblock = [&](const Ring& r) {
-                        mbar_wait(&a_free[r.s], r.ph ^ 1u);
-                        if (gw == 0 && lane == 0) mbar_expect_tx(&agg_bar[r.s], Cfg::TILE_BYTES);
-                    };
-                    auto store_row = [&](const Ring& r, int pass, const float4& acc) {
-                        // K-major SWIZZLE_128B tile: 16-byte chunk c of row r sits at c ^ (r & 7)
-                        const int row = rank * rows_share + gw * 4 + grp + 32 * pass;
-                        const uint32_t dst = r.s * Cfg::TILE_BYTES + row * 128 + ((l8 ^ (row & 7)) << 4);
-                        const uint32_t ab = p.off_bars + (8 + r.s) * 8;                 // agg_bar[r.s]
-                        st_async_v4(peer_base[0] + dst, acc, peer_base[0] + ab);
-                        if (cs > 1) st_async_v4(peer_base[1] + dst, acc, peer_base[1] + ab);
-                        if (cs > 2) {
-                            st_async_v4(peer_base[2] + dst, acc, peer_base[2] + ab);
-                            st_async_v4(peer_base[3] + dst, acc, peer_base[3] + ab);
+                    for (int u = 0; u < units; ++u) {
+                        const Pre cur = nxt;
+                        nxt = prefetch(u + 1 == units ? 0 : u + 1);        // wraps to the next chunk's first unit (same rows)
+                        const int pass = u & (n_pass - 1);
+                        if (pass == 0) {
+                            mbar_wait(&a_free[ra.s], ra.ph ^ 1u);
+                            if (gw == 0 && lane == 0) mbar_expect_tx(&agg_bar[ra.s], Cfg::TILE_BYTES);
                         }
-                    };
-                    for (int u = 0; u < units; u += 2) {
-                        const Pre ca = nxa, cb = nxb;
-                        const int un = u + 2 < units ? u + 2 : 0;             // wraps to the next chunk's first pair (same rows)
-                        nxa = prefetch(un);
-                        nxb = prefetch(un + 1);
-                        const bool has_b = u + 1 < units;
-                        const int pass_a = u & (n_pass - 1), pass_b = (u + 1) & (n_pass - 1);
-                        Ring rb = ra;                                        // unit b: the same K-block, or (n_pass == 1) the next
-                        if (n_pass == 1) rb.next();
-                        if (pass_a == 0) begin_kblock(ra);
-                        if (has_b && pass_b == 0) begin_kblock(rb);
-                        float4 acc_a = make_float4(0.0f, 0.0f, 0.0f, 0.0f), acc_b = acc_a;
-                        const int kmax = __reduce_max_sync(0xffffffffu, min(max(ca.cnt, cb.cnt), 16));
+                        float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                        const int kmax = __reduce_max_sync(0xffffffffu, min(cur.cnt, 16));
                         const int src0 = lane & 24;
 #pragma unroll 1
-                        for (int k = 0; k < kmax; k += 2) {       // entries past a row's end carry w = 0 (col = 0: a valid row)
-                            const int s0 = src0 | (k & 7), s1 = s0 + 1;
-                            const bool lo = k < 8;
-                            const int ca0 = __shfl_sync(0xffffffffu, lo ? ca.c0 : ca.c1, s0);
-                            const int cb0 = __shfl_sync(0xffffffffu, lo ? cb.c0 : cb.c1, s0);
-                            const int ca1 = __shfl_sync(0xffffffffu, lo ? ca.c0 : ca.c1, s1);
-                            const int cb1 = __shfl_sync(0xffffffffu, lo ? cb.c0 : cb.c1, s1);
-                            const float4 va0 = fetch(ca0), vb0 = fetch(cb0), va1 = fetch(ca1), vb1 = fetch(cb1);
-                            const float wa0 = __shfl_sync(0xffffffffu, lo ? ca.w0 : ca.w1, s0);
-                            const float wb0 = __shfl_sync(0xffffffffu, lo ? cb.w0 : cb.w1, s0);
-                            const float wa1 = __shfl_sync(0xffffffffu, lo ? ca.w0 : ca.w1, s1);
-                            const float wb1 = __shfl_sync(0xffffffffu, lo ? cb.w0 : cb.w1, s1);
-                            fma4(acc_a, wa0, va0);
-                            fma4(acc_b, wb0, vb0);
-                            fma4(acc_a, wa1, va1);
-                            fma4(acc_b, wb1, vb1);
+                        for (int k = 0; k < kmax; k += 4) {       // entries past the row's end carry w = 0 (col = 0: a valid row)
+                            int cc[4];
+                            float ww[4];
+                            float4 vv[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int kk = k + j, src = src0 | (kk & 7);
+                                cc[j] = __shfl_sync(0xffffffffu, kk < 8 ? cur.c0 : cur.c1, src);
+                                ww[j] = __shfl_sync(0xffffffffu, kk < 8 ? cur.w0 : cur.w1, src);
+                            }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) vv[j] = fetch(cc[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) fma4(acc, ww[j], vv[j]);
                         }
-                        if (ca.cnt > 16) {                                    // typed rows longer than 16 entries
-                            const int e0 = unit_e0(u);
-                            for (int e = e0 + 16; e < e0 + ca.cnt; ++e) fma4(acc_a, __ldg(p.w + e), fetch(__ldg(p.col + e)));
+                        for (int e = cur.e0 + 16; e < cur.e0 + cur.cnt; ++e)       // typed rows longer than 16 entries
+                            fma4(acc, __ldg(p.w + e), fetch(__ldg(p.col + e)));
+                        const int lr = gw * 4 + grp + ROWS_PER_PASS * pass;
+                        if (lr < rows_share) {
+                            // K-major SWIZZLE_128B tile: 16-byte chunk c of row r sits at c ^ (r & 7)
+                            const int row = rank * rows_share + lr;
+                            const uint32_t dst = ra.s * Cfg::TILE_BYTES + row * 128 + ((l8 ^ (row & 7)) << 4);
+                            const uint32_t ab = p.off_bars + (8 + ra.s) * 8;                 // agg_bar[ra.s]
+                            st_async_v4(peer_base[0] + dst, acc, peer_base[0] + ab);
+                            if (cs > 1) st_async_v4(peer_base[1] + dst, acc, peer_base[1] + ab);
+                            if (cs > 2) {
+                                st_async_v4(peer_base[2] + dst, acc, peer_base[2] + ab);
+                                st_async_v4(peer_base[3] + dst, acc, peer_base[3] + ab);
+                            }
                         }
-                        if (cb.cnt > 16) {
-                            const int e0 = unit_e0(u + 1);
-                            for (int e = e0 + 16; e < e0 + cb.cnt; ++e) fma4(acc_b, __ldg(p.w + e), fetch(__ldg(p.col + e)));
-                        }
-                        store_row(ra, pass_a, acc_a);
-                        if (has_b) store_row(rb, pass_b, acc_b);
-                        if (n_pass == 1) {
-                            ra.next();
-                            if (has_b) ra.next();
-                        } else if (pass_b == n_pass - 1) {
-                            ra.next();
-                        }
+                        if (pass == n_pass - 1) ra.next();
                     }
                     if (kSlab) {
                         __syncwarp();                           // every lane's slab reads of this chunk are in registers

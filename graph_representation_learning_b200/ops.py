@@ -619,10 +619,10 @@ class FusedGraphConv:
     (1.84 GB of HBM traffic per cfg2 layer).  Training keeps the unfused pair: dW = new_V^T dZ needs ``new_V`` again.
 
     ``enabled``: True = every supported layer, False = never, "auto" (default) = when the layer is at most ``max_waves``
-    waves of CTA clusters.  Measured (profiles/r02_s29_fused_*.jsonl): the aggregation producer has 8 of the SM's warps and is
-    bound by its own dependent instruction stream, so a full-machine layer runs 1.33x the unfused pair's time (1.23 vs
-    0.92 ms at cfg2's gcn1) while small batches, which are launch-bound, gain (whole eval forward 64 x 100 nodes:
-    0.99 -> 0.81 ms; 8 x 200: 0.92 -> 0.81 ms)."""
+    waves of CTA clusters.  Measured (profiles/r02_s58_fused_bench_16_gather_warps.jsonl): the aggregation producer is bound
+    by its own dependent instruction stream, so a full-machine layer runs 1.38x the unfused pair's time (1.15 vs 0.83 ms
+    at cfg2's gcn1) while small batches, which are launch-bound, gain (whole eval forward 64 x 100 nodes: 0.99 -> 0.78 ms;
+    8 x 200: 0.94 -> 0.78 ms)."""
     enabled = "auto"
     max_waves = 1.0
 

@@ -441,6 +441,8 @@ def run_b200(args):
         extra["cfg3"] = run_cfg3(torch, synthetic, make_step, timed, exposed_allreduce, world, rank, dev, args)
         torch.cuda.empty_cache()
         if world == 1:
+            extra["cfg1"] = run_cfg1(torch, synthetic, make_step, timed, dev)
+            torch.cuda.empty_cache()
             extra["cfg5"] = run_cfg5(torch, synthetic, GraphCNNDropEdge, PackedGraphBatch, dev,
                                      rank == 0 and not args.no_cpu_baseline)
             torch.cuda.empty_cache()
@@ -571,6 +573,26 @@ def run_cfg3(torch, synthetic, make_step, timed, exposed_allreduce, world, rank,
             torch.cuda.synchronize()
             torch.cuda.profiler.stop()
         del model, step, V, A, y, batch
+    return out
+
+
+def run_cfg1(torch, synthetic, make_step, timed, dev):
+    """BASELINE configs[0] on the GPU: 8 graphs x 200 nodes, in_dim 4369, S = 256, fp32 -- the reference's own CPU-runnable
+    case, launch-bound here.  Eager KVTrainStep against trainer.GraphedTrainStep (forward + CE + backward, dense pack
+    included, replayed as ONE CUDA graph; clip + Adam eager behind it)."""
+    from graph_representation_learning_b200.trainer import GraphedTrainStep
+    wl = synthetic.Workload("cfg1: 8 graphs x 200 nodes, ~8 nbrs/type, S=256, fp32", 8, 200)
+    V, A, y = synthetic.make_batch(wl, 4321, dev)
+    batch = {"textline_encoding": V, "adjacency_matrix": A, "node_label": y}
+    out = {"workload": wl.name, "dtype": "f32"}
+    for graphed in (False, True):
+        model, step = make_step(wl)
+        runner = GraphedTrainStep(step, wl.B, wl.N, wl.input_dim, wl.num_edges) if graphed else step
+        ms, launches, _ = timed(lambda: runner.run_train_step(batch), 20, 5)
+        key = "cuda_graph" if graphed else "eager"
+        out[key] = {"ms_per_step": ms, "graphs_per_s": wl.B / (ms * 1e-3), "gpu_launches_per_step_outside_graph": launches / 20}
+        del runner, step, model
+        torch.cuda.empty_cache()
     return out
 
 

@@ -99,6 +99,7 @@ SIGNATURES = {
     "grl_gemm_nt_bf16_set_persistent": (c_int, [c_int]),
     "grl_gemm_bc_set_multicast": (c_int, [c_int]),
     "grl_gemm_bc_set_pairs": (c_int, [c_int]),
+    "grl_rng_set_offset_ptr": (c_int, [c_void_p]),
     "grl_gemm_bc_set_promo": (c_int, [c_int]),
     "grl_gemm_tn_workspace_bytes": (c_size_t, [c_int, c_int]),
     "grl_gemm_tn": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int64,

@@ -17,7 +17,15 @@ int cuda_fail(cudaError_t e, const char* what) {
     return static_cast<int>(e);
 }
 
+static const uint64_t* g_rng_offset = nullptr;
+const uint64_t* rng_offset_ptr() { return g_rng_offset; }
+
 }  // namespace grl
+
+extern "C" int grl_rng_set_offset_ptr(const void* dev_u64) {
+    grl::g_rng_offset = static_cast<const uint64_t*>(dev_u64);
+    return 0;
+}
 
 extern "C" int grl_abi_version(void) { return GRL_ABI_VERSION; }
 

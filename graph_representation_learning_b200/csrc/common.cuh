@@ -29,6 +29,11 @@ int cuda_fail(cudaError_t e, const char* what);
         if (e__ != cudaSuccess) return ::grl::cuda_fail(e__, what); \
     } while (0)
 
+// Optional device-side offset added to every Philox stream id (grl_rng_set_offset_ptr): a CUDA graph that captured the
+// train step replays with fresh dropout / DropEdge masks by bumping ONE device counter between replays.
+const uint64_t* rng_offset_ptr();
+__device__ __forceinline__ uint64_t rng_stream(uint64_t stream_id, const uint64_t* off) { return off ? stream_id + __ldg(off) : stream_id; }
+
 static inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 // ---------------------------------------------------------------- Philox4x32-10 (counter based)

@@ -51,8 +51,10 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 bias_act_dropout_fwd_kernel(const T* X, int64_t ldx, const float* __restrict__ bias, T* Y,
                             int64_t ldy, int64_t M, int C, uint32_t flags, float scale, uint32_t thresh,
-                            const uint8_t* __restrict__ mask, uint64_t seed, uint64_t stream_id, bool vec) {
+                            const uint8_t* __restrict__ mask, uint64_t seed, uint64_t stream_id, bool vec,
+                            const uint64_t* __restrict__ rng_off) {
     // one thread = 4 consecutive columns of one row (C % 4 == 0): one Philox block per thread
+    stream_id = rng_stream(stream_id, rng_off);
     const int c4 = C >> 2;
     const int64_t total = M * c4;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -119,7 +121,9 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 bias_act_dropout_fwd_scalar_kernel(const T* X, int64_t ldx, const float* __restrict__ bias, T* Y, int64_t ldy, int64_t M,
                                    int C, uint32_t flags, float scale, uint32_t thresh,
-                                   const uint8_t* __restrict__ mask, uint64_t seed, uint64_t stream_id) {
+                                   const uint8_t* __restrict__ mask, uint64_t seed, uint64_t stream_id,
+                                   const uint64_t* __restrict__ rng_off) {
+    stream_id = rng_stream(stream_id, rng_off);
     const int64_t total = M * C;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
@@ -202,11 +206,11 @@ extern "C" int grl_bias_act_dropout_fwd(const void* X, int64_t ldx, const float*
         if (dtype == GRL_F32)
             bias_act_dropout_fwd_scalar_kernel<float><<<sgrid, 256, 0, st>>>(
                 static_cast<const float*>(X), ldx, bias, static_cast<float*>(Y), ldy, M, C, flags, scale, thresh, mask, seed,
-                stream_id);
+                stream_id, rng_offset_ptr());
         else if (dtype == GRL_BF16)
             bias_act_dropout_fwd_scalar_kernel<__nv_bfloat16><<<sgrid, 256, 0, st>>>(
                 static_cast<const __nv_bfloat16*>(X), ldx, bias, static_cast<__nv_bfloat16*>(Y), ldy, M, C, flags, scale,
-                thresh, mask, seed, stream_id);
+                thresh, mask, seed, stream_id, rng_offset_ptr());
         else {
             set_error("grl_bias_act_dropout_fwd: dtype %d unsupported", dtype);
             return GRL_E_UNSUP;
@@ -220,11 +224,11 @@ extern "C" int grl_bias_act_dropout_fwd(const void* X, int64_t ldx, const float*
     if (dtype == GRL_F32)
         bias_act_dropout_fwd_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(X), ldx, bias,
                                                                 static_cast<float*>(Y), ldy, M, C, flags, scale, thresh,
-                                                                mask, seed, stream_id, vec);
+                                                                mask, seed, stream_id, vec, rng_offset_ptr());
     else if (dtype == GRL_BF16)
         bias_act_dropout_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(X), ldx, bias,
                                                                         static_cast<__nv_bfloat16*>(Y), ldy, M, C, flags,
-                                                                        scale, thresh, mask, seed, stream_id, vec);
+                                                                        scale, thresh, mask, seed, stream_id, vec, rng_offset_ptr());
     else {
         set_error("grl_bias_act_dropout_fwd: dtype %d unsupported", dtype);
         return GRL_E_UNSUP;

@@ -28,6 +28,7 @@ struct GemmParams {
     uint32_t thresh;            // keep iff philox word >= thresh
     const uint8_t* mask;        // injected keep bits [M*N] or null
     uint64_t seed, stream_id;
+    const uint64_t* rng_off;    // device-side offset added to stream_id (null: none); see common.cuh rng_stream
 };
 
 // Fused epilogue for 4 consecutive columns [col, col+4) of one output row held in registers (bias already added).
@@ -48,12 +49,12 @@ __device__ __forceinline__ void epilogue_store4(const GemmParams& p, int row, in
 #pragma unroll
             for (int t = 0; t < 4; ++t) keep[t] = (col + t < p.N) && p.mask[e0 + t] != 0;
         } else if ((e0 & 3) == 0) {       // the 4 elements share one Philox block (always when N % 4 == 0)
-            const uint4 d = Philox::draw(p.seed, p.stream_id, static_cast<uint64_t>(e0) >> 2);
+            const uint4 d = Philox::draw(p.seed, rng_stream(p.stream_id, p.rng_off), static_cast<uint64_t>(e0) >> 2);
             keep[0] = d.x >= p.thresh; keep[1] = d.y >= p.thresh; keep[2] = d.z >= p.thresh; keep[3] = d.w >= p.thresh;
         } else {
 #pragma unroll
             for (int t = 0; t < 4; ++t)
-                keep[t] = Philox::word(p.seed, p.stream_id, static_cast<uint64_t>(e0 + t)) >= p.thresh;
+                keep[t] = Philox::word(p.seed, rng_stream(p.stream_id, p.rng_off), static_cast<uint64_t>(e0 + t)) >= p.thresh;
         }
 #pragma unroll
         for (int t = 0; t < 4; ++t) v[t] = keep[t] ? v[t] * p.scale : 0.0f;

@@ -538,7 +538,7 @@ extern "C" int grl_gemm_nt(const void* A0, int64_t lda0, const void* B0, const v
     if (p == 0.0f) flags &= ~GRL_EPI_DROPOUT;
     GemmParams gp{};
     gp.M = M; gp.N = N; gp.C = C; gp.ldc = ldc; gp.out_bf16 = out_dtype == GRL_BF16; gp.bias = bias; gp.flags = flags;
-    gp.scale = 1.0f / (1.0f - p); gp.thresh = keep_threshold(p); gp.mask = mask; gp.seed = seed; gp.stream_id = stream_id;
+    gp.scale = 1.0f / (1.0f - p); gp.thresh = keep_threshold(p); gp.mask = mask; gp.seed = seed; gp.stream_id = stream_id; gp.rng_off = rng_offset_ptr();
     GemmArgs ga{A0, B0, B0_lo, A1, B1, B1_lo, lda0, ldb0, lda1, ldb1, K0, K1};
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool wide = N > 128;

@@ -40,6 +40,7 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
         const bool leaky = !relu && (p.flags & kEpiAnyLeaky) != 0;
         const float slope = leaky_slope(p.flags);
         const int64_t ldc = p.ldc;
+        const uint64_t sid = drop ? rng_stream(p.stream_id, p.rng_off) : 0ull;
 #pragma unroll
         for (int c0 = 0; c0 < X3Cfg::DRAIN_COLS; c0 += CH) {
             __syncwarp();
@@ -65,7 +66,7 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
                             v.z = v.z > 0.0f ? v.z : slope * v.z; v.w = v.w > 0.0f ? v.w : slope * v.w;
                         }
                         if (drop) {     // same (row * N + col) >> 2 Philox block as epilogue_store4 / grl_bias_act_dropout_fwd
-                            const uint4 d = Philox::draw(p.seed, p.stream_id, static_cast<uint64_t>(static_cast<int64_t>(row0 + rr) * p.N + col) >> 2);
+                            const uint4 d = Philox::draw(p.seed, sid, static_cast<uint64_t>(static_cast<int64_t>(row0 + rr) * p.N + col) >> 2);
                             v.x = d.x >= p.thresh ? v.x * p.scale : 0.0f; v.y = d.y >= p.thresh ? v.y * p.scale : 0.0f;
                             v.z = d.z >= p.thresh ? v.z * p.scale : 0.0f; v.w = d.w >= p.thresh ? v.w * p.scale : 0.0f;
                         }
@@ -87,7 +88,7 @@ __device__ __forceinline__ void epilogue_from_regs(const GemmParams& p, const fl
                             v.z = v.z > 0.0f ? v.z : slope * v.z; v.w = v.w > 0.0f ? v.w : slope * v.w;
                         }
                         if (drop) {
-                            const uint4 d = Philox::draw(p.seed, p.stream_id, static_cast<uint64_t>(static_cast<int64_t>(row0 + rr) * p.N + col) >> 2);
+                            const uint4 d = Philox::draw(p.seed, sid, static_cast<uint64_t>(static_cast<int64_t>(row0 + rr) * p.N + col) >> 2);
                             v.x = d.x >= p.thresh ? v.x * p.scale : 0.0f; v.y = d.y >= p.thresh ? v.y * p.scale : 0.0f;
                             v.z = d.z >= p.thresh ? v.z * p.scale : 0.0f; v.w = d.w >= p.thresh ? v.w * p.scale : 0.0f;
                         }

@@ -527,7 +527,7 @@ extern "C" int grl_graphconv_fused_fwd(const int32_t* rowptr, const int32_t* col
     if (p_drop == 0.0f) flags &= ~GRL_EPI_DROPOUT;
     fp.g.M = B * N; fp.g.N = C; fp.g.C = Y; fp.g.ldc = ldy; fp.g.out_bf16 = 0; fp.g.bias = bias; fp.g.flags = flags;
     fp.g.scale = 1.0f / (1.0f - p_drop); fp.g.thresh = keep_threshold(p_drop); fp.g.mask = mask; fp.g.seed = seed;
-    fp.g.stream_id = stream_id;
+    fp.g.stream_id = stream_id; fp.g.rng_off = rng_offset_ptr();
     fp.rowptr = rowptr; fp.col = col; fp.w = w;
     fp.X0 = X0; fp.X1 = X1; fp.ldx0 = ldx0; fp.ldx1 = ldx1; fp.F0 = F0; fp.F1 = F1;
     fp.B = B; fp.N = N; fp.Lp1 = L + 1;

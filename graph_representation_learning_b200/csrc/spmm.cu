@@ -278,7 +278,8 @@ static int launch_spmm(const int32_t* ptr, const int32_t* idx, const int32_t* wi
 
 __global__ void dropedge_weights_kernel(const float* __restrict__ val, const uint8_t* __restrict__ mask, int64_t nnz,
                                         float scale, uint32_t thresh, uint64_t seed, uint64_t stream_id,
-                                        float* __restrict__ w) {
+                                        float* __restrict__ w, const uint64_t* __restrict__ rng_off) {
+    stream_id = rng_stream(stream_id, rng_off);
     const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     // each thread owns 4 consecutive entries = one Philox block
@@ -312,7 +313,7 @@ extern "C" int grl_dropedge_weights(const float* val, const uint8_t* mask, int64
     int64_t blocks = (nnz / 4 + 255) / 256 + 1;
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
     dropedge_weights_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        val, mask, nnz, scale, p > 0.0f ? keep_threshold(p) : 0u, seed, stream_id, w);
+        val, mask, nnz, scale, p > 0.0f ? keep_threshold(p) : 0u, seed, stream_id, w, rng_offset_ptr());
     GRL_LAUNCH_CHECK("dropedge_weights_kernel");
     return 0;
 }

@@ -135,7 +135,9 @@ __global__ void __launch_bounds__(256)
 dropedge_stream_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val,
                        const uint8_t* __restrict__ mask, int64_t n_nodes, int Lp1, float scale, uint32_t thresh,
                        uint64_t seed, uint64_t stream_id, float* __restrict__ w, uint2* __restrict__ ew,
-                       int2* __restrict__ nodeinfo, const int32_t* __restrict__ perm = nullptr) {
+                       int2* __restrict__ nodeinfo, const int32_t* __restrict__ perm = nullptr,
+                       const uint64_t* __restrict__ rng_off = nullptr) {
+    stream_id = rng_stream(stream_id, rng_off);
     const int lane = threadIdx.x & 31;
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
@@ -442,7 +444,7 @@ extern "C" int grl_dropedge_stream(const int32_t* rowptr, const int32_t* col, co
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
     dropedge_stream_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         rowptr, col, val, mask, n_nodes, L + 1, 1.0f / (1.0f - p), p > 0.0f ? keep_threshold(p) : 0u, seed, stream_id, w,
-        static_cast<uint2*>(ew), reinterpret_cast<int2*>(nodeinfo));
+        static_cast<uint2*>(ew), reinterpret_cast<int2*>(nodeinfo), nullptr, rng_offset_ptr());
     GRL_LAUNCH_CHECK("dropedge_stream_kernel");
     return 0;
 }

@@ -472,6 +472,79 @@ class KVTrainStep:
         return loss, pred.argmax(dim=-1)
 
 
+class GraphedTrainStep:
+    """CUDA-graph replay of the forward + loss + backward of ``KVProcedure._run_train_step``
+    (gnn/trainer/training_procedures/kv_procedure.py:143-164) for one fixed batch signature ``(B, N)`` (SURVEY.md 7.1
+    step 10).
+
+    Small batches make the train step launch-bound (cfg1, 8 x 200 nodes: ~170 kernels of a few microseconds each).  The
+    path -- CSR / CSC / typed-transpose pack of the dense adjacency, model forward, cross entropy, the whole backward into
+    the flat gradient bucket -- is stream-ordered, allocation-stable and free of host reads once the CSR capacity is
+    fixed, so it is captured ONCE; ``run_train_step`` copies the batch into static buffers, bumps ONE device counter and
+    replays.  That counter is the Philox stream offset every DropEdge / dropout kernel adds to its stream id
+    (``grl_rng_set_offset_ptr``: the pointer is baked into the captured kernel nodes), so each replay draws fresh masks --
+    the same masks the eager step draws at the same step index (``tests/test_gpu_procedures.py``).  ``clip_grad_norm_``,
+    the optimizer step and (N > 1) the gradient all-reduce stay eager behind the graph: their scalars (Adam bias
+    corrections, learning rate) change per step.  Single process only: the global valid-node count of the
+    data-parallel cross entropy is a collective inside the forward."""
+
+    def __init__(self, step: KVTrainStep, B: int, N: int, input_dim: int, num_edges: int,
+                 adj_dtype: torch.dtype = torch.float16, nnz_capacity: Optional[int] = None):
+        from . import _lib
+        from .graph import PackedGraphBatch
+        if _dp_world() > 1:
+            raise RuntimeError("GraphedTrainStep captures a single-process step; run KVTrainStep.run_train_step under torch.distributed")
+        dev = step.device
+        if dev.type != "cuda":
+            raise RuntimeError("GraphedTrainStep needs the model on a CUDA device (no CPU fallback)")
+        self.step, self.B, self.N, self.L = step, B, N, num_edges
+        self.capacity = int(nnz_capacity) if nnz_capacity is not None else B * N * (num_edges * N + 1)   # dense worst case
+        ld = (input_dim + 3) // 4 * 4                              # 16-byte row pitch: TMA reads V in place
+        self._Vp = torch.zeros(B, N, ld, device=dev)
+        self.V = self._Vp[:, :, :input_dim]
+        self.A = torch.zeros(B, N, num_edges, N, dtype=adj_dtype, device=dev)
+        self.y = torch.zeros(B, N, dtype=torch.int64, device=dev)
+        self.rng_offset = torch.zeros(1, dtype=torch.int64, device=dev)    # read as uint64 by the kernels
+        model = step.model.train()
+
+        def fwd_bwd():
+            step.bucket.zero()
+            g = PackedGraphBatch.from_dense(self.A, nnz_capacity=self.capacity, with_transpose=True)
+            loss = step.criterion(model.forward([self.V, g]), self.y)
+            loss.backward()
+            return loss.detach()
+
+        lib = _lib.load()
+        with torch.enable_grad():
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):                          # warm-up: library load, function attributes, pools
+                for _ in range(2):
+                    fwd_bwd()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            self.graph = torch.cuda.CUDAGraph()
+            _lib.check(lib.grl_rng_set_offset_ptr(self.rng_offset.data_ptr()), "grl_rng_set_offset_ptr")
+            try:
+                with torch.cuda.graph(self.graph):
+                    self.loss = fwd_bwd()
+            finally:
+                lib.grl_rng_set_offset_ptr(0)
+        step.bucket.zero()
+        self.replays = 0
+
+    def run_train_step(self, batch_sample: Dict[str, torch.Tensor]) -> torch.Tensor:
+        """batch_sample: {"textline_encoding" [B,N,D], "adjacency_matrix" dense [B,N,L,N], "node_label" [B,N]} (host or
+        device).  Returns the static device loss of this step (no host sync here)."""
+        self.V.copy_(batch_sample["textline_encoding"], non_blocking=True)
+        self.A.copy_(batch_sample["adjacency_matrix"], non_blocking=True)
+        self.y.copy_(batch_sample["node_label"], non_blocking=True)
+        self.rng_offset.add_(16)                                   # one forward's worth of Philox stream ids
+        self.graph.replay()
+        self.replays += 1
+        self.step.clip_and_step()
+        return self.loss
+
+
 # ----------------------------------------------------------------------------------------------------------
 # getattr-by-name factories of the reference trainer (losses / optimizers / lr_schedulers), restated
 # ----------------------------------------------------------------------------------------------------------

@@ -55,6 +55,12 @@ const char* grl_last_error(void);
 /* 1 when the running device is compute capability 10.x, 0 otherwise, <0 on CUDA error (host call). */
 int grl_device_ok(void);
 
+/* Device-side Philox offset (host call, process-global).  dev_u64 != NULL: every kernel that draws DropEdge / dropout
+ * bits adds *dev_u64 (read on the device at run time) to its stream_id.  A CUDA graph that captured the train step
+ * (trainer.GraphedTrainStep) replays with fresh masks by bumping that one counter between replays; NULL (default)
+ * switches it off.  Replaces the implicit generator state nn.Dropout advances per call (drop_robust_gcn.py:38,64-100). */
+int grl_rng_set_offset_ptr(const void* dev_u64);
+
 /* ------------------------------------------------------------------------------------------
  * CSR pack of the dense typed adjacency.
  * Replaces: GraphConv.preprocess_adj  gnn/models/networks/robust_gcn.py:53-72  (identity concat,

@@ -192,3 +192,47 @@ def test_graphed_eval_forward_matches_eager():
     with torch.no_grad():                                  # same path as the capture (fused GraphConv layers need no_grad)
         ref = model([V.to(dev), full.to(dev)])
     assert torch.equal(gf(V, full), ref)
+
+
+def test_graphed_train_step_matches_eager_step_bit_for_bit():
+    """trainer.GraphedTrainStep: forward + CE + backward captured in ONE CUDA graph (dense pack included), optimizer eager
+    behind it.  Replays draw fresh DropEdge / dropout masks through the device-side Philox offset
+    (grl_rng_set_offset_ptr) -- the masks of the eager step at the same step index -- so losses and weights after three
+    steps on changing batches equal the eager KVTrainStep's bit for bit."""
+    from graph_representation_learning_b200 import GraphCNNDropEdge
+    from graph_representation_learning_b200.trainer import GraphedTrainStep, KVTrainStep
+    dev = torch.device("cuda:0")
+    B, N, L, D, S, C = 4, 60, 6, 96, 64, 7
+
+    def make():
+        torch.manual_seed(5)
+        m = GraphCNNDropEdge(D, C, L, net_size=S).to(dev)
+        m.rng_seed = 1234
+        return m
+
+    gen = torch.Generator().manual_seed(3)
+    batches = []
+    for k in range(3):
+        A = (torch.rand(B, N, L, N, generator=gen) < (0.10 - 0.01 * k)).half()      # (the eager sync-free pack sizes its buffers by the first batch)
+        batches.append({"textline_encoding": torch.rand(B, N, D, generator=gen), "adjacency_matrix": A,
+                        "node_label": torch.randint(0, C, (B, N), generator=gen)})
+    m_g, m_e = make(), make()
+    step_g, step_e = KVTrainStep(m_g), KVTrainStep(m_e)
+    graphed = GraphedTrainStep(step_g, B, N, D, L)
+    for k, v in m_g.state_dict().items():                          # warm-up and capture did not touch the weights
+        assert torch.equal(v, m_e.state_dict()[k]), k
+    captured_calls = m_g._rng_calls - 1                            # the forward call the graph captured
+    masks_seen = []
+    for r, batch in enumerate(batches, start=1):
+        loss_g = graphed.run_train_step(batch).clone()
+        m_e._rng_calls = captured_calls + r                        # same Philox streams as replay r
+        dense = {k: v.to(dev) for k, v in batch.items()}
+        loss_e = step_e.run_train_step(dense)
+        assert torch.equal(loss_g, loss_e), (r, float(loss_g), float(loss_e))
+        masks_seen.append(float(loss_g))
+    for k, v in m_g.state_dict().items():
+        assert torch.equal(v, m_e.state_dict()[k]), k
+    # replaying the SAME batch twice gives different losses: the masks are redrawn per replay
+    a = float(graphed.run_train_step(batches[0]))
+    b = float(graphed.run_train_step(batches[0]))
+    assert a != b

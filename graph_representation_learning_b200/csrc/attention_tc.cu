@@ -155,9 +155,10 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
     uint8_t* sG = sQ + NP * SLAB;                 // NP slabs
     uint8_t* sH = sG + NP * SLAB;                 // NP * HS slabs
     uint64_t* bars = reinterpret_cast<uint64_t*>(sH + NP * HS * SLAB);
-    uint64_t* bar_tma = bars;
+    uint64_t* bar_tma = bars;                     // the query tile, then the G tile of the next key block
     uint64_t* bar_mma = bars + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+    uint64_t* bar_h = bars + 2;                   // the h tile of the next key block
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
 
     const int tid = threadIdx.x;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -170,6 +171,7 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         tma_prefetch_desc(&tmH);
         mbar_init(bar_tma, 1);
         mbar_init(bar_mma, 1);
+        mbar_init(bar_h, 1);
         fence_mbar_init();
     }
     if (warp == 0) tmem_alloc<512>(tmem_slot);
@@ -207,20 +209,38 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         __syncwarp();
     };
 
+    // The operand tiles of the NEXT key block are fetched as soon as the MMAs that read the current ones have retired (one
+    // buffer per operand): the G tile right after the score product, the h tile right after O += P h -- so a TMA round
+    // trip no longer sits in front of every score product.  The first h tile travels during pass 1.
+    auto load_G = [&](int kb) {            // tid 0
+        mbar_expect_tx(bar_tma, NP * SLAB);
+#pragma unroll
+        for (int pc = 0; pc < NP; ++pc) tma_load_3d(sG + pc * SLAB, &tmG, bar_tma, 0, kb * 128, pc * p.B + b);
+    };
+    auto load_H = [&](int kb) {            // tid 0
+        mbar_expect_tx(bar_h, NP * HS * SLAB);
+#pragma unroll
+        for (int pc = 0; pc < NP; ++pc)
+#pragma unroll
+            for (int s = 0; s < HS; ++s)
+                tma_load_3d(sH + (pc * HS + s) * SLAB, &tmH, bar_h, 64 * s, kb * 128, pc * p.B + b);
+    };
+    uint32_t ph_h = 0;
+    if (tid == 0) {
+        load_G(0);
+        load_H(0);
+    }
+
     // ------------------------------------------------------------ pass 1: row max
     float m = -INFINITY;
     for (int kb = 0; kb < nkb; ++kb) {
-        if (tid == 0) {
-            mbar_expect_tx(bar_tma, NP * SLAB);
-#pragma unroll
-            for (int pc = 0; pc < NP; ++pc) tma_load_3d(sG + pc * SLAB, &tmG, bar_tma, 0, kb * 128, pc * p.B + b);
-        }
         mbar_wait(bar_tma, ph_tma);
         ph_tma ^= 1;
         if (warp == 0) issue_S();
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         tc_fence_after_sync();
+        if (tid == 0) load_G(kb + 1 < nkb ? kb + 1 : 0);        // the last one is pass 2's first tile
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             uint32_t r[32];
@@ -238,22 +258,13 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
     // ------------------------------------------------------------ pass 2: P, row sum, O += P h
     float l = 0.0f;
     for (int kb = 0; kb < nkb; ++kb) {
-        if (tid == 0) {
-            mbar_expect_tx(bar_tma, (NP + NP * HS) * SLAB);
-#pragma unroll
-            for (int pc = 0; pc < NP; ++pc) {
-                tma_load_3d(sG + pc * SLAB, &tmG, bar_tma, 0, kb * 128, pc * p.B + b);
-#pragma unroll
-                for (int s = 0; s < HS; ++s)
-                    tma_load_3d(sH + (pc * HS + s) * SLAB, &tmH, bar_tma, 64 * s, kb * 128, pc * p.B + b);
-            }
-        }
         mbar_wait(bar_tma, ph_tma);
         ph_tma ^= 1;
         if (warp == 0) issue_S();
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         tc_fence_after_sync();
+        if (tid == 0 && kb + 1 < nkb) load_G(kb + 1);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             uint32_t r[32];
@@ -274,6 +285,8 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         tmem_st_wait();
         tc_fence_before_sync();
         __syncthreads();
+        mbar_wait(bar_h, ph_h);
+        ph_h ^= 1;
         if (warp == 0) {
             tc_fence_after_sync();
             if (elect_one_sync()) {
@@ -292,6 +305,7 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         mbar_wait(bar_mma, ph_mma);
         ph_mma ^= 1;
         tc_fence_after_sync();
+        if (tid == 0 && kb + 1 < nkb) load_H(kb + 1);
         __syncthreads();
     }
 

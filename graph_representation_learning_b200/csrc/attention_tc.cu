@@ -140,8 +140,13 @@ __device__ __forceinline__ void load_row_chunk(const void* base, int io_bf16, in
 
 // ================================================================================================ forward
 // NP pieces for every operand.  TMEM columns: S [0,128) | O [128, 128+H) | P pieces [128+H, 128+H+64*NP).
+// kFwdGroups warps share every TMEM lane quarter (a warp may touch lanes 32 (warp % 4) ...): thread (quarter, lane) of
+// group g owns query row quarter*32 + lane and the 32-column score chunks c with c % kFwdGroups == g.  With one group
+// (128 threads) the exp / piece-split / TMEM traffic of 128 x 128 scores per key block ran on 4 warps while the tensor
+// core idled: ~6.8 us per key block.
+constexpr int kFwdGroups = 4;
 template <int NP, int H, int D>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(128 * kFwdGroups, 1)
 attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF, const __grid_constant__ CUtensorMap tmG,
                    const __grid_constant__ CUtensorMap tmH) {
     constexpr int NC = n_combos(NP), HS = H / 64, SLAB = 128 * 128;
@@ -159,9 +164,11 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
     uint64_t* bar_mma = bars + 1;
     uint64_t* bar_h = bars + 2;                   // the h tile of the next key block
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+    float* red = reinterpret_cast<float*>(bars + 8);           // [kFwdGroups][128] row max / row sum partials
 
     const int tid = threadIdx.x;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int grp = warp >> 2, rit = (warp & 3) * 32 + (tid & 31);      // column group, query row inside the tile
     const int b = blockIdx.y, q0 = blockIdx.x * 128;
     const int N = p.N, nkb = (N + 127) / 128;
 
@@ -179,7 +186,7 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t lane_sel = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t lane_sel = static_cast<uint32_t>((warp & 3) * 32) << 16;
     uint32_t ph_tma = 0, ph_mma = 0;
 
     if (tid == 0) {
@@ -242,7 +249,7 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         tc_fence_after_sync();
         if (tid == 0) load_G(kb + 1 < nkb ? kb + 1 : 0);        // the last one is pass 2's first tile
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = grp; c < 4; c += kFwdGroups) {
             uint32_t r[32];
             tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, r);
             tmem_ld_wait();
@@ -254,6 +261,11 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         tc_fence_before_sync();
         __syncthreads();
     }
+    red[grp * 128 + rit] = m;                   // the row max over all column groups
+    __syncthreads();
+#pragma unroll
+    for (int g2 = 0; g2 < kFwdGroups; ++g2) m = fmaxf(m, red[g2 * 128 + rit]);
+    __syncthreads();
 
     // ------------------------------------------------------------ pass 2: P, row sum, O += P h
     float l = 0.0f;
@@ -266,7 +278,7 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
         tc_fence_after_sync();
         if (tid == 0 && kb + 1 < nkb) load_G(kb + 1);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = grp; c < 4; c += kFwdGroups) {
             uint32_t r[32];
             tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, r);
             tmem_ld_wait();
@@ -310,16 +322,21 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
     }
 
     // ------------------------------------------------------------ epilogue
-    const int row = q0 + tid;
+    red[grp * 128 + rit] = l;                   // the row sum over all column groups, added in group order
+    __syncthreads();
+    l = 0.0f;
+#pragma unroll
+    for (int g2 = 0; g2 < kFwdGroups; ++g2) l += red[g2 * 128 + rit];
+    const int row = q0 + rit;
     const bool live = row < N;
     const int64_t grow = static_cast<int64_t>(b) * N + row;
     const float inv_l = 1.0f / l;
-    if (live && p.m_save) {
+    if (live && p.m_save && grp == 0) {
         p.m_save[grow] = m;
         p.l_save[grow] = l;
     }
 #pragma unroll 1
-    for (int c = 0; c < H / 32; ++c) {
+    for (int c = grp; c < H / 32; c += kFwdGroups) {
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + lane_sel + COL_O + 32 * c, r);
         tmem_ld_wait();
@@ -343,8 +360,10 @@ attn_tc_fwd_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF
 // df_i = sum_j dS_ij g_j.  NPS pieces for the score product, NP (<= 2) for dP = do h^T and for dS g.
 // Shared memory: F (NPS slabs), DO (NP*HS) of this query block; G (NPS), Hh (NP*HS) of the current key block.
 // TMEM: S [0,128) (overwritten chunk by chunk with the dS pieces) | dP [128,256) | dF [256,320).
+// kBwdGroups warps per TMEM lane quarter (as in the forward): group g owns the score chunks c with c % kBwdGroups == g.
+constexpr int kBwdGroups = 2;
 template <int NPS, int NP, int H, int D>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(128 * kBwdGroups, 1)
 attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF, const __grid_constant__ CUtensorMap tmG,
                      const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmDO) {
     constexpr int NCS = n_combos(NPS), NC = n_combos(NP), HS = H / 64, SLAB = 128 * 128;
@@ -361,9 +380,11 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
     uint64_t* bar_tma = bars;
     uint64_t* bar_mma = bars + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+    float* red = reinterpret_cast<float*>(bars + 8);           // [kBwdGroups][128] partial D_i
 
     const int tid = threadIdx.x;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int grp = warp >> 2, rit = (warp & 3) * 32 + (tid & 31);
     const int b = blockIdx.y, q0 = blockIdx.x * 128;
     const int N = p.N, nkb = (N + 127) / 128;
 
@@ -381,7 +402,7 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t lane_sel = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t lane_sel = static_cast<uint32_t>((warp & 3) * 32) << 16;
     uint32_t ph_tma = 0, ph_mma = 0;
 
     if (tid == 0) {
@@ -393,7 +414,7 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
 #pragma unroll
             for (int s = 0; s < HS; ++s) tma_load_3d(sDO + (pc * HS + s) * SLAB, &tmDO, bar_tma, 64 * s, q0, pc * p.B + b);
     }
-    const int row = q0 + tid;
+    const int row = q0 + rit;
     const bool live = row < N;
     const int64_t grow = static_cast<int64_t>(b) * N + row;
     const float m = live ? p.m_save[grow] : 0.0f;
@@ -452,7 +473,7 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
             if (pass == 0) {
                 float dacc = 0.0f;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
+                for (int c = grp; c < 4; c += kBwdGroups) {
                     uint32_t rs[32], rp[32];
                     tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, rs);
                     tmem_ld_32x32(tmem_base + lane_sel + COL_DP + 32 * c, rp);
@@ -470,7 +491,7 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
                 continue;
             }
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = grp; c < 4; c += kBwdGroups) {
                 uint32_t rs[32], rp[32];
                 tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, rs);
                 tmem_ld_32x32(tmem_base + lane_sel + COL_DP + 32 * c, rp);
@@ -510,10 +531,17 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
             tc_fence_after_sync();
             __syncthreads();
         }
-        if (pass == 0 && live) p.Dvec[grow] = Dv;
+        if (pass == 0) {                        // D_i over all column groups, added in group order
+            red[grp * 128 + rit] = Dv;
+            __syncthreads();
+            Dv = 0.0f;
+#pragma unroll
+            for (int g2 = 0; g2 < kBwdGroups; ++g2) Dv += red[g2 * 128 + rit];
+            if (live && grp == 0) p.Dvec[grow] = Dv;
+        }
     }
 
-    {
+    if (grp == 0) {
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + lane_sel + COL_DF, r);
         tmem_ld_wait();
@@ -542,7 +570,7 @@ attn_tc_bwd_q_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
 // Shared memory: G (NPS slabs), Hh (NP*HS) of this key block; F (NPS slabs of BQ rows), DO (NP*HS) of the current query
 // block; row statistics of the query block.  TMEM: S^T [0,BQ) | dP^T [BQ,2BQ) | dG [2BQ, 2BQ+64) | dH [2BQ+64, 2BQ+64+H).
 template <int NPS, int NP, int H, int D, int BQ>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(128 * kBwdGroups, 1)
 attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap tmF, const __grid_constant__ CUtensorMap tmG,
                      const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmDO) {
     constexpr int NCS = n_combos(NPS), NC = n_combos(NP), HS = H / 64, SLAB = 128 * 128, SLABQ = BQ * 128;
@@ -563,6 +591,7 @@ attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
 
     const int tid = threadIdx.x;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int grp = warp >> 2, rit = (warp & 3) * 32 + (tid & 31);
     const int b = blockIdx.y, k0 = blockIdx.x * 128;
     const int N = p.N, nqb = (N + BQ - 1) / BQ;
 
@@ -580,7 +609,7 @@ attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t lane_sel = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t lane_sel = static_cast<uint32_t>((warp & 3) * 32) << 16;
     uint32_t ph_tma = 0, ph_mma = 0;
 
     if (tid == 0) {
@@ -592,7 +621,7 @@ attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
 #pragma unroll
             for (int s = 0; s < HS; ++s) tma_load_3d(sH + (pc * HS + s) * SLAB, &tmH, bar_tma, 64 * s, k0, pc * p.B + b);
     }
-    const int krow = k0 + tid;
+    const int krow = k0 + rit;
     const bool live = krow < N;
     const int64_t gkrow = static_cast<int64_t>(b) * N + krow;
     mbar_wait(bar_tma, ph_tma);
@@ -653,7 +682,7 @@ attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
         ph_mma ^= 1;
         tc_fence_after_sync();
 #pragma unroll
-        for (int c = 0; c < BQ / 32; ++c) {
+        for (int c = grp; c < BQ / 32; c += kBwdGroups) {
             uint32_t rs[32], rp[32];
             tmem_ld_32x32(tmem_base + lane_sel + COL_S + 32 * c, rs);
             tmem_ld_32x32(tmem_base + lane_sel + COL_DP + 32 * c, rp);
@@ -703,7 +732,7 @@ attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
     }
 
 #pragma unroll 1
-    for (int c = 0; c < H / 32; ++c) {
+    for (int c = grp; c < H / 32; c += kBwdGroups) {
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + lane_sel + COL_DH + 32 * c, r);
         tmem_ld_wait();
@@ -714,7 +743,7 @@ attn_tc_bwd_k_kernel(const AttnTcParams p, const __grid_constant__ CUtensorMap t
             store_row_chunk(p.dh, p.io_bf16, gkrow, H, 32 * c, v);
         }
     }
-    {
+    if (grp == 0) {
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + lane_sel + COL_DG, r);
         tmem_ld_wait();
@@ -828,7 +857,7 @@ int launch_fwd(const AttnTcParams& p, const void* f_p, const void* g_p, const vo
     if ((rc = make_tmap_graph_rows(&tF, f_p, static_cast<int64_t>(NP) * p.B, p.N, D, 128))) return rc;
     if ((rc = make_tmap_graph_rows(&tG, g_p, static_cast<int64_t>(NP) * p.B, p.N, D, 128))) return rc;
     if ((rc = make_tmap_graph_rows(&tH, h_p, static_cast<int64_t>(NP) * p.B, p.N, H, 128))) return rc;
-    constexpr int SMEM = (2 * NP + NP * (H / 64)) * 16384 + 1024 + 64;
+    constexpr int SMEM = (2 * NP + NP * (H / 64)) * 16384 + 1024 + 64 + kFwdGroups * 128 * 4;
     static_assert(SMEM <= 227 * 1024, "forward shared memory");
     auto kern = attn_tc_fwd_kernel<NP, H, D>;
     static bool attr = false;
@@ -836,7 +865,7 @@ int launch_fwd(const AttnTcParams& p, const void* f_p, const void* g_p, const vo
         if ((rc = set_smem(kern, SMEM, "cudaFuncSetAttribute(attn_tc_fwd_kernel)"))) return rc;
         attr = true;
     }
-    kern<<<dim3((p.N + 127) / 128, p.B), 128, SMEM, st>>>(p, tF, tG, tH);
+    kern<<<dim3((p.N + 127) / 128, p.B), 128 * kFwdGroups, SMEM, st>>>(p, tF, tG, tH);
     GRL_LAUNCH_CHECK("attn_tc_fwd_kernel");
     return 0;
 }
@@ -853,7 +882,7 @@ int launch_bwd(const AttnTcParams& p, const void* f_p, const void* g_p, const vo
     if ((rc = make_tmap_graph_rows(&tFq, f_p, nbS, p.N, D, BQ))) return rc;
     if ((rc = make_tmap_graph_rows(&tDOq, do_p, nb, p.N, H, BQ))) return rc;
     constexpr int HS = H / 64;
-    constexpr int SMEM_Q = 2 * (NPS + NP * HS) * 16384 + 1024 + 64;
+    constexpr int SMEM_Q = 2 * (NPS + NP * HS) * 16384 + 1024 + 64 + kBwdGroups * 128 * 4;
     constexpr int SMEM_K = (NPS + NP * HS) * (16384 + BQ * 128) + 3 * BQ * 4 + 1024 + 64;
     static_assert(SMEM_Q <= 227 * 1024 && SMEM_K <= 227 * 1024, "backward shared memory");
     auto kq = attn_tc_bwd_q_kernel<NPS, NP, H, D>;
@@ -865,9 +894,9 @@ int launch_bwd(const AttnTcParams& p, const void* f_p, const void* g_p, const vo
         attr = true;
     }
     const dim3 grid((p.N + 127) / 128, p.B);
-    kq<<<grid, 128, SMEM_Q, st>>>(p, tF, tG, tH, tDO);
+    kq<<<grid, 128 * kBwdGroups, SMEM_Q, st>>>(p, tF, tG, tH, tDO);
     GRL_LAUNCH_CHECK("attn_tc_bwd_q_kernel");
-    kk<<<grid, 128, SMEM_K, st>>>(p, tFq, tG, tH, tDOq);
+    kk<<<grid, 128 * kBwdGroups, SMEM_K, st>>>(p, tFq, tG, tH, tDOq);
     GRL_LAUNCH_CHECK("attn_tc_bwd_k_kernel");
     return 0;
 }

@@ -551,8 +551,35 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
     if GraphConvBackward.aggregate_first and h_weights.shape[1] <= sum(x.shape[1] for x in xs) and torch.is_grad_enabled() \
             and any(x.requires_grad for x in xs):
         return _GraphConv.apply(g, w_edge, h_weights, bias, relu, float(p), mask, seed, stream_id, *xs)
+    if not torch.is_grad_enabled() and len(xs) == 2:
+        # no-grad layers over a virtual concat (gcn3 = GraphConv([g1, g2])): aggregate every input on its own -- in eval the
+        # edge weights are the same object for all layers, so A' g1 of the previous layer (gcn2 = GraphConv([g1])) is reused
+        # instead of being aggregated again -- and project with one K segment per input
+        L1, F_total, C = g.L + 1, sum(x.shape[1] for x in xs), h_weights.shape[1]
+        w3 = h_weights.view(L1, F_total, C)
+        aggs, b_views, off = [], [], 0
+        for x in xs:
+            aggs.append(_aggregate_cached(g, w_edge, x))
+            b_views.append(w3[:, off:off + x.shape[1], :].reshape(L1 * x.shape[1], C).t())
+            off += x.shape[1]
+        return gemm_nt(aggs, b_views, None, bias, relu, p, mask, seed, stream_id)
+    if not torch.is_grad_enabled() and len(xs) == 1:
+        return linear_act([_aggregate_cached(g, w_edge, xs[0])], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
     new_v = spmm_aggregate(g, w_edge, xs)
     return linear_act([new_v], h_weights, bias, relu, p, mask, seed, stream_id, weight_is_kn=True)
+
+
+def _aggregate_cached(g: PackedGraphBatch, w_edge: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """A' x [B*N, (L+1) F] for a no-grad layer; the LAST aggregate is remembered on the weight tensor (keyed by the input's
+    storage and version), which is what lets gcn3 reuse gcn2's A' g1 in eval"""
+    key = (x.data_ptr(), x._version, tuple(x.shape), x.dtype)
+    hit = getattr(w_edge, "_grl_agg", None)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    y = torch.empty(g.num_nodes, (g.L + 1) * x.shape[1], dtype=x.dtype, device=x.device)
+    spmm_fwd_(g, w_edge, x, y.view(g.num_rows, x.shape[1]))
+    w_edge._grl_agg = (key, y, x)          # keeps x alive: the key is its address
+    return y
 
 
 class GraphConvBackward:

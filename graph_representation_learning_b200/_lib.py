@@ -110,6 +110,8 @@ SIGNATURES = {
     "grl_dz_split_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "grl_dz_split": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64,
                              c_int, c_uint32, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "grl_dz_colsum_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_uint32, c_float,
+                                   c_void_p, c_void_p, c_size_t, c_void_p]),
     "grl_split_act_mn": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "grl_gemm_tn_bc": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p,
                                c_int, c_void_p, c_size_t, c_void_p]),

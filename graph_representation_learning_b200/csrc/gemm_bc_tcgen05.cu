@@ -566,6 +566,51 @@ dz_split_kernel(const float* __restrict__ dY, int64_t lddy, const float* __restr
     }
 }
 
+// The same producer for bf16 activations (no operand split: the bf16 weight-gradient kernel reads dZ in place):
+//   dZ = bf16(dY * (Y > 0 ? 1/(1-p) : 0)),  partial[block][c] = column sums of the STORED dZ over the block's 32 rows.
+// Replaces bias_act_dropout_bwd + colsum (atomics) of the bf16 backward: one read of dY / Y, a bias gradient summed in a
+// fixed order.
+__global__ void __launch_bounds__(256)
+dz_colsum_bf16_kernel(const __nv_bfloat16* __restrict__ dY, int64_t lddy, const __nv_bfloat16* __restrict__ Y, int64_t ldy,
+                      __nv_bfloat16* __restrict__ dZ, int64_t lddz, int64_t M, int C, bool relu, float scale,
+                      float* __restrict__ partial) {
+    __shared__ float red[256 * 8];
+    const int groups = C >> 3, rows_per_pass = 256 / groups;
+    const int cg = threadIdx.x % groups, r_first = threadIdx.x / groups;
+    const int c0 = cg * 8;
+    const int64_t row0 = static_cast<int64_t>(blockIdx.x) * 32;
+    float sum[8] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    for (int r = r_first; r < 32; r += rows_per_pass) {
+        const int64_t m = row0 + r;
+        if (m >= M) continue;
+        float g[8], y[8];
+        Vec16<__nv_bfloat16>::load(dY + m * lddy + c0, g);
+        if (relu) {
+            Vec16<__nv_bfloat16>::load(Y + m * ldy + c0, y);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] = y[k] > 0.0f ? g[k] * scale : 0.0f;
+        }
+        const uint4 packed = Vec16<__nv_bfloat16>::pack(g);
+        *reinterpret_cast<uint4*>(dZ + m * lddz + c0) = packed;
+        const uint32_t w[4] = {packed.x, packed.y, packed.z, packed.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            sum[2 * k] += __uint_as_float(w[k] << 16);
+            sum[2 * k + 1] += __uint_as_float(w[k] & 0xFFFF0000u);
+        }
+    }
+    if (partial) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) red[r_first * C + c0 + k] = sum[k];
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += 256) {
+            float sacc = 0.0f;
+            for (int q = 0; q < rows_per_pass; ++q) sacc += red[q * C + c];
+            partial[static_cast<int64_t>(blockIdx.x) * C + c] = sacc;
+        }
+    }
+}
+
 // out[c] = sum_b partial[b][c] in a fixed order: thread (x, y) adds rows y, y + 32, ... of column blockIdx.x*32 + x, then the
 // 32 row-lane sums are added in lane order.  (A single block walking all partial rows serially costs 0.2 ms per layer.)
 __global__ void __launch_bounds__(1024) colsum_partials_kernel(const float* __restrict__ partial, int n_rows, int C,
@@ -676,6 +721,36 @@ extern "C" int grl_gemm_tn_bc(const float* A, int64_t lda, int Ma, const float* 
                                                                                     transpose_out, tA, tB, tBp, tA, tB, tBp);
     GRL_LAUNCH_CHECK("gemm_bc_kernel<TN>");
     return launch_reduce_splits(static_cast<const float*>(workspace), C, static_cast<int64_t>(Ma) * Nb, splits, st);
+}
+
+extern "C" size_t grl_dz_split_workspace_bytes(int64_t M, int C);
+
+extern "C" int grl_dz_colsum_bf16(const void* dY, int64_t lddy, const void* Y, int64_t ldy, void* dZ, int64_t lddz, int64_t M,
+                                  int C, uint32_t flags, float p, float* colsum_out, void* workspace, size_t workspace_bytes,
+                                  void* stream) {
+    GRL_CHECK_ARG(dY && dZ, GRL_E_BADARG, "grl_dz_colsum_bf16: null pointer");
+    GRL_CHECK_ARG(M > 0 && C > 0 && C % 8 == 0 && C <= 2048 && 256 % (C / 8) == 0, GRL_E_UNSUP,
+                  "grl_dz_colsum_bf16: C=%d must be a multiple of 8 with 256 %% (C/8) == 0", C);
+    const bool relu = (flags & GRL_EPI_RELU) != 0;
+    GRL_CHECK_ARG(relu || !(flags & GRL_EPI_DROPOUT) || p == 0.0f, GRL_E_UNSUP, "grl_dz_colsum_bf16: dropout without ReLU is not supported");
+    GRL_CHECK_ARG(!relu || Y, GRL_E_BADARG, "grl_dz_colsum_bf16: RELU needs the forward output Y");
+    GRL_CHECK_ARG(lddy % 8 == 0 && lddz % 8 == 0 && (!relu || ldy % 8 == 0) && aligned_to(dY, 16) && aligned_to(dZ, 16) &&
+                      (!relu || aligned_to(Y, 16)),
+                  GRL_E_ALIGN, "grl_dz_colsum_bf16: operands need 16-byte aligned bases and pitches");
+    GRL_CHECK_ARG(!colsum_out || (workspace && workspace_bytes >= grl_dz_split_workspace_bytes(M, C)), GRL_E_WORKSPACE,
+                  "grl_dz_colsum_bf16: workspace too small for the column sums");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const float scale = (flags & GRL_EPI_DROPOUT) ? 1.0f / (1.0f - p) : 1.0f;
+    const int blocks = static_cast<int>((M + 31) / 32);
+    dz_colsum_bf16_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dY), lddy, static_cast<const __nv_bfloat16*>(Y), ldy,
+                                                  static_cast<__nv_bfloat16*>(dZ), lddz, M, C, relu, scale,
+                                                  colsum_out ? static_cast<float*>(workspace) : nullptr);
+    GRL_LAUNCH_CHECK("dz_colsum_bf16_kernel");
+    if (colsum_out) {
+        colsum_partials_kernel<<<(C + 31) / 32, dim3(32, 32), 0, st>>>(static_cast<const float*>(workspace), blocks, C, colsum_out);
+        GRL_LAUNCH_CHECK("colsum_partials_kernel");
+    }
+    return 0;
 }
 
 extern "C" size_t grl_dz_split_workspace_bytes(int64_t M, int C) {

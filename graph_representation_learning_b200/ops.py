@@ -394,6 +394,18 @@ def _linear_grads(dY: torch.Tensor, y: Optional[torch.Tensor], xs: Sequence[torc
         _lib.count_launch(2 if want_b else 1)
         if split:
             cache[(dZ.data_ptr(), dZ.stride(0), M, C)] = (hi, packed, dZ)
+    elif (relu is True and dY.dtype == torch.bfloat16 and C % 8 == 0 and C <= 2048 and 256 % (C // 8) == 0 and M > 0 and
+          y.stride(0) % 8 == 0 and dY.stride(0) % 8 == 0):
+        # bf16: dZ and the bias gradient in one pass (grl_dz_colsum_bf16), the bias gradient summed in a fixed order
+        lib = _lib.load()
+        dZ = torch.empty_like(dY)
+        d_bias = torch.empty(C, dtype=torch.float32, device=dY.device) if want_b else None
+        ws = torch.empty(lib.grl_dz_split_workspace_bytes(M, C) if want_b else 0, dtype=torch.uint8, device=dY.device)
+        flags = _lib.EPI_RELU | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+        _lib.check(lib.grl_dz_colsum_bf16(dY.data_ptr(), dY.stride(0), y.data_ptr(), y.stride(0), dZ.data_ptr(), dZ.stride(0),
+                                          M, C, flags, float(p), _lib.ptr(d_bias), _lib.ptr(ws) if want_b else 0, ws.numel(),
+                                          _lib.stream_ptr(dY.device)), "grl_dz_colsum_bf16")
+        _lib.count_launch(2 if want_b else 1)
     elif relu or p > 0.0:
         dZ = torch.empty_like(dY)
         epilogue_bwd_(dY, y, dZ, relu, p)

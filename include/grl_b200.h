@@ -304,6 +304,13 @@ size_t grl_dz_split_workspace_bytes(int64_t M, int C);
 int grl_dz_split(const float* dY, int64_t lddy, const float* Y, int64_t ldy, float* dZ, int64_t lddz, float* hi,
                  void* packed, int64_t ld_split, int64_t M, int C, uint32_t flags, float p, float* colsum_out,
                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* The same for bf16 activations (no operand split: the bf16 weight-gradient kernel reads dZ in place):
+ *   dZ = bf16(dY * (Y > 0 ? 1/(1-p) : 0)),  colsum_out[c] = sum_m dZ[m, c] over the STORED values, in a fixed order.
+ * Workspace: grl_dz_split_workspace_bytes(M, C).  Replaces bias_act_dropout_bwd + colsum of the bf16 backward
+ * (autograd of F.relu + nn.Dropout and the bias gradient, drop_robust_gcn.py:64-100) with one pass. */
+int grl_dz_colsum_bf16(const void* dY, int64_t lddy, const void* Y, int64_t ldy, void* dZ, int64_t lddz, int64_t M, int C,
+                       uint32_t flags, float p, float* colsum_out, void* workspace, size_t workspace_bytes, void* stream);
 /* BatchNorm1d over the M node rows of X[M, C] followed by leaky ReLU(slope) -- GCNBlock / EmbeddingBlock of the DeepRP
  * sibling models (deep_rp_robust_gcn.py:30-62: nn.BatchNorm1d on [B, C, N] + F.leaky_relu(0.2)); fp32.
  * training != 0: batch statistics (biased variance) normalise, running_mean / running_var (may be null) are updated with

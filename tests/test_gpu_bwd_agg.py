@@ -88,3 +88,30 @@ def test_graphconv_gradients_aggregate_first(dev, dtype, widths, C, N):
     for k in range(len(widths)):
         assert rel_err(dx1[k], xs64[k].grad) < tol, (k, rel_err(dx1[k], xs64[k].grad))
         assert rel_err(dx1[k], dx0[k]) < tol_paths
+
+
+@pytest.mark.parametrize("M,C,p", [(1000, 512, 0.5), (777, 64, 0.0), (4097, 256, 0.3)])
+def test_bf16_dz_and_bias_gradient_in_one_pass(dev, M, C, p):
+    """grl_dz_colsum_bf16 (the bf16 backward of F.relu + nn.Dropout + the bias gradient in one pass) against the two
+    kernels it replaces: dZ bit for bit, the bias gradient to fp32 summation order -- and deterministic."""
+    from graph_representation_learning_b200 import _lib, ops
+    gen = torch.Generator().manual_seed(M + C)
+    dY = torch.randn(M, C, generator=gen).to(dev).bfloat16()
+    Y = (torch.randn(M, C, generator=gen).clamp_min(0) * (torch.rand(M, C, generator=gen) < 0.6)).to(dev).bfloat16()
+    ref_dz = torch.empty_like(dY)
+    ops.epilogue_bwd_(dY, Y, ref_dz, True, p)
+    ref_db = ops.colsum(ref_dz)
+    lib = _lib.load()
+    outs = []
+    for _ in range(2):
+        dZ = torch.empty_like(dY)
+        db = torch.empty(C, dtype=torch.float32, device=dev)
+        ws = torch.empty(lib.grl_dz_split_workspace_bytes(M, C), dtype=torch.uint8, device=dev)
+        flags = _lib.EPI_RELU | (_lib.EPI_DROPOUT if p > 0.0 else 0)
+        _lib.check(lib.grl_dz_colsum_bf16(dY.data_ptr(), dY.stride(0), Y.data_ptr(), Y.stride(0), dZ.data_ptr(), dZ.stride(0), M, C,
+                                          flags, float(p), db.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev)),
+                   "grl_dz_colsum_bf16")
+        outs.append((dZ, db))
+    assert torch.equal(outs[0][0], ref_dz)
+    assert torch.equal(outs[0][1], outs[1][1])
+    assert rel_err(outs[0][1], ref_dz.double().sum(0)) < 1e-6 and rel_err(ref_db, ref_dz.double().sum(0)) < 1e-5

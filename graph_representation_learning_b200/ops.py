@@ -561,7 +561,7 @@ def graph_conv(xs: Sequence[torch.Tensor], g: PackedGraphBatch, w_edge: torch.Te
         if out is not None:
             return out
     if GraphConvBackward.aggregate_first and h_weights.shape[1] <= sum(x.shape[1] for x in xs) and torch.is_grad_enabled() \
-            and any(x.requires_grad for x in xs):
+            and any(x.requires_grad for x in xs) and g.L + 1 <= 31:      # (the typed-transpose builder keeps a node's types one per lane)
         return _GraphConv.apply(g, w_edge, h_weights, bias, relu, float(p), mask, seed, stream_id, *xs)
     if not torch.is_grad_enabled() and len(xs) == 2:
         # no-grad layers over a virtual concat (gcn3 = GraphConv([g1, g2])): aggregate every input on its own -- in eval the

@@ -188,3 +188,23 @@ def test_product_model_refuses_cpu():
     m = GraphCNNDropEdge(8, 3, 6, net_size=16)
     with pytest.raises(GrlError):
         m([torch.zeros(1, 4, 8), torch.zeros(1, 4, 6, 4)])
+
+
+def test_fused_graphconv_policy_is_one_wave_of_clusters():
+    """ops.FusedGraphConv.wants: "auto" runs a no-grad GraphConv layer fused when its CTA clusters fit one wave of the
+    148 SMs (B * ceil(N / 128) tiles x ceil(C / 128) CTAs); True / False force it (host logic only)."""
+    from types import SimpleNamespace
+    from graph_representation_learning_b200 import ops
+    prev = ops.FusedGraphConv.enabled
+    try:
+        ops.FusedGraphConv.enabled = "auto"
+        assert ops.FusedGraphConv.wants(SimpleNamespace(B=64, N=100), 256)            # 64 tiles x 2 CTAs
+        assert not ops.FusedGraphConv.wants(SimpleNamespace(B=64, N=200), 256)        # 128 tiles x 2
+        assert ops.FusedGraphConv.wants(SimpleNamespace(B=8, N=200), 512)             # 16 tiles x 4
+        assert not ops.FusedGraphConv.wants(SimpleNamespace(B=256, N=500), 128)
+        ops.FusedGraphConv.enabled = True
+        assert ops.FusedGraphConv.wants(SimpleNamespace(B=256, N=500), 256)
+        ops.FusedGraphConv.enabled = False
+        assert not ops.FusedGraphConv.wants(SimpleNamespace(B=1, N=10), 64)
+    finally:
+        ops.FusedGraphConv.enabled = prev

@@ -260,7 +260,7 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
             const int maxkept = __reduce_max_sync(0xffffffffu, ni.y);
             // walk state: thr = (open row type + 1) << 24 (0: nothing open yet); S + x = gather address of entry x of
             // the open row; yrow = output row of the open typed row (one row before the node's first while none is)
-            uint32_t thr = 0, S = slab_lane;
+            uint32_t thr = 0;
             uint8_t* yrow = ynode - ldy;
             SlabAcc<T> acc[VW];
 #pragma unroll
@@ -269,7 +269,16 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
             // One entry (x = t << 24 | slab byte offset).  The first entry of a typed row stores the previous row,
             // zero-fills skipped rows, re-bases the state and starts the accumulator with a multiply
             // (w*x == fma(w, x, +0) up to the sign of zero).
-            auto walk_step = [&](uint32_t x, uint32_t wbits) {
+            // The gather address never depends on the walk state: S + x = slab_lane - (t_open << 24) + (t << 24 | offset) is
+            // slab_lane + offset for every entry of the open row, and a row opening re-bases S first.  So the gather of an
+            // entry is issued ONE STEP AHEAD (before the previous entry's compare / FMAs), which takes the LDS latency off
+            // the walk's dependency chain at the price of one mask per entry.
+            auto gather_of = [&](uint32_t x, Q (&q)[VW]) {
+                const uint32_t a = slab_lane + (x & 0x00FFFFFFu);
+#pragma unroll
+                for (int v = 0; v < VW; ++v) q[v] = SlabAcc<T>::gather(a + v * WORD_PITCH);
+            };
+            auto walk_step = [&](uint32_t x, uint32_t wbits, const Q (&q)[VW]) {
                 if (x >= thr) {
                     const uint32_t d = x - thr;                   // (typed rows skipped) << 24 | column offset
                     if (thr != 0u) {
@@ -282,12 +291,11 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
                     yrow = reinterpret_cast<uint8_t*>(yn);
                     const uint32_t tb = x & 0xFF000000u;
                     thr = tb + 0x01000000u;
-                    S = slab_lane - tb;
 #pragma unroll
-                    for (int v = 0; v < VW; ++v) acc[v].mul(SlabAcc<T>::gather(S + x + v * WORD_PITCH), wbits);
+                    for (int v = 0; v < VW; ++v) acc[v].mul(q[v], wbits);
                 } else {
 #pragma unroll
-                    for (int v = 0; v < VW; ++v) acc[v].fma(SlabAcc<T>::gather(S + x + v * WORD_PITCH), wbits);
+                    for (int v = 0; v < VW; ++v) acc[v].fma(q[v], wbits);
                 }
             };
 
@@ -326,15 +334,21 @@ spmm_slab2_kernel(const Slab2Params p, const __grid_constant__ CUtensorMap tmX) 
                 // ---------------- walk: 4 steps per iteration, entries fetched two at a time
                 uint32_t sa = stage_g;
                 uint4 ea = lds128(sa);
+                Q qa[VW], qb[VW];
+                gather_of(ea.x, qa);
 #pragma unroll 1
-                for (int k = 0; k < n; k += 4) {
-                    const uint4 eb2 = lds128(sa + 16);
-                    walk_step(ea.x, ea.y);
-                    walk_step(ea.z, ea.w);
+                for (int k = 0; k < n; k += 4) {             // every gather is issued one step ahead of its use (two ahead
+                    const uint4 eb2 = lds128(sa + 16);       // measured equal in fp32 and slower in bf16: registers)
+                    gather_of(ea.z, qb);
+                    walk_step(ea.x, ea.y, qa);
+                    gather_of(eb2.x, qa);
+                    walk_step(ea.z, ea.w, qb);
                     ea = lds128(sa + 32);
                     sa += 32;
-                    walk_step(eb2.x, eb2.y);
-                    walk_step(eb2.z, eb2.w);
+                    gather_of(eb2.z, qb);
+                    walk_step(eb2.x, eb2.y, qa);
+                    gather_of(ea.x, qa);                     // first entry of the next iteration (a terminator past the end)
+                    walk_step(eb2.z, eb2.w, qb);
                 }
                 __syncwarp();                                // staging is rewritten by the next batch
                 if (final_warp) break;

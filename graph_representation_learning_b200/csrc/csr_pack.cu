@@ -120,11 +120,64 @@ __global__ void __launch_bounds__(256) csr_fill_kernel(const T* __restrict__ adj
 // adjacency row, 1/16 of an fp16 A), so the fill pass never re-reads the dense tensor -- it walks the bitmap and fetches
 // only the stored values.  Loads of a row are issued four deep (the plain kernels keep one 8/16-byte load per lane in
 // flight: 0.24 + 0.36 ms for the 768 MB fp16 adjacency of cfg2, against 0.12 ms per pass at HBM speed).
+// The same test on a register copy: the bitmap pass issues every load of its rows first (plain predicated loads, no
+// tail path: its vector widths divide N) and only then looks at the bits -- with the test inlined next to each load the
+// compiler serialised them (one DRAM latency per 8-byte load: 2.0 TB/s on cfg2's adjacency).
+template <typename T, int VEC>
+__device__ __forceinline__ uint4 load_raw_vec(const T* p, bool ok) {
+    static_assert(sizeof(T) * VEC == 16 || sizeof(T) * VEC == 8, "vector loads of 8 or 16 bytes");
+    uint4 r = make_uint4(0u, 0u, 0u, 0u);
+    if constexpr (sizeof(T) * VEC == 16) {
+        if (ok) r = __ldcs(reinterpret_cast<const uint4*>(p));
+    } else {
+        if (ok) {
+            const uint2 t = __ldcs(reinterpret_cast<const uint2*>(p));
+            r.x = t.x;
+            r.y = t.y;
+        }
+    }
+    return r;
+}
+
+template <typename T, int VEC>
+__device__ __forceinline__ unsigned nz_bits_of(const uint4& r) {
+    constexpr int WORDS = static_cast<int>(sizeof(T)) * VEC / 4;
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+    unsigned bits = 0;
+#pragma unroll
+    for (int k = 0; k < WORDS; ++k) {
+        if constexpr (sizeof(T) == 4) {
+            bits |= ((w[k] << 1) != 0u) << k;                     // ignore the sign bit: -0.0 is zero
+        } else {
+            bits |= ((w[k] & 0x7FFFu) != 0u) << (2 * k);
+            bits |= ((w[k] & 0x7FFF0000u) != 0u) << (2 * k + 1);
+        }
+    }
+    return bits;
+}
+
+// Non-zero when some element of the vector is neither +0 nor exactly +1 (1.0 = 0x3C00 / 0x3F800000: a run of exponent
+// bits; anything else has a bit outside the run or two unequal neighbours inside it).  Three instructions per word.
+// -0.0 counts as "other": the batch then only takes the slower, still exact, value-fetching fill.
+template <typename T, int VEC>
+__device__ __forceinline__ uint32_t not_zero_or_one(const uint4& r) {
+    constexpr int WORDS = static_cast<int>(sizeof(T)) * VEC / 4;
+    constexpr uint32_t ONE = sizeof(T) == 4 ? 0x3F800000u : 0x3C003C00u;
+    constexpr uint32_t INNER = sizeof(T) == 4 ? 0x1F800000u : 0x1C001C00u;    // the run without its top bit
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+    uint32_t bad = 0;
+#pragma unroll
+    for (int k = 0; k < WORDS; ++k) bad |= (w[k] & ~ONE) | ((w[k] ^ (w[k] >> 1)) & INNER);
+    return bad;
+}
+
 template <typename T, int VEC>
 __global__ void __launch_bounds__(256) csr_count_bitmap_kernel(const T* __restrict__ adj, int64_t n_adj_rows, int N, int L,
                                                                int self_loop, int32_t* __restrict__ rowptr,
-                                                               uint32_t* __restrict__ bitmap, int words) {
+                                                               uint32_t* __restrict__ bitmap, int words,
+                                                               uint32_t* __restrict__ weighted) {
     constexpr int LPW = 32 / VEC;                        // lanes that share one 32-bit bitmap word
+    uint32_t other = 0;                                  // non-zero: this lane saw an element that is neither 0 nor 1
     const int lane = threadIdx.x & 31;
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
@@ -132,19 +185,44 @@ __global__ void __launch_bounds__(256) csr_count_bitmap_kernel(const T* __restri
     // two adjacency rows per warp iteration, all loads of both issued before the first use: the pass is bound by bytes in
     // flight per SM (one 1000-byte row per warp gave 2.9 TB/s)
     constexpr int ROWS = 2;
+    // (node, l) of row ar0 is stepped along with it: a 64-bit division per row was a third of this kernel's instructions
+    const uint32_t uL = static_cast<uint32_t>(L);
+    const uint32_t step_node = static_cast<uint32_t>((n_warps * ROWS) / uL), step_l = static_cast<uint32_t>((n_warps * ROWS) % uL);
+    uint32_t node0 = static_cast<uint32_t>((warp * ROWS) / uL), l0 = static_cast<uint32_t>((warp * ROWS) % uL);
     for (int64_t ar0 = warp * ROWS; ar0 < n_adj_rows; ar0 += n_warps * ROWS) {
         int cnt[ROWS];
 #pragma unroll
         for (int q = 0; q < ROWS; ++q) cnt[q] = 0;
         for (int jb = 0; jb < N; jb += 4 * 32 * VEC) {
             unsigned b[ROWS][4];
+            if constexpr (VEC > 1) {
+                uint4 raw[ROWS][4];
 #pragma unroll
-            for (int q = 0; q < ROWS; ++q) {
-                const T* row = adj + (ar0 + q) * N;
+                for (int q = 0; q < ROWS; ++q) {
+                    const T* row = adj + (ar0 + q) * N;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int j0 = jb + u * 32 * VEC + lane * VEC;
-                    b[q][u] = (ar0 + q < n_adj_rows && j0 < N) ? load_nz_bits<T, VEC>(row, j0, N) : 0u;
+                    for (int u = 0; u < 4; ++u) {
+                        const int j0 = jb + u * 32 * VEC + lane * VEC;
+                        raw[q][u] = load_raw_vec<T, VEC>(row + j0, ar0 + q < n_adj_rows && j0 < N);
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < ROWS; ++q)
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        b[q][u] = nz_bits_of<T, VEC>(raw[q][u]);
+                        other |= not_zero_or_one<T, VEC>(raw[q][u]);
+                    }
+            } else {
+#pragma unroll
+                for (int q = 0; q < ROWS; ++q) {
+                    const T* row = adj + (ar0 + q) * N;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int j0 = jb + u * 32 * VEC + lane * VEC;
+                        b[q][u] = (ar0 + q < n_adj_rows && j0 < N) ? load_nz_bits<T, VEC>(row, j0, N) : 0u;
+                        if (b[q][u]) other |= to_float(row[j0]) != 1.0f;      // VEC == 1: the one element of this lane
+                    }
                 }
             }
 #pragma unroll
@@ -168,57 +246,77 @@ __global__ void __launch_bounds__(256) csr_count_bitmap_kernel(const T* __restri
             for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
             const int64_t ar = ar0 + q;
             if (lane == 0 && ar < n_adj_rows) {
-                const int64_t node = ar / L;
-                const int l = static_cast<int>(ar - node * L);
-                const int64_t r = node * (L + self_loop) + l + self_loop;
+                uint32_t node = node0, l = l0 + q;
+                if (l >= uL) {
+                    l -= uL;
+                    ++node;
+                }
+                const int64_t r = static_cast<int64_t>(node) * (L + self_loop) + l + self_loop;
                 rowptr[r + 1] = c;
                 if (self_loop && l == 0) rowptr[r] = 1;
             }
         }
+        l0 += step_l;
+        node0 += step_node;
+        if (l0 >= uL) {
+            l0 -= uL;
+            ++node0;
+        }
     }
+    if (other) *weighted = 1u;                           // cleared by the launcher; every writer stores the same word
 }
 
+// One THREAD per (b, i, l) adjacency row: a row of cfg2 holds 8 entries in 16 bitmap words, so a warp per row spent ~100
+// warp instructions (scan shuffles, a divergent bit loop) on 8 stores; a lane walking its own row's words needs no
+// shuffle at all, the 32 rows of a warp are contiguous in the bitmap (L1 serves the re-touched sectors) and their entries
+// are contiguous in col / val.  The count pass left a word behind the bitmap: 0 = every stored value is 1 (a 0/1
+// adjacency) and nothing of A is read here -- a 2-byte value per entry costs a 32-byte DRAM sector at a random address.
+// Measured at cfg2 (6.3 M entries): 0.197 ms (warp per row) -> 0.147 ms with values fetched, 0.060 ms without.
 template <typename T>
 __global__ void __launch_bounds__(256) csr_fill_bitmap_kernel(const T* __restrict__ adj, const uint32_t* __restrict__ bitmap,
                                                               int words, int64_t n_adj_rows, int N, int L, int self_loop,
                                                               const int32_t* __restrict__ rowptr, int32_t* __restrict__ col,
                                                               float* __restrict__ val) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-    const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
-    for (int64_t ar = warp; ar < n_adj_rows; ar += n_warps) {
-        const int64_t node = ar / L;
-        const int l = static_cast<int>(ar - node * L);
-        const int64_t r = node * (L + self_loop) + l + self_loop;
-        if (self_loop && l == 0 && lane == 0) {
-            const int32_t e = rowptr[r - 1];
-            col[e] = static_cast<int32_t>(node % N);
-            val[e] = 1.0f;
+    const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    const bool weighted = __ldg(bitmap + n_adj_rows * words) != 0u;
+    const uint32_t uL = static_cast<uint32_t>(L);
+    const bool vec4 = (words & 3) == 0 && (reinterpret_cast<uintptr_t>(bitmap) & 15) == 0;   // 16-byte aligned bitmap rows
+    for (int64_t ar = tid; ar < n_adj_rows; ar += stride) {
+        const uint32_t node = static_cast<uint32_t>(ar) / uL;          // n_adj_rows < 2^31 (checked by the launcher)
+        const uint32_t l = static_cast<uint32_t>(ar) - node * uL;
+        const int64_t r = static_cast<int64_t>(node) * (L + self_loop) + l + self_loop;
+        int32_t pos = __ldg(rowptr + r);
+        const int32_t end = __ldg(rowptr + r + 1);                     // may be the clamped capacity (grl_csr_clamp_rowptr)
+        if (self_loop && l == 0) {
+            // the self-loop row (t = 0) holds exactly the diagonal entry; empty when the capacity clamp cut it off
+            const int32_t e = __ldg(rowptr + r - 1);
+            if (e < pos) {
+                col[e] = static_cast<int32_t>(node % static_cast<uint32_t>(N));
+                val[e] = 1.0f;
+            }
         }
-        int32_t out = rowptr[r];
-        const int32_t end = rowptr[r + 1];
-        if (out == end) continue;
         const T* row = adj + ar * N;
         const uint32_t* brow = bitmap + ar * words;
-        for (int wb = 0; wb < words && out < end; wb += 32) {
-            unsigned bits = (wb + lane < words) ? __ldg(brow + wb + lane) : 0u;
-            const int mine = __popc(bits);
-            int incl = mine;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
-            }
-            int pos = out + incl - mine;
-            const int j_base = (wb + lane) << 5;
-            while (bits) {
+        auto emit = [&](uint32_t bits, int j_base) {
+            while (bits && pos < end) {
                 const int k = __ffs(bits) - 1;
                 bits &= bits - 1;
                 col[pos] = j_base + k;
-                val[pos] = to_float(row[j_base + k]);
+                val[pos] = weighted ? to_float(row[j_base + k]) : 1.0f;
                 ++pos;
             }
-            out += __shfl_sync(0xffffffffu, incl, 31);
+        };
+        if (vec4) {
+            for (int w = 0; w < words && pos < end; w += 4) {
+                const uint4 q = __ldg(reinterpret_cast<const uint4*>(brow + w));
+                emit(q.x, w << 5);
+                emit(q.y, (w + 1) << 5);
+                emit(q.z, (w + 2) << 5);
+                emit(q.w, (w + 3) << 5);
+            }
+        } else {
+            for (int w = 0; w < words && pos < end; ++w) emit(__ldg(brow + w), w << 5);
         }
     }
 }
@@ -439,12 +537,15 @@ static int launch_count_bitmap(const T* adj, int B, int N, int L, int self_loop,
     const int grid = grid_for(rows * 32, 256);
     const int words = (N + 31) / 32;
     constexpr int V16 = 16 / sizeof(T), V8 = 8 / sizeof(T);
+    uint32_t* weighted = bitmap + rows * words;          // trailer word of the bitmap buffer (grl_csr_bitmap_bytes)
+    cudaError_t e = cudaMemsetAsync(weighted, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(bitmap trailer)");
     if (N % V16 == 0 && aligned_to(adj, 16))
-        csr_count_bitmap_kernel<T, V16><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words);
+        csr_count_bitmap_kernel<T, V16><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words, weighted);
     else if (N % V8 == 0 && aligned_to(adj, 8))
-        csr_count_bitmap_kernel<T, V8><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words);
+        csr_count_bitmap_kernel<T, V8><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words, weighted);
     else
-        csr_count_bitmap_kernel<T, 1><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words);
+        csr_count_bitmap_kernel<T, 1><<<grid, 256, 0, st>>>(adj, rows, N, L, self_loop, rowptr, bitmap, words, weighted);
     GRL_LAUNCH_CHECK("csr_count_bitmap_kernel");
     return 0;
 }
@@ -454,7 +555,8 @@ static int launch_count_bitmap(const T* adj, int B, int N, int L, int self_loop,
 using namespace grl;
 
 extern "C" size_t grl_csr_bitmap_bytes(int B, int N, int L) {
-    return sizeof(uint32_t) * static_cast<size_t>(B) * N * L * ((N + 31) / 32);
+    // one bit per element, row-major, plus a trailer word: 0 = every stored value is exactly 1 (the fill pass then skips A)
+    return sizeof(uint32_t) * (static_cast<size_t>(B) * N * L * ((N + 31) / 32) + 4);
 }
 
 extern "C" int grl_csr_count_bitmap(const void* adj, int adj_dtype, int B, int N, int L, int self_loop, int32_t* rowptr,
@@ -478,7 +580,8 @@ extern "C" int grl_csr_fill_bitmap(const void* adj, int adj_dtype, const void* b
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     self_loop = self_loop ? 1 : 0;
     const int64_t rows = static_cast<int64_t>(B) * N * L;
-    const int grid = grid_for(rows * 32, 256);
+    GRL_CHECK_ARG(rows < INT32_MAX, GRL_E_UNSUP, "grl_csr_fill_bitmap: too many rows for int32");
+    const int grid = grid_for(rows, 256);                // one thread per row
     const int words = (N + 31) / 32;
     const uint32_t* bm = static_cast<const uint32_t*>(bitmap);
     if (adj_dtype == GRL_F32)

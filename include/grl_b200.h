@@ -84,7 +84,9 @@ int grl_csr_fill(const void* adj, int adj_dtype, int B, int N, int L, int self_l
 
 /* The same pack with ONE read of the dense tensor: the count pass also writes one bit per element (row-major,
  * ceil(N/32) uint32 words per (b, i, l) row; grl_csr_bitmap_bytes), the fill pass walks the bitmap and fetches only the
- * stored values.  Same rowptr / col / val, bit for bit. */
+ * stored values.  Same rowptr / col / val, bit for bit.  The buffer ends in a trailer word the count pass sets when any
+ * stored value differs from 1: for a 0/1 adjacency the fill pass writes 1.0 and does not touch `adj` at all (a 2-byte value
+ * per entry costs a 32-byte DRAM sector at a random address).  `bitmap` must come from grl_csr_count_bitmap. */
 size_t grl_csr_bitmap_bytes(int B, int N, int L);
 int grl_csr_count_bitmap(const void* adj, int adj_dtype, int B, int N, int L, int self_loop,
                          int32_t* rowptr, void* bitmap, void* stream);

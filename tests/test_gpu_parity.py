@@ -715,6 +715,23 @@ def test_csr_pack_single_read_bitmap_equals_two_pass_pack(dev, B, N, L, dtype, d
     assert int(outs[1][0][-1]) == int((A.float() != 0).sum()) + B * N
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+@pytest.mark.parametrize("odd", [None, 2.0, -1.0, 0.5, 6.1e-5, 0.0625, 1.5])
+def test_csr_pack_fetches_values_unless_every_one_is_1(dev, dtype, odd):
+    """the count pass flags a batch that holds ANY stored value other than +1 (one element out of 1.2 M here: -1, a value
+    whose bits are a subset of 1.0's, a near-subnormal half); only an all-ones batch lets the fill pass skip the dense tensor"""
+    from graph_representation_learning_b200 import PackedGraphBatch
+    gen = torch.Generator().manual_seed(11)
+    B, N, L = 2, 100, 6
+    A = (torch.rand(B, N, L, N, generator=gen) < 0.05).float()
+    if odd is not None:
+        A[1, 57, 3, 99] = odd
+    A = A.to(dtype).to(dev)
+    g = PackedGraphBatch.from_dense(A, with_transpose=False)
+    dense = g.to_dense(g.val)                                       # [B, (L+1) N, N], identity block at t = 0
+    eye = torch.eye(N, device=dev).view(1, N, 1, N).expand(B, N, 1, N)
+    want = torch.cat([eye, A.float()], 2).reshape(B, N * (L + 1), N)
+    assert torch.equal(dense, want)
 
 
 # ---------------------------------------------------------------------------------------- advisor findings (round 1)

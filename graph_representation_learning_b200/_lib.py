@@ -88,6 +88,7 @@ SIGNATURES = {
     "grl_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p,
                            c_void_p, c_int64, c_void_p]),
     "grl_l2_norm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "grl_l2_norm_static": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
     "grl_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float, c_float,
                               c_float, c_int64, c_void_p, c_float, c_void_p]),
     "grl_colsum": (c_int, [c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p]),

@@ -9,6 +9,7 @@
 //                             moment buffer, with the clip coefficient min(1, max_norm / (norm + 1e-6)) applied on the
 //                             fly from the device-resident norm (no host sync between clip and step).
 #include "common.cuh"
+#include <mutex>
 
 namespace grl {
 
@@ -205,6 +206,64 @@ extern "C" int grl_l2_norm(const float* x, int64_t n, float* out, void* workspac
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int blocks = grid_for(n, kTrainThreads * 4);
     float* partial = static_cast<float*>(workspace);
+    sumsq_kernel<<<blocks, kTrainThreads, 0, st>>>(x, n, partial);
+    GRL_LAUNCH_CHECK("sumsq_kernel");
+    norm_finish_kernel<<<1, kTrainThreads, 0, st>>>(partial, blocks, out);
+    GRL_LAUNCH_CHECK("norm_finish_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------- grl_l2_norm without any allocation by anybody
+// The block partial sums of sumsq_kernel live in a file-scope device array instead of a caller workspace, for callers that
+// cannot allocate (CUDA graph capture, serving loops).  Every GPU that loads the library holds the 16 KB until exit.  The
+// array's name is only a host-side handle here: its device address is looked up once per device, with that device
+// current, and that pointer is what the kernels get.  Nothing in the array has to start at zero (sumsq_kernel overwrites
+// the `blocks` partials norm_finish_kernel reads); calls that overlap on one GPU (two streams) race on it.
+namespace grl {
+constexpr int kL2StaticFloats = 4096;                                  // 16 KB of block partials
+constexpr int64_t kL2StaticMaxN = int64_t(1) << 28;                    // 268 435 456 floats (1 GiB of gradients)
+static __device__ __align__(256) float g_l2_static_scratch[kL2StaticFloats];
+
+static int l2_static_scratch_ptr(float** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static float* ptrs[kMaxDevices] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("grl_l2_norm_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+        return GRL_E_UNSUP;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_l2_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_l2_static_scratch)");
+        if (!p) {
+            set_error("grl_l2_norm_static: cudaGetSymbolAddress returned a null device address");
+            return static_cast<int>(cudaErrorInvalidSymbol);
+        }
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+}  // namespace grl
+
+extern "C" int grl_l2_norm_static(const float* x, int64_t n, float* out, void* stream) {
+    GRL_CHECK_ARG(x && out, GRL_E_BADARG, "grl_l2_norm_static: null pointer");
+    GRL_CHECK_ARG(n > 0, GRL_E_BADARG, "grl_l2_norm_static: n <= 0");
+    GRL_CHECK_ARG(n <= kL2StaticMaxN, GRL_E_UNSUP,
+                  "grl_l2_norm_static: n = %lld exceeds the %lld elements this entry point serves (use grl_l2_norm with a "
+                  "caller workspace)", static_cast<long long>(n), static_cast<long long>(kL2StaticMaxN));
+    const int blocks = grid_for(n, kTrainThreads * 4);                 // the same launch shape as grl_l2_norm: same bits
+    GRL_CHECK_ARG(blocks <= kL2StaticFloats, GRL_E_UNSUP, "grl_l2_norm_static: %d block partials exceed the static scratch (%d)",
+                  blocks, kL2StaticFloats);
+    float* partial = nullptr;
+    const int rc = l2_static_scratch_ptr(&partial);
+    if (rc != 0) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
     sumsq_kernel<<<blocks, kTrainThreads, 0, st>>>(x, n, partial);
     GRL_LAUNCH_CHECK("sumsq_kernel");
     norm_finish_kernel<<<1, kTrainThreads, 0, st>>>(partial, blocks, out);

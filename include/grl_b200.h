@@ -406,6 +406,13 @@ int grl_ce_bwd(const float* logits, int64_t ld, const int64_t* target, const flo
                int64_t M, int C, const float* lse, const float* loss_out, const float* grad_out,
                float* dlogits, int64_t ldd, void* stream);
 int grl_l2_norm(const float* x, int64_t n, float* out, void* workspace, void* stream);
+/* grl_l2_norm with NO workspace argument and no allocation anywhere (no counterpart in the reference: added
+ * for callers that cannot allocate -- CUDA graph capture, serving loops).  The block partial sums
+ * live in a 16 KB file-scope device array (4096 floats; every GPU that loads the library holds it until exit), whose
+ * device address is looked up once per device.  Serves n <= 2^28 floats (GRL_E_UNSUP beyond: use grl_l2_norm); same launch
+ * shape and summation order as grl_l2_norm, so out[0] has the same bits.  Nothing in the array carries over between calls,
+ * but calls that OVERLAP on one GPU (two streams) share it and race: serialise them. */
+int grl_l2_norm_static(const float* x, int64_t n, float* out, void* stream);
 int grl_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                   float eps, float weight_decay, int64_t step, const float* grad_norm, float max_norm, void* stream);
 

@@ -52,6 +52,7 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
     "grl_stream_from_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p,
                                         c_void_p]),
+    "grl_typed_transpose": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "grl_csc_typed_regroup": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                       c_void_p]),
     "grl_spmm_fwd_stream": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int,

@@ -148,7 +148,7 @@ class PackedGraphBatch:
         _lib.count_launch(1)
         g = PackedGraphBatch(B, N, L, nnz, rowptr, col, val)
         if with_transpose:
-            g.build_transpose()
+            g.prepare_backward()
         return g
 
     @staticmethod
@@ -187,8 +187,17 @@ class PackedGraphBatch:
         _lib.count_launch(5)
         g = PackedGraphBatch(B, N, L, nnz, rowptr, col, val)
         if with_transpose:
-            g.build_transpose()
+            g.prepare_backward()
         return g
+
+    def prepare_backward(self) -> None:
+        """Build now what the backward aggregation will read: the typed transpose (aggregate-then-project form,
+        ops._GraphConv) when the model's edge types fit its kernels, else the CSC of the legacy transposed SpMM.  Both are
+        also built on first use."""
+        if self.L + 1 <= 31:
+            self.typed_transpose()
+        else:
+            self.build_transpose()
 
     def build_transpose(self) -> None:
         """CSC + perm for the transposed SpMM of the backward pass (csrc/csr_pack.cu)."""
@@ -215,19 +224,35 @@ class PackedGraphBatch:
         it (ops._GraphConv: dX = sum_t (A_t^T dZ) W_t^T, autograd of robust_gcn.py:45-50)."""
         if self._typed_T is not None:
             return self._typed_T
-        self.build_transpose()
         dev = self.device
+        lib = _lib.load()
         t_rowptr = torch.empty(self.num_rows + 1, dtype=torch.int32, device=dev)
         t_col = torch.empty(self.nnz, dtype=torch.int32, device=dev)
         t_perm = torch.empty(self.nnz, dtype=torch.int32, device=dev)
-        _lib.check(_lib.load().grl_csc_typed_regroup(self.colptr.data_ptr(), self.rowidx.data_ptr(), self.perm.data_ptr(),
-                                                     self.B, self.N, self.L, t_rowptr.data_ptr(), t_col.data_ptr(),
-                                                     t_perm.data_ptr(), _lib.stream_ptr(dev)), "grl_csc_typed_regroup")
-        _lib.count_launch(1)
+        rc = _lib.GRL_E_UNSUP
+        if self.direct_typed_transpose and self.colptr is None:
+            # one CTA per graph, counters in shared memory (csrc/typed_transpose.cu); graphs too large for that take the CSC
+            rc = lib.grl_typed_transpose(self.rowptr.data_ptr(), self.col.data_ptr(), self.B, self.N, self.L,
+                                         t_rowptr.data_ptr(), t_col.data_ptr(), t_perm.data_ptr(), _lib.stream_ptr(dev))
+            if rc != _lib.GRL_E_UNSUP:
+                _lib.check(rc, "grl_typed_transpose")
+                _lib.count_launch(1)
+        if rc == _lib.GRL_E_UNSUP:
+            self._typed_from_csc(t_rowptr, t_col, t_perm)
         gT = PackedGraphBatch(self.B, self.N, self.L, self.nnz, t_rowptr, t_col, self.val)
         gT.t_perm = t_perm
         self._typed_T = gT
         return gT
+
+    direct_typed_transpose = True      # tests switch it off to compare the two builds
+
+    def _typed_from_csc(self, t_rowptr, t_col, t_perm) -> None:
+        self.build_transpose()
+        dev = self.device
+        _lib.check(_lib.load().grl_csc_typed_regroup(self.colptr.data_ptr(), self.rowidx.data_ptr(), self.perm.data_ptr(),
+                                                     self.B, self.N, self.L, t_rowptr.data_ptr(), t_col.data_ptr(),
+                                                     t_perm.data_ptr(), _lib.stream_ptr(dev)), "grl_csc_typed_regroup")
+        _lib.count_launch(1)
 
     def transposed_weights(self, w: torch.Tensor) -> torch.Tensor:
         """per-entry weights ``w`` of this packing (one GraphConv layer's DropEdge weights) in the entry order of

@@ -160,6 +160,12 @@ class RanPACLayer(nn.Module):
         return ops.linear_act([_flat(x)], self.projection.weight, None).view(*x.shape[:-1], -1)
 
 
+def _pack_dense(A: torch.Tensor, training: bool) -> PackedGraphBatch:
+    """CSR pack of a dense [B, N, L, N] batch adjacency; the transposes of the backward only when a backward can follow"""
+    grad = torch.is_grad_enabled()
+    return PackedGraphBatch.from_dense(A, sync_free=training and grad, with_transpose=grad)
+
+
 @register_model
 class GraphCNNDropEdge(BaseNetwork):
     def __init__(self, input_dim: int, output_dim: int, num_edges: int, net_size: int = 256,
@@ -214,7 +220,7 @@ class GraphCNNDropEdge(BaseNetwork):
         sparse_v = isinstance(V, SparseNodeFeatures)
         _lib.require_cuda(V.val if sparse_v else V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
+        g = A if isinstance(A, PackedGraphBatch) else _pack_dense(A, self.training)
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -303,7 +309,7 @@ class RobustGCN(BaseNetwork):
         V, A = inputs
         _lib.require_cuda(V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
+        g = A if isinstance(A, PackedGraphBatch) else _pack_dense(A, self.training)
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -370,7 +376,7 @@ class RPGraphCNNDropEdge(BaseNetwork):
         sparse_v = isinstance(V, SparseNodeFeatures)
         _lib.require_cuda(V.val if sparse_v else V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
+        g = A if isinstance(A, PackedGraphBatch) else _pack_dense(A, self.training)
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -470,7 +476,7 @@ class DeepRPRobustGCN(BaseNetwork):
         V, A = inputs
         _lib.require_cuda(V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
+        g = A if isinstance(A, PackedGraphBatch) else _pack_dense(A, self.training)
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")
@@ -549,7 +555,7 @@ class DeepRPGCN(BaseNetwork):
         V, A = inputs
         _lib.require_cuda(V, "V")
         B, N = V.shape[0], V.shape[1]
-        g = A if isinstance(A, PackedGraphBatch) else PackedGraphBatch.from_dense(A, sync_free=self.training and torch.is_grad_enabled())
+        g = A if isinstance(A, PackedGraphBatch) else _pack_dense(A, self.training)
         if g.B != B or g.N != N or g.L != self.num_edges:
             raise _lib.GrlError(f"graph batch (B={g.B}, N={g.N}, L={g.L}) does not match V {tuple(V.shape)} / "
                                 f"num_edges={self.num_edges}")

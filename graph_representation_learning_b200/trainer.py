@@ -711,7 +711,9 @@ class DevicePrefetcher:
                     for t in v.tensors():
                         t.record_stream(main)
                 elif hasattr(v, "rowptr"):
-                    for t in (v.rowptr, v.col, v.val, v.colptr, v.rowidx, v.perm):
+                    gT = getattr(v, "_typed_T", None)      # built on the copy stream by prepare_backward()
+                    for t in (v.rowptr, v.col, v.val, v.colptr, v.rowidx, v.perm,
+                              *((gT.rowptr, gT.col, gT.t_perm) if gT is not None else ())):
                         if t is not None:
                             t.record_stream(main)
             try:

@@ -213,6 +213,11 @@ int grl_spmm_set_tile_mode(int mode);
  * (dX = sum_t (A_t^T dZ) W_t^T,  robust_gcn.py:45-50). */
 int grl_csc_typed_regroup(const int32_t* colptr, const int32_t* rowidx, const int32_t* perm, int B, int N, int L,
                           int32_t* t_rowptr, int32_t* t_col, int32_t* t_perm, void* stream);
+/* The same three arrays built DIRECTLY from the forward packing, one CTA per graph with the N (L+1) typed-row counters in
+ * shared memory (csrc/typed_transpose.cu): no CSC, no global atomics, one launch.  GRL_E_UNSUP when a graph's counters do
+ * not fit (N (L+1) > 21 500): the caller then goes through grl_csr_transpose + grl_csc_typed_regroup.  Bit-identical. */
+int grl_typed_transpose(const int32_t* rowptr, const int32_t* col, int B, int N, int L,
+                        int32_t* t_rowptr, int32_t* t_col, int32_t* t_perm, void* stream);
 
 /* Transposed SpMM (gradient wrt V).  Replaces autograd of robust_gcn.py:45-47.
  *   dX[b*N+j, 0:F] = sum_{k in column (b*N+j)} w[perm[k]] * dY[rowidx[k], 0:F]

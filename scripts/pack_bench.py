@@ -42,3 +42,13 @@ tw = timeit(lambda: lib.grl_csr_fill_bitmap(A2.data_ptr(), code, bitmap.data_ptr
                                             col2.data_ptr(), val2.data_ptr(), st))
 assert torch.equal(col2, g2.col) and torch.equal(val2, g2.val)
 print(f"fill from bitmap, weighted adjacency {tw:.3f} ms")
+
+# typed transpose of the batch: one CTA per graph (csrc/typed_transpose.cu) against CSC + regroup by type
+def typed(direct):
+    h = PackedGraphBatch(g.B, g.N, g.L, g.nnz, g.rowptr, g.col, g.val)
+    h.direct_typed_transpose = direct
+    return h.typed_transpose()
+td, tc2 = timeit(lambda: typed(True)), timeit(lambda: typed(False))
+a, b = typed(True), typed(False)
+assert torch.equal(a.rowptr, b.rowptr) and torch.equal(a.col, b.col) and torch.equal(a.t_perm, b.t_perm)
+print(f"typed transpose: direct {td:.3f} ms, through the CSC {tc2:.3f} ms")

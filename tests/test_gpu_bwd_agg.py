@@ -44,6 +44,61 @@ def test_typed_transpose_is_the_dense_transpose(dev, B, N, density, weighted):
     assert getattr(wT, "_grl_stream", None) is not None
 
 
+def _both_builds(g):
+    """(t_rowptr, t_col, t_perm) from the one-CTA-per-graph kernel and from the CSC route"""
+    from graph_representation_learning_b200 import PackedGraphBatch
+    outs = []
+    for direct in (True, False):
+        h = PackedGraphBatch(g.B, g.N, g.L, g.nnz, g.rowptr, g.col, g.val)
+        h.direct_typed_transpose = direct
+        gT = h.typed_transpose()
+        assert (h.colptr is None) == direct, "the wrong build ran"
+        outs.append((gT.rowptr, gT.col, gT.t_perm))
+    return outs
+
+
+@pytest.mark.parametrize("case", ["sparse", "mid_rows", "hub", "many_hubs", "dense_small", "empty", "two_waves", "edges_dup"])
+def test_direct_typed_transpose_equals_the_csc_route_bit_for_bit(dev, case):
+    """csrc/typed_transpose.cu against grl_csr_transpose + grl_csc_typed_regroup: rows sorted by their owner thread
+    (<= 32 entries), by a warp through shared memory (<= 256), hub rows rebuilt by the CTA (listed, and more than the list
+    holds), more graphs than SMs, graphs without edges, duplicate edges from an edge list."""
+    from graph_representation_learning_b200 import PackedGraphBatch
+    gen = torch.Generator().manual_seed(len(case))
+    L = 6
+    if case == "edges_dup":
+        B, N = 2, 50
+        e = torch.stack([torch.randint(0, B, (4000,), generator=gen), torch.randint(0, N, (4000,), generator=gen),
+                         torch.randint(0, L, (4000,), generator=gen), torch.randint(0, 3, (4000,), generator=gen)], 1).int()
+        g = PackedGraphBatch.from_edges(e.to(dev), B, N, L, with_transpose=False)     # ~ 4 copies of every (i, l, j < 3)
+    else:
+        B, N, dens = {"sparse": (3, 300, 0.02), "mid_rows": (2, 400, 0.3), "hub": (2, 600, 0.01), "many_hubs": (1, 300, 0.95),
+                      "dense_small": (4, 40, 1.0), "empty": (3, 64, 0.0), "two_waves": (310, 24, 0.2)}[case]
+        A = (torch.rand(B, N, L, N, generator=gen) < dens)
+        if case == "hub":
+            A[:, :, 2, 7] = True                                     # every node points at node 7 through type 2: d = N
+            A[1, :, 5, 599] = True
+        g = PackedGraphBatch.from_dense(A.half().to(dev), with_transpose=False)
+    (ra, ca, pa), (rb, cb, pb) = _both_builds(g)
+    nnz = int(g.rowptr[-1])
+    assert torch.equal(ra, rb)
+    assert torch.equal(pa[:nnz], pb[:nnz])
+    assert torch.equal(ca[:nnz], cb[:nnz])
+
+
+def test_direct_typed_transpose_declines_graphs_whose_counters_do_not_fit(dev):
+    from graph_representation_learning_b200 import PackedGraphBatch, _lib
+    N, L = 5000, 6                                                   # 35 000 typed rows per graph > 34 816
+    e = torch.tensor([[0, 1, 2, 3], [0, 4999, 5, 0]], dtype=torch.int32, device=dev)
+    g = PackedGraphBatch.from_edges(e, 1, N, L, with_transpose=False)
+    t = [torch.empty(g.num_rows + 1, dtype=torch.int32, device=dev), torch.empty(g.nnz, dtype=torch.int32, device=dev),
+         torch.empty(g.nnz, dtype=torch.int32, device=dev)]
+    rc = _lib.load().grl_typed_transpose(g.rowptr.data_ptr(), g.col.data_ptr(), 1, N, L, t[0].data_ptr(), t[1].data_ptr(),
+                                         t[2].data_ptr(), _lib.stream_ptr(dev))
+    assert rc == _lib.GRL_E_UNSUP
+    gT = g.typed_transpose()                                         # the public path still answers, through the CSC
+    assert g.colptr is not None and int(gT.rowptr[-1]) == int(g.rowptr[-1])
+
+
 @pytest.mark.parametrize("dtype,widths,C,N", [(torch.float32, (64,), 64, 130), (torch.float32, (128, 128), 128, 300),
                                               (torch.bfloat16, (128,), 128, 257)])
 def test_graphconv_gradients_aggregate_first(dev, dtype, widths, C, N):

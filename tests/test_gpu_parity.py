@@ -66,6 +66,7 @@ def test_csr_pack_and_transpose_bit_exact(dev, B, N, L, density):
     order = torch.sort(gcol, stable=True).indices
     colptr = torch.zeros(B * N + 1, dtype=torch.int64)
     colptr[1:] = torch.cumsum(torch.bincount(gcol, minlength=B * N), 0)
+    g.build_transpose()                                               # the CSC is built on demand (legacy backward)
     assert torch.equal(g.colptr.cpu().long(), colptr)
     assert torch.equal(g.perm.cpu().long(), order)
     assert torch.equal(g.rowidx.cpu().long(), rows[order])
@@ -82,6 +83,7 @@ def test_edge_list_pack_equals_dense_pack(dev):
     edges = A.nonzero()[:, [0, 1, 2, 3]].to(torch.int32)
     edges = edges[torch.randperm(edges.shape[0], generator=gen)]          # arrival order must not matter
     ge = PackedGraphBatch.from_edges(edges.to(dev), B, N, L)
+    gd.build_transpose(), ge.build_transpose()
     for name in ("rowptr", "col", "val", "colptr", "rowidx", "perm"):
         assert torch.equal(getattr(gd, name), getattr(ge, name)), name
     empty = PackedGraphBatch.from_edges(torch.zeros(0, 4, dtype=torch.int32, device=dev), 2, 5, L)
@@ -490,6 +492,7 @@ def test_model_eval_on_edge_list_equals_dense_path(dev):
     edges = torch.stack([b, i, l, j], 1).to(torch.int32)
     edges = edges[torch.randperm(edges.shape[0], device=dev)]                    # the pack must not depend on edge order
     g_d, g_e = PackedGraphBatch.from_dense(A), PackedGraphBatch.from_edges(edges, wl.B, wl.N, wl.num_edges)
+    g_d.build_transpose(), g_e.build_transpose()
     for name in ("rowptr", "col", "val", "colptr", "rowidx", "perm"):
         assert torch.equal(getattr(g_d, name), getattr(g_e, name)), name
     torch.manual_seed(2)

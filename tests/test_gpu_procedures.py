@@ -38,6 +38,7 @@ def test_edge_list_collate_packs_the_same_graph_as_the_dense_collate():
     host = C.EdgeListCollate(num_edges=6)([dict(s) for s in samples])
     packed = C.EdgeListCollate.to_device(host, dev)
     g_edge, g_dense = packed["adjacency_matrix"], PackedGraphBatch.from_dense(dense["adjacency_matrix"].to(dev))
+    g_edge.build_transpose(), g_dense.build_transpose()
     for name in ("rowptr", "col", "val", "colptr", "rowidx", "perm"):
         assert torch.equal(getattr(g_edge, name), getattr(g_dense, name)), name            # integer work: bit-exact
     assert torch.equal(packed["node_label"].cpu(), dense["node_label"])

@@ -232,7 +232,7 @@ gemm_bc_2sm_kernel(const GemmParams p, const int promo, const int n_pairs, const
             for (int q = 0; q < X3Cfg::DRAIN_COLS; ++q) acc[q] = 0.0f;
             for (int c = 0; c < n_chunks; ++c, ++cg) {
                 const int buf = cg & 1;
-                mbar_wait(&acc_full[buf], (cg >> 1) & 1);
+                mbar_wait_parked(&acc_full[buf], (cg >> 1) & 1);
                 tc_fence_after_sync();
                 uint32_t r0[32], r1[32];
                 tmem_ld_32x32(lane_base + buf * 128, r0);
@@ -422,7 +422,7 @@ gemm_bc_tn_2sm_kernel(const GemmParams p, const int promo, const int kb_per_spli
         for (int q = 0; q < X3Cfg::DRAIN_COLS; ++q) acc[q] = 0.0f;
         for (int c = 0; c < n_chunks; ++c) {
             const int buf = c & 1;
-            mbar_wait(&acc_full[buf], (c >> 1) & 1);
+            mbar_wait_parked(&acc_full[buf], (c >> 1) & 1);
             tc_fence_after_sync();
             uint32_t r0[32], r1[32];
             tmem_ld_32x32(lane_base + buf * 128, r0);
@@ -589,7 +589,7 @@ gemm_nt_bf16_2sm_kernel(const GemmParams p, int n_pairs, int tiles_n, const __gr
         for (int t = t_first; t < n_pairs; t += t_step, ++ct) {
             const int m0 = (2 * (t / tiles_n) + rank) * Cfg::BLOCK_M, n0 = (t % tiles_n) * Cfg::BLOCK_N;
             const int buf = ct & 1;
-            mbar_wait(&acc_full[buf], (ct >> 1) & 1);
+            mbar_wait_parked(&acc_full[buf], (ct >> 1) & 1);
             tc_fence_after_sync();
 #pragma unroll 1
             for (int pass = 0; pass < 2; ++pass) {

@@ -57,6 +57,29 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, 
     }
 }
 
+// Long waits next to warps that need the issue slots: try_wait with a suspend-time hint.  The plain form returns after
+// a few tens of cycles, so eight drain warps polling (try_wait + clock check + branch, ~10 instructions per round) took
+// about a third of the SM's issue slots away from the operand splitters (ncu source page of gemm_bc_2sm_kernel: 11 M poll
+// rounds per launch).  With the hint the hardware parks the warp until the phase completes or the limit passes.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_hint(bar, parity, 4000u)) {
+        if (clock64() - t0 > 4000000000LL) __trap();
+    }
+}
+
 // ------------------------------------------------------------------------------------------ fences
 __device__ __forceinline__ void fence_proxy_async_smem() {  // generic-proxy smem writes -> visible to TMA / tcgen05
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

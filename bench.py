@@ -459,7 +459,7 @@ def run_b200(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if wl.dtype == torch.float32 else "bf16", "data": "synthetic",
-            "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam (forward includes the CSR/CSC pack of dense A)",
+            "config": {"workload": wl.name, "step": "fwd+bwd+clip+adam (forward includes the CSR pack of dense A and its typed transpose)",
                        "graphs_per_gpu": B, "global_batch": world * B, "parallelism": f"dp{world}",
                        "l2": "inputs (V %.2f GB) larger than L2" % v_gb, "features": "dense U[0,1)",
                        "host_cpus_rank0": (f"{len(numa_cpus)} GPU-local cores" if numa_cpus else "unbound")},

@@ -25,6 +25,51 @@ ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __res
     const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
     float loss_sum = 0.f, w_sum = 0.f, bad = 0.f;
+    if (C <= 64) {
+        // a row fits two registers per lane: loaded once, the next row (and its label) prefetched while this one is reduced,
+        // x[y] taken from the registers by a shuffle.  Same operations in the same order as the general loop below; that one
+        // paid four dependent memory latencies per row (49 us for 128 000 rows of 53 classes).
+        const int c1 = lane + 32;
+        float n0 = -INFINITY, n1 = -INFINITY;
+        int64_t ny = 0;
+        if (warp < M) {
+            const float* x = logits + warp * ld;
+            if (lane < C) n0 = x[lane];
+            if (c1 < C) n1 = x[c1];
+            ny = target[warp];
+        }
+        for (int64_t r = warp; r < M; r += n_warps) {
+            const float v0 = n0, v1 = n1;
+            const int64_t y = ny;
+            const int64_t rn = r + n_warps;
+            if (rn < M) {
+                const float* x = logits + rn * ld;
+                n0 = lane < C ? x[lane] : -INFINITY;
+                n1 = c1 < C ? x[c1] : -INFINITY;
+                ny = target[rn];
+            }
+            float m = -INFINITY;
+            if (lane < C) m = fmaxf(m, v0);
+            if (c1 < C) m = fmaxf(m, v1);
+            for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            float s = 0.f;
+            if (lane < C) s += expf(v0 - m);
+            if (c1 < C) s += expf(v1 - m);
+            for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            const float l = m + logf(s);
+            if (lane == 0) lse[r] = l;
+            const bool ok = y != ignore_index && y >= 0 && y < C;
+            const int yy = ok ? static_cast<int>(y) : 0;
+            const float xy = __shfl_sync(0xffffffffu, yy < 32 ? v0 : v1, yy & 31);
+            if (ok) {
+                const float w = weight ? weight[y] : 1.0f;
+                loss_sum += w * (l - xy);
+                w_sum += w;
+            } else if (y != ignore_index) {
+                bad += 1.0f;
+            }
+        }
+    } else
     for (int64_t r = warp; r < M; r += n_warps) {
         const float* x = logits + r * ld;
         float m = -INFINITY;

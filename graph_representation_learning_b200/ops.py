@@ -411,6 +411,7 @@ def _linear_grads(dY: torch.Tensor, y: Optional[torch.Tensor], xs: Sequence[torc
         epilogue_bwd_(dY, y, dZ, relu, p)
     else:
         dZ = dY
+    dZ = _tma_ready(dZ)          # a width like 53 is re-laid to a 16-byte pitch ONCE, for the dW and the dX products alike
     if want_w:
         parts = [gemm_tn(x, dZ, bwd, cache) if weight_is_kn else gemm_tn(dZ, x, bwd, cache) for x in xs]
         d_weight = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0 if weight_is_kn else 1)

@@ -109,6 +109,9 @@ SIGNATURES = {
     "grl_gemm_tn_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int64,
                                  c_void_p, c_size_t, c_void_p]),
     "grl_split_tf32": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "grl_split_tf32_strided": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "grl_split_tf32_mix_strided": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int,
+                                           c_void_p]),
     "grl_dz_split_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "grl_dz_split": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64,
                              c_int, c_uint32, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -448,7 +448,8 @@ int launch_gemm_bc(const GemmArgs& a, GemmParams p, cudaStream_t st, bool x3, in
 // Weight operand: hi = src rounded to nearest tf32 (fp32 storage), packed = bf16 [rows, 2 * ceil4(cols)] with 16-byte
 // chunk c of a row = {hi[4c..4c+3], lo[4c..4c+3]} (lo = src - hi), zeros past cols.
 __global__ void split_tf32_mix_kernel(const float* __restrict__ src, int64_t ld_src, float* __restrict__ hi, int64_t ld_hi,
-                                      uint4* __restrict__ packed, int64_t ld_packed_chunks, int64_t rows, int cols) {
+                                      uint4* __restrict__ packed, int64_t ld_packed_chunks, int64_t rows, int cols,
+                                      int64_t cs) {          // cs: element stride between the columns of `src`
     const int chunks = (cols + 3) / 4;
     const int64_t total = rows * chunks;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -459,7 +460,7 @@ __global__ void split_tf32_mix_kernel(const float* __restrict__ src, int64_t ld_
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             const int k = 4 * c + e;
-            const float v = k < cols ? src[r * ld_src + k] : 0.0f;
+            const float v = k < cols ? src[r * ld_src + k * cs] : 0.0f;
             h[e] = __uint_as_float(tf32_rn_bits(__float_as_uint(v)));
             l[e] = v - h[e];
             if (k < cols) hi[r * ld_hi + k] = h[e];
@@ -671,7 +672,24 @@ extern "C" int grl_split_tf32_mix(const float* src, int64_t ld_src, float* hi, i
     int64_t blocks = (rows * (c4 / 4) + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     split_tf32_mix_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        src, ld_src, hi, ld_hi, static_cast<uint4*>(packed), ld_packed / 8, rows, cols);
+        src, ld_src, hi, ld_hi, static_cast<uint4*>(packed), ld_packed / 8, rows, cols, 1);
+    GRL_LAUNCH_CHECK("split_tf32_mix_kernel");
+    return 0;
+}
+
+extern "C" int grl_split_tf32_mix_strided(const float* src, int64_t stride_row, int64_t stride_col, float* hi, int64_t ld_hi,
+                                          void* packed, int64_t ld_packed, int64_t rows, int cols, void* stream) {
+    GRL_CHECK_ARG(src && hi && packed, GRL_E_BADARG, "grl_split_tf32_mix_strided: null pointer");
+    const int64_t c4 = (static_cast<int64_t>(cols) + 3) / 4 * 4;
+    GRL_CHECK_ARG(rows >= 0 && cols > 0 && stride_row > 0 && stride_col > 0 && ld_hi >= cols && ld_packed >= 2 * c4, GRL_E_BADARG,
+                  "grl_split_tf32_mix_strided: bad shape");
+    GRL_CHECK_ARG(ld_packed % 8 == 0 && aligned_to(packed, 16), GRL_E_ALIGN,
+                  "grl_split_tf32_mix_strided: packed rows need a 16-byte aligned base and pitch");
+    if (rows == 0) return 0;
+    int64_t blocks = (rows * (c4 / 4) + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    split_tf32_mix_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        src, stride_row, hi, ld_hi, static_cast<uint4*>(packed), ld_packed / 8, rows, cols, stride_col);
     GRL_LAUNCH_CHECK("split_tf32_mix_kernel");
     return 0;
 }

@@ -480,14 +480,15 @@ gemm_tn_bf16_kernel(const GemmParams p, const int kb_per_split, const __grid_con
     if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
+// cs: element stride between the columns of `src` (1 = row-major; a transposed weight view has cs = its pitch, ld_src = 1)
 __global__ void split_tf32_kernel(const float* __restrict__ src, int64_t ld_src, float* __restrict__ hi,
-                                  float* __restrict__ lo, int64_t ld_dst, int64_t rows, int cols) {
+                                  float* __restrict__ lo, int64_t ld_dst, int64_t rows, int cols, int64_t cs) {
     const int64_t total = rows * cols;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += stride) {
         const int64_t r = t / cols;
         const int c = static_cast<int>(t - r * cols);
-        const float v = src[r * ld_src + c];
+        const float v = src[r * ld_src + c * cs];
         const float h = __uint_as_float(tf32_rn_bits(__float_as_uint(v)));
         hi[r * ld_dst + c] = h;
         lo[r * ld_dst + c] = __uint_as_float(tf32_rn_bits(__float_as_uint(v - h)));
@@ -506,7 +507,21 @@ extern "C" int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float
     int64_t blocks = (rows * cols + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     split_tf32_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, ld_src, hi, lo, ld_dst,
-                                                                                             rows, cols);
+                                                                                             rows, cols, 1);
+    GRL_LAUNCH_CHECK("split_tf32_kernel");
+    return 0;
+}
+
+extern "C" int grl_split_tf32_strided(const float* src, int64_t stride_row, int64_t stride_col, float* hi, float* lo,
+                                      int64_t ld_dst, int64_t rows, int cols, void* stream) {
+    GRL_CHECK_ARG(src && hi && lo, GRL_E_BADARG, "grl_split_tf32_strided: null pointer");
+    GRL_CHECK_ARG(rows >= 0 && cols > 0 && stride_row > 0 && stride_col > 0 && ld_dst >= cols, GRL_E_BADARG,
+                  "grl_split_tf32_strided: bad shape");
+    if (rows == 0) return 0;
+    int64_t blocks = (rows * cols + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    split_tf32_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, stride_row, hi, lo, ld_dst,
+                                                                                             rows, cols, stride_col);
     GRL_LAUNCH_CHECK("split_tf32_kernel");
     return 0;
 }

@@ -168,12 +168,16 @@ def _prep_weight(b_view: torch.Tensor, dtype: torch.dtype, mode: int):
     N, K = b_view.shape
     m = _ld_multiple(dtype)
     Kp = (K + m - 1) // m * m
+    # fp32 weight views are split where they lie (any strides: h_weights and nn.Linear weights are wanted in both
+    # orientations); the contiguous copy that used to come first was one more launch per operand
+    if mode in (_lib.GEMM_TF32_BF16C, _lib.GEMM_TF32X3):
+        src = b_view if b_view.dtype == torch.float32 else b_view.float()
     if mode == _lib.GEMM_TF32_BF16C:
-        src = b_view.float().contiguous()
         hi = torch.empty(N, Kp, dtype=torch.float32, device=b_view.device)
         packed = torch.empty(N, 2 * Kp, dtype=torch.bfloat16, device=b_view.device)
-        _lib.check(_lib.load().grl_split_tf32_mix(src.data_ptr(), K, hi.data_ptr(), Kp, packed.data_ptr(), 2 * Kp, N, K,
-                                                  _lib.stream_ptr(src.device)), "grl_split_tf32_mix")
+        _lib.check(_lib.load().grl_split_tf32_mix_strided(src.data_ptr(), src.stride(0), src.stride(1), hi.data_ptr(), Kp,
+                                                          packed.data_ptr(), 2 * Kp, N, K, _lib.stream_ptr(src.device)),
+                   "grl_split_tf32_mix_strided")
         _lib.count_launch(1)
         return hi[:, :K], packed
     if mode != _lib.GEMM_TF32X3:
@@ -182,11 +186,10 @@ def _prep_weight(b_view: torch.Tensor, dtype: torch.dtype, mode: int):
         buf = torch.empty(N, Kp, dtype=dtype, device=b_view.device)
         buf[:, :K].copy_(b_view)
         return buf[:, :K], None
-    src = b_view.float().contiguous()
     hi = torch.empty(N, Kp, dtype=torch.float32, device=b_view.device)
     lo = torch.empty(N, Kp, dtype=torch.float32, device=b_view.device)
-    _lib.check(_lib.load().grl_split_tf32(src.data_ptr(), K, hi.data_ptr(), lo.data_ptr(), Kp, N, K,
-                                          _lib.stream_ptr(src.device)), "grl_split_tf32")
+    _lib.check(_lib.load().grl_split_tf32_strided(src.data_ptr(), src.stride(0), src.stride(1), hi.data_ptr(), lo.data_ptr(), Kp,
+                                                  N, K, _lib.stream_ptr(src.device)), "grl_split_tf32_strided")
     _lib.count_launch(1)
     return hi[:, :K], lo[:, :K]
 

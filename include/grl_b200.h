@@ -341,6 +341,13 @@ int grl_split_tf32_mix(const float* src, int64_t ld_src, float* hi, int64_t ld_h
 /* hi = src rounded to the nearest tf32 (10 explicit mantissa bits), lo = (src - hi) rounded to the nearest tf32. */
 int grl_split_tf32(const float* src, int64_t ld_src, float* hi, float* lo, int64_t ld_dst,
                    int64_t rows, int cols, void* stream);
+/* The two splits over a STRIDED source, src[r * stride_row + c * stride_col] (elements): a transposed weight view
+ * (GraphConv.h_weights is [in, out], nn.Linear [out, in]; the backward products want the other orientation) is split in
+ * place instead of being copied contiguous first. */
+int grl_split_tf32_strided(const float* src, int64_t stride_row, int64_t stride_col, float* hi, float* lo, int64_t ld_dst,
+                           int64_t rows, int cols, void* stream);
+int grl_split_tf32_mix_strided(const float* src, int64_t stride_row, int64_t stride_col, float* hi, int64_t ld_hi,
+                               void* packed, int64_t ld_packed, int64_t rows, int cols, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * NodeSelfAtten core (per graph, dense, unscaled, unmasked; exact two-pass softmax, fp32 arithmetic):

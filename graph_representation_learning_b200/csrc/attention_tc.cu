@@ -788,35 +788,114 @@ __global__ void attn_split_kernel(const T* __restrict__ x, int64_t ld, int64_t r
     }
 }
 
+// The same, eight consecutive columns per thread: 16-byte loads and one 16-byte store per piece (the element-per-thread
+// form above -- a 64-bit division and 2-byte stores per element -- took 73 us for the 128 000 x 128 h operand of cfg2).
+// Needs C % 8 == 0 and 16-byte aligned rows of x / out.
+__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 a = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        v[2 * k] = __uint_as_float(w[k] << 16);
+        v[2 * k + 1] = __uint_as_float(w[k] & 0xFFFF0000u);
+    }
+}
+// v -> np bf16 pieces of eight values each, stored as one uint4 per piece at out + pc * piece_stride
+__device__ __forceinline__ void split_store8(float (&v)[8], int np, __nv_bfloat16* out, int64_t piece_stride) {
+    for (int pc = 0; pc < np; ++pc) {
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const __nv_bfloat16 a = __float2bfloat16_rn(v[2 * k]), b = __float2bfloat16_rn(v[2 * k + 1]);
+            w[k] = static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
+            v[2 * k] -= __bfloat162float(a);
+            v[2 * k + 1] -= __bfloat162float(b);
+        }
+        *reinterpret_cast<uint4*>(out + pc * piece_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+template <typename T>
+__global__ void attn_split_vec8_kernel(const T* __restrict__ x, int64_t ld, int64_t rows, int C, const float* __restrict__ scale,
+                                       int np, __nv_bfloat16* __restrict__ out) {
+    const int c8 = C >> 3;
+    const int64_t total8 = rows * c8, total = rows * C;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total8; t += stride) {
+        const int64_t r = t / c8;
+        const int c = static_cast<int>(t - r * c8) << 3;
+        float v[8];
+        load8(x + r * ld + c, v);
+        if (scale) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] *= __ldg(scale + c + e);
+        }
+        split_store8(v, np, out + r * C + c, total);
+    }
+}
+
 // Backward preparation, one pass over dOut and o: do = gamma * dOut as np bf16 pieces and the per-block partial sums of
 // d(gamma)_c = sum_i dOut_ic o_ic (rows of a block in order; the caller adds the blocks up).  D_i is computed by the
 // query-major kernel itself.
 // Block = 256 threads = 8 warps over kPrepRows rows.
 constexpr int kPrepRows = 64;
+__device__ __forceinline__ void load4(const float* p, float (&v)[4]) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+__device__ __forceinline__ void load4(const __nv_bfloat16* p, float (&v)[4]) {
+    const uint2 a = *reinterpret_cast<const uint2*>(p);
+    v[0] = __uint_as_float(a.x << 16); v[1] = __uint_as_float(a.x & 0xFFFF0000u);
+    v[2] = __uint_as_float(a.y << 16); v[3] = __uint_as_float(a.y & 0xFFFF0000u);
+}
+// One pass: a lane owns four consecutive columns (16-byte loads of dOut and o, one 8-byte store per piece) and carries
+// their dOut * o sums over its warp's rows; the eight warps' sums are added in warp order.  H % 4 == 0, H <= 256.
+// (The first version stored 2 bytes per thread and then re-read dOut and o column by column with half the block idle:
+// 97 us at cfg2.)
 template <typename T>
 __global__ void __launch_bounds__(256)
 attn_bwd_prep_kernel(const T* __restrict__ dOut, const float* __restrict__ o, const float* __restrict__ gamma, int64_t rows,
                      int H, int np, __nv_bfloat16* __restrict__ do_p, float* __restrict__ part) {
+    __shared__ float red[8][256];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kPrepRows;
     const int64_t total = rows * H;
-    for (int rr = wib; rr < kPrepRows; rr += 8) {
-        const int64_t r = r0 + rr;
-        if (r >= rows) break;
-        for (int c = lane; c < H; c += 32) {
-            float v = to_float(dOut[r * H + c]) * gamma[c];
+    for (int c = lane * 4; c < H; c += 128) {
+        const float4 gm = make_float4(__ldg(gamma + c), __ldg(gamma + c + 1), __ldg(gamma + c + 2), __ldg(gamma + c + 3));   // a parameter view: 4-byte aligned
+        float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        for (int rr = wib; rr < kPrepRows; rr += 8) {
+            const int64_t r = r0 + rr;
+            if (r >= rows) break;
+            float d[4];
+            load4(dOut + r * H + c, d);
+            const float4 ov = *reinterpret_cast<const float4*>(o + r * H + c);
+            acc[0] = fmaf(d[0], ov.x, acc[0]); acc[1] = fmaf(d[1], ov.y, acc[1]);
+            acc[2] = fmaf(d[2], ov.z, acc[2]); acc[3] = fmaf(d[3], ov.w, acc[3]);
+            float v[4] = {d[0] * gm.x, d[1] * gm.y, d[2] * gm.z, d[3] * gm.w};
             for (int pc = 0; pc < np; ++pc) {
-                const __nv_bfloat16 h = __float2bfloat16_rn(v);
-                do_p[pc * total + r * H + c] = h;
-                v -= __bfloat162float(h);
+                uint32_t w[2];
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const __nv_bfloat16 a = __float2bfloat16_rn(v[2 * k]), b = __float2bfloat16_rn(v[2 * k + 1]);
+                    w[k] = static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
+                    v[2 * k] -= __bfloat162float(a);
+                    v[2 * k + 1] -= __bfloat162float(b);
+                }
+                *reinterpret_cast<uint2*>(do_p + pc * total + r * H + c) = make_uint2(w[0], w[1]);
             }
         }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) red[wib][c + e] = acc[e];
     }
-    const int64_t r_end = r0 + kPrepRows < rows ? r0 + kPrepRows : rows;
+    __syncthreads();
     for (int c = threadIdx.x; c < H; c += 256) {
-        float acc = 0.0f;
-        for (int64_t r = r0; r < r_end; ++r) acc = fmaf(to_float(dOut[r * H + c]), o[r * H + c], acc);
-        part[static_cast<int64_t>(blockIdx.x) * H + c] = acc;
+        float sum = 0.0f;
+#pragma unroll
+        for (int w8 = 0; w8 < 8; ++w8) sum += red[w8][c];
+        part[static_cast<int64_t>(blockIdx.x) * H + c] = sum;
     }
 }
 
@@ -936,6 +1015,18 @@ extern "C" int grl_attn_split(const void* x, int64_t ld, int dtype, int64_t rows
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     __nv_bfloat16* out = static_cast<__nv_bfloat16*>(pieces);
+    const int es = dtype == GRL_F32 ? 4 : 2;
+    if ((dtype == GRL_F32 || dtype == GRL_BF16) && C % 8 == 0 && (ld * es) % 16 == 0 && aligned_to(x, 16) && aligned_to(out, 16)) {
+        int64_t b8 = (rows * (C / 8) + 255) / 256;
+        if (b8 > kNumSMs * 16) b8 = kNumSMs * 16;
+        if (dtype == GRL_F32)
+            attn_split_vec8_kernel<float><<<static_cast<int>(b8), 256, 0, st>>>(static_cast<const float*>(x), ld, rows, C, scale, np, out);
+        else
+            attn_split_vec8_kernel<__nv_bfloat16><<<static_cast<int>(b8), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld, rows, C,
+                                                                                      scale, np, out);
+        GRL_LAUNCH_CHECK("attn_split_vec8_kernel");
+        return 0;
+    }
     if (dtype == GRL_F32)
         attn_split_kernel<float><<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const float*>(x), ld, rows, C, scale, np, out);
     else if (dtype == GRL_BF16)
@@ -980,8 +1071,8 @@ extern "C" int grl_selfatten_tc_bwd(const void* dOut, const float* o_save, const
     int npf, nps, npb;
     GRL_CHECK_ARG(tc_config(io_dtype, H, D, &npf, &nps, &npb), GRL_E_UNSUP,
                   "grl_selfatten_tc_bwd: (dtype %d, H %d, D %d) has no tensor-core instantiation", io_dtype, H, D);
-    GRL_CHECK_ARG(aligned_to(do_p, 16) && aligned_to(df, 16) && aligned_to(dg, 16) && aligned_to(dh, 16), GRL_E_ALIGN,
-                  "grl_selfatten_tc_bwd: 16-byte aligned pointers");
+    GRL_CHECK_ARG(aligned_to(do_p, 16) && aligned_to(df, 16) && aligned_to(dg, 16) && aligned_to(dh, 16) && aligned_to(dOut, 16) &&
+                      aligned_to(o_save, 16), GRL_E_ALIGN, "grl_selfatten_tc_bwd: 16-byte aligned pointers");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int64_t rows = static_cast<int64_t>(B) * N;
     const int blocks = static_cast<int>((rows + kPrepRows - 1) / kPrepRows);
